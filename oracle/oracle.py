@@ -1,0 +1,199 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes front-end for the CPU oracle.
+
+`libmsoracle.so`  : fp64 C restatement of the hot path (oracle/ms_oracle.c).
+`_ref/libmsref.so`: the reference's own float32 C++ compiled in place from
+                    /root/reference (oracle/ref_shim.cpp), when it was built.
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline leg and
+--impl reference) may import this module.  The product package never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_REF = None
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+
+
+def build():
+    """Compile the C restatement (and oracle/_ref when /root/reference exists)."""
+    subprocess.run(["make", "-s", "-C", _HERE], check=True, stdout=subprocess.DEVNULL)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libmsoracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        L.orc_ghosts.restype = C.c_int64
+        L.orc_ghosts.argtypes = [_f32p, C.c_int64, _f32p, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_mesh_normals.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, _f64p]
+        L.orc_pointareas.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, _f64p]
+        L.orc_curvatures.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, C.c_double, C.c_double, _f64p, _f64p]
+        L.orc_face_keep.argtypes = [_f32p, _u32p, C.c_int64, C.c_double, C.c_double, _u8p]
+        L.orc_kde.argtypes = [_f32p, C.c_int64, _i32p, C.c_int64, C.c_int, C.c_int, _f32p, C.c_float, C.c_int, _f64p]
+        L.orc_kde_raw.argtypes = [_f32p, C.c_int64, _i32p, C.c_int64, C.c_int, C.c_int, _f32p, C.c_float, _f64p]
+        L.orc_knn_brute.argtypes = [_f32p, C.c_int64, C.c_int, _i32p, C.c_void_p]
+        L.orc_knn_grid.argtypes = [_f32p, C.c_int64, C.c_int, _i32p, C.c_void_p]
+        L.orc_pca_normals.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p]
+        L.orc_mst_orient.restype = C.c_int64
+        L.orc_mst_orient.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p, _u8p]
+        _LIB = L
+    return _LIB
+
+
+def ref():
+    """The compiled reference (float32), or None when oracle/_ref was not built."""
+    global _REF
+    if _REF is None:
+        path = os.path.join(_HERE, "_ref", "libmsref.so")
+        if not os.path.exists(path):
+            return None
+        R = C.CDLL(path)
+        R.msref_need_normals.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _f32p]
+        R.msref_need_pointareas.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _f32p]
+        R.msref_kde.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, C.c_int,
+                                _i32p, C.c_int, _f32p]
+        _REF = R
+    return _REF
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _faces(f):
+    return np.ascontiguousarray(f, dtype=np.uint32).reshape(-1, 3)
+
+
+# ---------------------------------------------------------------------------- fp64 restatement
+def ghosts(points, bbox, blayer=0.2):
+    """PointSet.cpp:94-147 -> (ghost points (G,3) f32, source index (G,) i32)."""
+    p = _f32(points)
+    box = _f32(np.asarray(bbox).reshape(-1))
+    n = lib().orc_ghosts(p, p.shape[0], box, blayer, None, None)
+    out = np.empty((n, 3), np.float32)
+    src = np.empty((n,), np.int32)
+    lib().orc_ghosts(p, p.shape[0], box, blayer, out.ctypes.data, src.ctypes.data)
+    return out, src
+
+
+def mesh_normals(verts, faces):
+    v, f = _f32(verts), _faces(faces)
+    out = np.empty((v.shape[0], 3), np.float64)
+    lib().orc_mesh_normals(v, v.shape[0], f, f.shape[0], out)
+    return out
+
+
+def pointareas(verts, faces):
+    v, f = _f32(verts), _faces(faces)
+    out = np.empty((v.shape[0],), np.float64)
+    lib().orc_pointareas(v, v.shape[0], f, f.shape[0], out)
+    return out
+
+
+def curvatures(verts, faces, half_box=None):
+    """half_box = (xw, yw) enables the trimesh.py:484-499 face filter."""
+    v, f = _f32(verts), _faces(faces)
+    xw, yw = (-1.0, -1.0) if half_box is None else (float(half_box[0]), float(half_box[1]))
+    H = np.empty((v.shape[0],), np.float64)
+    K = np.empty((v.shape[0],), np.float64)
+    rc = lib().orc_curvatures(v, v.shape[0], f, f.shape[0], xw, yw, H, K)
+    assert rc == 0
+    return H, K
+
+
+def kde(verts, ids, type, sigma, get_counts, bbox=None, raw=False):
+    v = _f32(verts)
+    ids = np.ascontiguousarray(ids, dtype=np.int32).reshape(-1)
+    periodic = bbox is not None
+    box = _f32(np.asarray(bbox).reshape(-1)) if periodic else np.zeros(6, np.float32)
+    out = np.empty((v.shape[0],), np.float64)
+    if raw:
+        lib().orc_kde_raw(v, v.shape[0], ids, ids.shape[0], type, int(periodic), box, sigma, out)
+    else:
+        lib().orc_kde(v, v.shape[0], ids, ids.shape[0], type, int(periodic), box, sigma, int(get_counts), out)
+    return out
+
+
+def knn(points, k1, brute=False, with_d2=False):
+    p = _f32(points)
+    nbr = np.empty((p.shape[0], k1), np.int32)
+    d2 = np.empty((p.shape[0], k1), np.float64) if with_d2 else None
+    fn = lib().orc_knn_brute if brute else lib().orc_knn_grid
+    fn(p, p.shape[0], k1, nbr, d2.ctypes.data if with_d2 else None)
+    return (nbr, d2) if with_d2 else nbr
+
+
+def pca_normals(points, nbr):
+    p = _f32(points)
+    nbr = np.ascontiguousarray(nbr, dtype=np.int32)
+    out = np.empty((p.shape[0], 3), np.float64)
+    lib().orc_pca_normals(p, p.shape[0], nbr, nbr.shape[1], out)
+    return out
+
+
+def mst_orient(points, nbr, normals):
+    """Returns (oriented normals (M,3) f64, oriented flags (M,) u8, n_unoriented)."""
+    p = _f32(points)
+    nbr = np.ascontiguousarray(nbr, dtype=np.int32)
+    n = np.array(normals, dtype=np.float64, order="C", copy=True)
+    flags = np.zeros((p.shape[0],), np.uint8)
+    bad = lib().orc_mst_orient(p, p.shape[0], nbr, nbr.shape[1], n, flags)
+    return n, flags, int(bad)
+
+
+def point_normals(points, bbox=None, blayer=0.2, knbrs=18, ndir_hint=+1, return_all=False):
+    """Membrane.compute_pnormals (membrane.py:124-157) end to end, fp64."""
+    p = _f32(points)
+    n = p.shape[0]
+    allp = p
+    if bbox is not None:
+        g, _ = ghosts(p, bbox, blayer)
+        allp = np.ascontiguousarray(np.concatenate([p, g], axis=0))
+    nbr = knn(allp, knbrs + 1)
+    nrm = pca_normals(allp, nbr)
+    nrm, flags, bad = mst_orient(allp, nbr, nrm)
+    out = nrm[:n].copy()
+    imax = int(np.argmax(np.abs(out[:, 2].astype(np.float32))))
+    if out[imax, 2] * ndir_hint < 0:
+        out *= -1.0
+    if return_all:
+        return out, dict(points=allp, nbr=nbr, normals_all=nrm, oriented=flags, n_unoriented=bad)
+    return out
+
+
+# ---------------------------------------------------------------------------- compiled reference (float32)
+def ref_need_normals(verts, faces):
+    v, f = _f32(verts), _faces(faces)
+    out = np.empty((v.shape[0], 3), np.float32)
+    assert ref().msref_need_normals(v, v.shape[0], f, f.shape[0], out) == 0
+    return out
+
+
+def ref_need_pointareas(verts, faces):
+    v, f = _f32(verts), _faces(faces)
+    out = np.empty((v.shape[0],), np.float32)
+    assert ref().msref_need_pointareas(v, v.shape[0], f, f.shape[0], out) == 0
+    return out
+
+
+def ref_kde(verts, ids, type, sigma, get_counts, bbox=None):
+    v = _f32(verts)
+    ids = np.ascontiguousarray(ids, dtype=np.int32).reshape(-1)
+    periodic = bbox is not None
+    box = _f32(np.asarray(bbox).reshape(-1)) if periodic else np.zeros(6, np.float32)
+    out = np.empty((v.shape[0],), np.float32)
+    assert ref().msref_kde(v, v.shape[0], type, int(get_counts), sigma, int(periodic), box, 6, ids, ids.shape[0], out) == 0
+    return out
