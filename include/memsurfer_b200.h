@@ -1,0 +1,122 @@
+/* memsurfer_b200.h -- C ABI of libmemsurfer_b200.so (hand-written sm_100a CUDA).
+ *
+ * Drop-in replacement for the native half of MemSurfer's per-frame hot path.
+ * Every entry point names the reference interface it replaces (paths under
+ * the LLNL/MemSurfer tree).  Conventions:
+ *   - all array arguments are DEVICE pointers (HBM) unless marked "host";
+ *   - the caller owns every buffer, including the workspace `ws` whose size is
+ *     returned by the matching *_workspace_bytes(); nothing is allocated or
+ *     kept by the library (no global mutable state; re-entrant per stream);
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on
+ *     it except where "syncs" is noted (a small device->host read-back);
+ *   - return value: 0 = ok, non-zero = error (see ms_last_error(), a
+ *     thread-local string).  Nothing throws across this boundary (the
+ *     reference aborts the interpreter on C++ exceptions: memsurfer.i has no
+ *     %exception);
+ *   - arithmetic is fp64 on the float32-valued inputs; *_f32 outputs are the
+ *     reference's dtypes (may be NULL), *_f64 the full-precision twins.
+ */
+#ifndef MEMSURFER_B200_H
+#define MEMSURFER_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int         ms_version(void);
+const char *ms_last_error(void);
+
+/* ---------------------------------------------------------------- point normals
+ * Replaces memsurfer_cmod.PointSet: set_periodic (PointSet.cpp:94-147),
+ * need_normals -> CGAL::pca_estimate_normals + CGAL::mst_orient_normals
+ * (PointSet.cpp:156-200), get_normals (PointSet.cpp:70-88) and the global flip
+ * of Membrane.compute_pnormals (membrane.py:145-152).                          */
+
+/* Upper bound of points incl. ghost images (each point gets <= 3 images). */
+int64_t ms_pointset_capacity(int64_t n, int periodic);
+
+/* Stage 1: ghost images.  points (n,3) f32 -> points_all (cap,3) f32 = points ++ ghosts in the
+ * reference's order; ghost_src (cap,) i32 = original index of every row.  box6 (host) =
+ * {b0x,b0y,b0z,b1x,b1y,b1z} as float32; blayer in (0,1).  periodic == 0 copies the points only.
+ * *m_out (host) receives n + #ghosts.  Syncs the stream once.                                  */
+size_t ms_ghosts_workspace_bytes(int64_t n);
+int ms_ghosts(const float *points, int64_t n, int periodic, const float *box6, float blayer,
+              float *points_all, int32_t *ghost_src, int64_t *m_out,
+              void *ws, size_t ws_bytes, void *stream);
+
+/* Stage 2: exact (k1 = k+1)-nearest neighbours incl. self for all m points, sorted by
+ * (squared distance in fp64, index), via a uniform xy cell list.  nbr (m,k1) i32.             */
+size_t ms_knn_workspace_bytes(int64_t m, int k1);
+int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
+           void *ws, size_t ws_bytes, void *stream);
+
+/* Stage 3: PCA normal of every point from its k1 neighbours (unit eigenvector of the smallest
+ * eigenvalue of the 3x3 covariance; sign arbitrary).  normals (m,3) f64.                      */
+int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
+                   double *normals, void *stream);
+
+/* Stage 4: minimum-spanning-tree orientation over the Riemannian graph (edge {a<b} iff b in
+ * NN(a), weight float(max(0,1-|na.nb|)), ties by (w,a,b)); source = first max-z point flipped
+ * to n_z >= 0.  normals updated in place.  *n_unoriented (host) = points not connected to the
+ * source.  Syncs the stream.                                                                   */
+size_t ms_orient_workspace_bytes(int64_t m, int k1);
+int ms_orient_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
+                      double *normals, int64_t *n_unoriented,
+                      void *ws, size_t ws_bytes, void *stream);
+
+/* Stage 5: first n normals -> float32, flipped globally if the z of the normal with the largest
+ * |n_z| (float32) times ndir_hint is negative (membrane.py:148-152).                            */
+size_t ms_finish_workspace_bytes(int64_t n);
+int ms_finish_pnormals(const double *normals, int64_t n, int ndir_hint,
+                       float *pnormals_f32, double *pnormals_f64,
+                       void *ws, size_t ws_bytes, void *stream);
+
+/* ---------------------------------------------------------------- mesh properties
+ * Replaces memsurfer_cmod.TriMesh.need_normals / need_pointareas (TriMesh.hpp:346-407,
+ * TriMesh.cpp:99-190) and the vtkCurvatures calls of TriMesh.compute_curvatures
+ * (trimesh.py:284-316, mesh assembly + half-box face filter trimesh.py:441-500).
+ *
+ * verts_all (nv_all,3) f32 = vertices ++ duplicated verts; faces_all (nf,3) u32 = faces ++
+ * trimmed faces (the concatenation of TriMesh.hpp:360-364); outputs cover the first nv rows.   */
+
+/* Vertex -> incident (face,corner) lists in ascending order (CSR) + the per-face keep mask of
+ * the half-box filter (half_xw/half_yw < 0 disables it).  csr_off (nv+1) i32,
+ * csr_adj (3*nf) i32 packed face*4+corner, keep (nf) u8.                                        */
+size_t ms_mesh_topology_workspace_bytes(int64_t nv, int64_t nf);
+int ms_mesh_topology(const float *verts_all, int64_t nv_all, int64_t nv,
+                     const uint32_t *faces_all, int64_t nf, double half_xw, double half_yw,
+                     int32_t *csr_off, int32_t *csr_adj, uint8_t *keep,
+                     void *ws, size_t ws_bytes, void *stream);
+
+/* One fused per-vertex gather: area-weighted vertex normals, mixed Voronoi point areas, mean
+ * (dihedral) and Gaussian (angle-deficit) curvature.  Any output may be NULL.                  */
+int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
+                       const uint32_t *faces_all, int64_t nf,
+                       const int32_t *csr_off, const int32_t *csr_adj, const uint8_t *keep,
+                       double *vnormals_f64, float *vnormals_f32,
+                       double *pareas_f64, float *pareas_f32,
+                       double *mean_curv, double *gaus_curv, void *stream);
+
+/* ---------------------------------------------------------------- KDE densities
+ * Replaces memsurfer_cmod.TriMesh.kde types 2 and 3 (TriMesh_kde.cpp:344-392, 443-532) with
+ * GaussianKernel2D/3D (DensityKernels.hpp:44-84) and DistanceSquared /
+ * DistancePeriodicXYSquared (DistanceKernels.hpp:75-136) fused in.
+ * verts (nv,3) f32 = the mesh's own vertices (targets: all of them); ids (nids) i32 = source
+ * vertex ids, nids == 0 -> all.  type 2|3.  periodic: box6 (host) = bboxl.  cutoff_sigmas <= 0:
+ * all pairs (the reference's sum); > 0: pairs beyond cutoff_sigmas*sigma are dropped through a
+ * cell list (relative tail mass exp(-c^2/2)).  get_counts as TriMesh_kde.cpp:515-524.          */
+size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids);
+int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+           int type, int periodic, const float *box6, float sigma, int get_counts,
+           double cutoff_sigmas, double *density_f64, float *density_f32,
+           void *ws, size_t ws_bytes, void *stream);
+
+/* fp64 FMA peak probe used for the KDE roofline: runs `iters` dependent-chain DFMA rounds on
+ * every SM and returns the number of FLOP issued in *flop (host); time it with events.         */
+int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

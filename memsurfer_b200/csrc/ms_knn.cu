@@ -1,0 +1,322 @@
+// ms_knn.cu -- point-normal estimation, stages 1-3: periodic ghost images, exact k-nearest
+// neighbours through a uniform xy cell list (one warp per query), PCA normal per point.
+//
+// Replaces (LLNL/MemSurfer): PointSet::set_periodic memsurfer/src/PointSet.cpp:94-147 and the
+// CGAL::pca_estimate_normals call of PointSet::need_normals PointSet.cpp:163-165 (kd-tree
+// (k+1)-NN + 3x3 covariance + eigen-solve; CGAL 4.13 itself is not in the tree -- algorithm as
+// in SURVEY.md Appendix A.1).
+//
+// Parity notes: ghosts are materialised explicitly, in the reference's order and with its
+// float32 rounding, so neighbour INDICES are comparable bit for bit.  Squared distances are formed
+// in fp64 as dx*dx + dy*dy + dz*dz without FMA contraction (this file is built --fmad=false);
+// ties break by ascending index.
+#include "ms_common.cuh"
+#include <float.h>
+
+// ------------------------------------------------------------------ stage 1: ghosts
+struct GhostCuts { float boxw0, boxw1, l0, l1, r0, r1; };
+
+__device__ __forceinline__ int ghost_flags(const float *__restrict__ p, const GhostCuts &c) {
+    const float x = __ldg(p), y = __ldg(p + 1);
+    const int lx = x < c.l0, ly = y < c.l1, rx = x > c.r0, ry = y > c.r1;
+    return lx | (rx << 1) | (ly << 2) | (ry << 3);
+}
+
+__global__ void __launch_bounds__(256) k_ghost_count(const float *__restrict__ pts, int64_t n, GhostCuts c, int32_t *cnt) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int f = ghost_flags(pts + 3*i, c);
+    const int hx = (f & 3) != 0, hy = (f & 12) != 0;
+    cnt[i] = hx + hy + (hx & hy);
+}
+
+__global__ void __launch_bounds__(256) k_ghost_fill(const float *__restrict__ pts, int64_t n, GhostCuts c,
+                                                    const int32_t *__restrict__ off, float *out, int32_t *src) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = pts[3*i], y = pts[3*i+1], z = pts[3*i+2];
+    out[3*i] = x; out[3*i+1] = y; out[3*i+2] = z; src[i] = (int32_t)i;
+    const int f = ghost_flags(pts + 3*i, c);
+    const int lx = f & 1, rx = (f >> 1) & 1, ly = (f >> 2) & 1, ry = (f >> 3) & 1;
+    if (!f) return;
+    // create_point(const float&...) narrows the double sums to float (PointSet.cpp:26-28,133-142)
+    const float gx = lx ? (float)((double)x + (double)c.boxw0) : (float)((double)x - (double)c.boxw0);
+    const float gy = ly ? (float)((double)y + (double)c.boxw1) : (float)((double)y - (double)c.boxw1);
+    int64_t g = n + off[i];
+    if (lx | rx) { out[3*g] = gx; out[3*g+1] = y;  out[3*g+2] = z; src[g] = (int32_t)i; g++; }
+    if (ly | ry) { out[3*g] = x;  out[3*g+1] = gy; out[3*g+2] = z; src[g] = (int32_t)i; g++; }
+    if ((lx | rx) && (ly | ry)) { out[3*g] = gx; out[3*g+1] = gy; out[3*g+2] = z; src[g] = (int32_t)i; }
+}
+
+__global__ void __launch_bounds__(256) k_copy_points(const float *__restrict__ pts, int64_t n, float *out, int32_t *src) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[3*i] = pts[3*i]; out[3*i+1] = pts[3*i+1]; out[3*i+2] = pts[3*i+2]; src[i] = (int32_t)i;
+}
+
+extern "C" int64_t ms_pointset_capacity(int64_t n, int periodic) { return periodic ? 4 * n : n; }
+extern "C" size_t ms_ghosts_workspace_bytes(int64_t n) {
+    return 2 * ms_align((size_t)(n + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(n) + 1024;
+}
+
+extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const float *box6, float blayer,
+                         float *points_all, int32_t *ghost_src, int64_t *m_out,
+                         void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(n > 0 && m_out, "ms_ghosts: bad arguments");
+    if (!periodic) {
+        k_copy_points<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, points_all, ghost_src);
+        MS_LAUNCH_CHECK();
+        *m_out = n;
+        return 0;
+    }
+    MS_REQUIRE(box6, "ms_ghosts: periodic point set needs the box");
+    MS_REQUIRE(blayer > 0.0f && blayer < 1.0f, "PointSet::set_periodic(): Invalid thickness of boundary layer (should be 0 < t < 1)! got %g", (double)blayer);
+    MS_REQUIRE(ws_bytes >= ms_ghosts_workspace_bytes(n), "ms_ghosts: workspace too small");
+    // float32 arithmetic exactly as PointSet.cpp:114-118 (volatile: keep each rounding step)
+    volatile float bw0 = box6[3] - box6[0], bw1 = box6[4] - box6[1];
+    volatile float t0 = blayer * bw0, t1 = blayer * bw1;
+    GhostCuts c; c.boxw0 = bw0; c.boxw1 = bw1;
+    c.l0 = box6[0] + t0; c.l1 = box6[1] + t1; c.r0 = box6[3] - t0; c.r1 = box6[4] - t1;
+    MsArena A(ws, ws_bytes);
+    int32_t *cnt = A.take<int32_t>(n + 1), *off = A.take<int32_t>(n + 1);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(n));
+    k_ghost_count<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, cnt);
+    if (ms_exclusive_scan_i32(cnt, off, n, scan_ws, s)) return 2;
+    k_ghost_fill<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, off, points_all, ghost_src);
+    MS_LAUNCH_CHECK();
+    int32_t total = 0;
+    MS_CUDA(cudaMemcpyAsync(&total, off + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *m_out = n + (int64_t)total;
+    return 0;
+}
+
+// ------------------------------------------------------------------ stage 2: cell list + exact kNN
+struct Grid { float lox, loy; double h, inv_h; int nx, ny; };
+
+__device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+
+// bb[0..3] = ordered-uint (min x, min y, max x, max y)
+__global__ void __launch_bounds__(256) k_bbox(const float *__restrict__ pts, int64_t m, unsigned *bb) {
+    unsigned mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0u, mxy = 0u;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned x = f2ord(pts[3*i]), y = f2ord(pts[3*i+1]);
+        mnx = min(mnx, x); mny = min(mny, y); mxx = max(mxx, x); mxy = max(mxy, y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+        mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o)); mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(bb, mnx); atomicMin(bb + 1, mny); atomicMax(bb + 2, mxx); atomicMax(bb + 3, mxy); }
+}
+
+__device__ __forceinline__ int cell_of(const Grid &g, float x, float y, int &cx, int &cy) {
+    cx = (int)(((double)x - (double)g.lox) * g.inv_h); cy = (int)(((double)y - (double)g.loy) * g.inv_h);
+    cx = max(0, min(g.nx - 1, cx)); cy = max(0, min(g.ny - 1, cy));
+    return cy * g.nx + cx;
+}
+
+__global__ void __launch_bounds__(256) k_cell_count(const float *__restrict__ pts, int64_t m, Grid g, int32_t *cell, int32_t *cnt) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    int cx, cy; const int c = cell_of(g, pts[3*i], pts[3*i+1], cx, cy);
+    cell[i] = c; atomicAdd(cnt + c, 1);
+}
+
+// sorted[p] = (x, y, z, original index as int bits) grouped by cell
+__global__ void __launch_bounds__(256) k_cell_scatter(const float *__restrict__ pts, int64_t m, const int32_t *__restrict__ cell,
+                                                      const int32_t *__restrict__ start, int32_t *cursor, float4 *sorted) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const int c = cell[i];
+    const int p = start[c] + atomicAdd(cursor + c, 1);
+    sorted[p] = make_float4(pts[3*i], pts[3*i+1], pts[3*i+2], __int_as_float((int)i));
+}
+
+__device__ __forceinline__ bool key_lt(double d, int i, double e, int j) { return d < e || (d == e && i < j); }
+
+// One warp per query (queries taken in cell order for locality).  Lane l keeps the l-th best
+// (d2, index) so far; candidates are read 32 at a time and inserted by warp shuffles.
+#define KNN_WARPS 8
+__global__ void __launch_bounds__(KNN_WARPS * 32) k_knn(const float4 *__restrict__ sorted, int64_t m, Grid g,
+                                                        const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * KNN_WARPS + (threadIdx.x >> 5);
+    if (w >= m) return;
+    const float4 q = sorted[w];
+    const int qi = __float_as_int(q.w);
+    const double qx = q.x, qy = q.y, qz = q.z;
+    int cx, cy; cell_of(g, q.x, q.y, cx, cy);
+    double bd = DBL_MAX; int bi = 0x7fffffff;            // this lane's slot
+    const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
+    for (int r = 0; ; r++) {
+        for (int yy = cy - r; yy <= cy + r; yy++) {
+            if (yy < 0 || yy >= g.ny) continue;
+            const bool full_row = (yy == cy - r) || (yy == cy + r);
+            const int nseg = full_row ? 1 : 2;
+            for (int sg = 0; sg < nseg; sg++) {
+                int x0, x1;
+                if (full_row) { x0 = cx - r; x1 = cx + r; } else { x0 = x1 = (sg == 0 ? cx - r : cx + r); }
+                x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
+                if (x0 > x1) continue;
+                const int pb = __ldg(start + yy * g.nx + x0), pe = __ldg(start + yy * g.nx + x1 + 1);
+                for (int p0 = pb; p0 < pe; p0 += 32) {
+                    const int p = p0 + lane;
+                    double cd = DBL_MAX; int cidx = 0x7fffffff;
+                    if (p < pe) {
+                        const float4 c = __ldg(sorted + p);
+                        const double dx = qx - (double)c.x, dy = qy - (double)c.y, dz = qz - (double)c.z;
+                        cd = 0.0; cd += dx * dx; cd += dy * dy; cd += dz * dz;
+                        cidx = __float_as_int(c.w);
+                    }
+                    double td = __shfl_sync(0xffffffffu, bd, k1 - 1); int ti = __shfl_sync(0xffffffffu, bi, k1 - 1);
+                    unsigned mask = __ballot_sync(0xffffffffu, key_lt(cd, cidx, td, ti));
+                    while (mask) {
+                        const int srcl = __ffs(mask) - 1;
+                        const double nd = __shfl_sync(0xffffffffu, cd, srcl); const int ni = __shfl_sync(0xffffffffu, cidx, srcl);
+                        const double pd = __shfl_up_sync(0xffffffffu, bd, 1); const int pi = __shfl_up_sync(0xffffffffu, bi, 1);
+                        const bool lt_me = key_lt(nd, ni, bd, bi);
+                        const bool lt_prev = lane > 0 && key_lt(nd, ni, pd, pi);
+                        if (lt_me) { if (lt_prev) { bd = pd; bi = pi; } else { bd = nd; bi = ni; } }
+                        td = __shfl_sync(0xffffffffu, bd, k1 - 1); ti = __shfl_sync(0xffffffffu, bi, k1 - 1);
+                        mask &= ~(1u << srcl);
+                        mask &= __ballot_sync(0xffffffffu, key_lt(cd, cidx, td, ti));
+                    }
+                }
+            }
+        }
+        if (cx - r <= 0 && cy - r <= 0 && cx + r >= g.nx - 1 && cy + r >= g.ny - 1) break;
+        // distance to the unexplored region; a side on which the window already reaches the grid edge has none
+        const double b0 = cx - r > 0 ? rx - (double)(cx - r) * g.h : DBL_MAX;
+        const double b1 = cx + r < g.nx - 1 ? (double)(cx + r + 1) * g.h - rx : DBL_MAX;
+        const double b2 = cy - r > 0 ? ry - (double)(cy - r) * g.h : DBL_MAX;
+        const double b3 = cy + r < g.ny - 1 ? (double)(cy + r + 1) * g.h - ry : DBL_MAX;
+        const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
+        const double td = __shfl_sync(0xffffffffu, bd, k1 - 1);
+        if (bm > 0.0 && td < DBL_MAX && sqrt(td) < bm * (1.0 - 1e-9)) break;
+    }
+    if (lane < k1) nbr[(int64_t)qi * k1 + lane] = (bi == 0x7fffffff) ? -1 : bi;
+}
+
+extern "C" size_t ms_knn_workspace_bytes(int64_t m, int k1) {
+    (void)k1;
+    const size_t ncell = (size_t)m + 2048;
+    return ms_align((size_t)m * 4) + 3 * ms_align(ncell * 4) + ms_align((size_t)m * 16) + ms_scan_ws_bytes((int64_t)ncell) + 4096;
+}
+
+extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
+                      void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(m > 0 && k1 >= 1 && k1 <= 32, "ms_knn: need m > 0 and 1 <= k+1 <= 32 (got m=%lld, k+1=%d)", (long long)m, k1);
+    MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_knn: too many points");
+    MS_REQUIRE(ws_bytes >= ms_knn_workspace_bytes(m, k1), "ms_knn: workspace too small");
+    const int64_t ncell_max = m + 2048;
+    MsArena A(ws, ws_bytes);
+    int32_t *cell = A.take<int32_t>(m);
+    int32_t *cnt = A.take<int32_t>(ncell_max), *start = A.take<int32_t>(ncell_max), *cursor = A.take<int32_t>(ncell_max);
+    float4 *sorted = A.take<float4>(m);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(ncell_max));
+    unsigned *bb = (unsigned*)A.take<unsigned>(64);
+    const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
+    MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, bb);
+    unsigned hb[4];
+    MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    float lo[2], hi[2];
+    for (int d = 0; d < 2; d++) {
+        unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
+        u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
+    }
+    double wx = (double)hi[0] - lo[0], wy = (double)hi[1] - lo[1];
+    MS_REQUIRE(wx == wx && wy == wy && wx < 1e30 && wy < 1e30, "ms_knn: non-finite coordinates");
+    if (!(wx > 0.0)) wx = 1e-6; if (!(wy > 0.0)) wy = 1e-6;
+    double ppc = 0.37 * (double)k1; if (ppc < 2.0) ppc = 2.0;
+    double h = sqrt(wx * wy * ppc / (double)m);
+    Grid g;
+    for (;;) {
+        const double nxd = floor(wx / h) + 1.0, nyd = floor(wy / h) + 1.0;
+        if (nxd * nyd <= (double)(ncell_max - 1)) { g.nx = (int)nxd; g.ny = (int)nyd; break; }
+        h *= 1.5;
+    }
+    g.lox = lo[0]; g.loy = lo[1]; g.h = h; g.inv_h = 1.0 / h;
+    const int64_t ncell = (int64_t)g.nx * g.ny;
+    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
+    k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, g, cell, cnt);
+    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
+    k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
+    k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ stage 3: PCA normals
+// One thread per point: centroid and covariance in neighbour order, cyclic Jacobi (CGAL's internal
+// 3x3 solver when CGAL_EIGEN3_ENABLED is off, setup.py:217), smallest-eigenvalue eigenvector.
+__global__ void __launch_bounds__(128) k_pca(const float *__restrict__ pts, int64_t m, const int32_t *__restrict__ nbr, int k1,
+                                             double *__restrict__ normals) {
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= m) return;
+    double c0 = 0.0, c1 = 0.0, c2 = 0.0; int cnt = 0;
+    for (int j = 0; j < k1; j++) {
+        const int i = __ldg(nbr + q * k1 + j); if (i < 0) continue;
+        c0 += ms_ld_f(pts + 3*(size_t)i); c1 += ms_ld_f(pts + 3*(size_t)i + 1); c2 += ms_ld_f(pts + 3*(size_t)i + 2); cnt++;
+    }
+    c0 /= cnt; c1 /= cnt; c2 /= cnt;
+    double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0;
+    for (int j = 0; j < k1; j++) {
+        const int i = __ldg(nbr + q * k1 + j); if (i < 0) continue;
+        const double dx = ms_ld_f(pts + 3*(size_t)i) - c0, dy = ms_ld_f(pts + 3*(size_t)i + 1) - c1, dz = ms_ld_f(pts + 3*(size_t)i + 2) - c2;
+        a00 += dx*dx; a01 += dx*dy; a02 += dx*dz; a11 += dy*dy; a12 += dy*dz; a22 += dz*dz;
+    }
+    double a[3][3] = { { a00, a01, a02 }, { a01, a11, a12 }, { a02, a12, a22 } };
+    double v[3][3] = { { 1, 0, 0 }, { 0, 1, 0 }, { 0, 0, 1 } };
+    for (int sweep = 0; sweep < 64; sweep++) {
+        const double offn = a[0][1]*a[0][1] + a[0][2]*a[0][2] + a[1][2]*a[1][2];
+        if (offn == 0.0) break;
+#pragma unroll
+        for (int p = 0; p < 2; p++) {
+#pragma unroll
+            for (int qq = p + 1; qq < 3; qq++) {
+                if (a[p][qq] == 0.0) continue;
+                const double theta = (a[qq][qq] - a[p][p]) / (2.0 * a[p][qq]);
+                const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                const double cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
+                const double apq = a[p][qq];
+                a[p][p] -= t * apq; a[qq][qq] += t * apq; a[p][qq] = a[qq][p] = 0.0;
+                const int r = 3 - p - qq;
+                const double arp = a[r][p], arq = a[r][qq];
+                a[r][p] = a[p][r] = cs * arp - sn * arq;
+                a[r][qq] = a[qq][r] = sn * arp + cs * arq;
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const double vip = v[i][p], viq = v[i][qq];
+                    v[i][p] = cs * vip - sn * viq;
+                    v[i][qq] = sn * vip + cs * viq;
+                }
+            }
+        }
+    }
+    double n0, n1, n2;
+    if (a[0][0] == a[1][1] && a[1][1] == a[2][2]) { n0 = 0.0; n1 = 0.0; n2 = 1.0; }
+    else {
+        double e = a[0][0]; n0 = v[0][0]; n1 = v[1][0]; n2 = v[2][0];
+        if (a[1][1] < e) { e = a[1][1]; n0 = v[0][1]; n1 = v[1][1]; n2 = v[2][1]; }
+        if (a[2][2] < e) { e = a[2][2]; n0 = v[0][2]; n1 = v[1][2]; n2 = v[2][2]; }
+        const double l = sqrt(n0*n0 + n1*n1 + n2*n2);
+        n0 /= l; n1 /= l; n2 /= l;
+    }
+    normals[3*q] = n0; normals[3*q+1] = n1; normals[3*q+2] = n2;
+}
+
+extern "C" int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
+                              double *normals, void *stream) {
+    MS_REQUIRE(m > 0 && k1 >= 1, "ms_pca_normals: bad arguments");
+    k_pca<<<ms_blocks(m, 128), 128, 0, (cudaStream_t)stream>>>(points_all, m, nbr, k1, normals);
+    MS_LAUNCH_CHECK();
+    return 0;
+}

@@ -416,12 +416,12 @@ void orc_knn_grid(const float *pts, int64_t m, int k1, int32_t *nbr, double *nbr
                 }
             }
             /* distance from q to the boundary of the explored window */
-            double bx0 = qx - (double)(cx - r) * h, bx1 = (double)(cx + r + 1) * h - qx;
-            double by0 = qy - (double)(cy - r) * h, by1 = (double)(cy + r + 1) * h - qy;
+            double bx0 = cx - r > 0 ? qx - (double)(cx - r) * h : 1e300, bx1 = cx + r < nx - 1 ? (double)(cx + r + 1) * h - qx : 1e300;
+            double by0 = cy - r > 0 ? qy - (double)(cy - r) * h : 1e300, by1 = cy + r < ny - 1 ? (double)(cy + r + 1) * h - qy : 1e300;
             double bmin = bx0; if (bx1 < bmin) bmin = bx1; if (by0 < bmin) bmin = by0; if (by1 < bmin) bmin = by1;
             const int covers_all = (cx - r <= 0 && cy - r <= 0 && cx + r >= nx - 1 && cy + r >= ny - 1);
             if (covers_all) break;
-            if (cnt == k1 && bmin > 0.0 && bd[k1-1] < bmin * bmin * (1.0 - 1e-9)) break;
+            if (cnt == k1 && bmin > 0.0 && sqrt(bd[k1-1]) < bmin * (1.0 - 1e-9)) break;
         }
         for (int j = 0; j < k1; j++) {
             nbr[q*k1 + j] = j < cnt ? bi[j] : -1;
@@ -494,16 +494,15 @@ void orc_pca_normals(const float *pts, int64_t m, const int32_t *nbr, int k1, do
 /* float(max(0, 1-|na.nb|)).  Minimum spanning tree of the source's component, */
 /* then parent->child propagation: child flipped iff dot(parent, child) < 0.   */
 /* The MST is unique when weights are distinct; for exact float ties boost's   */
-/* Prim order is not pinned -- here ties break by the total order (w, a, b)    */
+/* Prim order is not pinned -- here ties break by the total order (w, a, slot of b in NN(a))    */
 /* (Kruskal), which the CUDA Boruvka path uses too.  normals updated in place; */
 /* oriented[i] = 1 for points reached from the source.  Returns #unoriented.   */
 /* ------------------------------------------------------------------------- */
-typedef struct { float w; int32_t a, b; } orc_edge;
+typedef struct { float w; int32_t a, b; int64_t eid; } orc_edge;
 static int orc_edge_cmp(const void *x, const void *y) {
     const orc_edge *p = (const orc_edge*)x, *q = (const orc_edge*)y;
     if (p->w != q->w) return p->w < q->w ? -1 : 1;
-    if (p->a != q->a) return p->a < q->a ? -1 : 1;
-    return p->b < q->b ? -1 : (p->b > q->b);
+    return p->eid < q->eid ? -1 : (p->eid > q->eid);   /* eid = a*k1 + slot of b in a's list */
 }
 static int32_t orc_find(int32_t *par, int32_t x) {
     while (par[x] != x) { par[x] = par[par[x]]; x = par[x]; }
@@ -520,7 +519,7 @@ int64_t orc_mst_orient(const float *pts, int64_t m, const int32_t *nbr, int k1,
         const double *na = normals + 3*a, *nb = normals + 3*(int64_t)b;
         double dot = na[0]*nb[0] + na[1]*nb[1] + na[2]*nb[2];
         double w = 1.0 - fabs(dot); if (w < 0.0) w = 0.0;
-        E[ne].w = (float)w; E[ne].a = (int32_t)a; E[ne].b = b; ne++;
+        E[ne].w = (float)w; E[ne].a = (int32_t)a; E[ne].b = b; E[ne].eid = a * k1 + j; ne++;
     }
     qsort(E, (size_t)ne, sizeof(orc_edge), orc_edge_cmp);
     int32_t *par = (int32_t*)malloc(sizeof(int32_t) * (size_t)m);
