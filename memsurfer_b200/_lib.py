@@ -1,0 +1,90 @@
+"""ctypes binding of libmemsurfer_b200.so (the C ABI declared in include/memsurfer_b200.h).
+
+This is the only door between the Python host code and the sm_100a kernels.  There is no CPU
+fallback: if the shared library is missing or a call fails, an exception is raised.
+PyTorch is used purely as the device-buffer / stream provider.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmemsurfer_b200.so")
+_lib = None
+
+
+class MemSurferCudaError(RuntimeError):
+    pass
+
+
+_vp, _i64, _i32, _f32, _f64, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_double, C.c_size_t
+
+_SIGNATURES = {
+    "ms_version": (C.c_int, []),
+    "ms_last_error": (C.c_char_p, []),
+    "ms_pointset_capacity": (_i64, [_i64, _i32]),
+    "ms_ghosts_workspace_bytes": (_sz, [_i64]),
+    "ms_ghosts": (C.c_int, [_vp, _i64, _i32, C.POINTER(_f32), _f32, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_knn_workspace_bytes": (_sz, [_i64, _i32]),
+    "ms_knn": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _sz, _vp]),
+    "ms_pca_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
+    "ms_orient_workspace_bytes": (_sz, [_i64, _i32]),
+    "ms_orient_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_finish_workspace_bytes": (_sz, [_i64]),
+    "ms_finish_pnormals": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "ms_mesh_topology_workspace_bytes": (_sz, [_i64, _i64]),
+    "ms_mesh_topology": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _f64, _f64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ms_mesh_properties": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ms_kde_workspace_bytes": (_sz, [_i64, _i64]),
+    "ms_kde": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _i32, C.POINTER(_f32), _f32, _i32, _f64, _vp, _vp, _vp, _sz, _vp]),
+    "ms_dfma_probe": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp]),
+}
+EXPORTS = tuple(_SIGNATURES.keys())
+
+
+def lib():
+    """Load the shared library (once).  Raises if it was not built -- there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MemSurferCudaError(
+                f"{LIB_PATH} not found: build it with `make -C memsurfer_b200/csrc` "
+                "(or __graft_entry__.build()); memsurfer_b200 has no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().ms_last_error().decode("utf-8", "replace")
+        raise MemSurferCudaError(f"{what} failed (status {rc}): {msg}")
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise MemSurferCudaError("memsurfer_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(device=None):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def workspace(nbytes, device):
+    return torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=device)
+
+
+def box6(a):
+    arr = (C.c_float * 6)()
+    for i in range(6):
+        arr[i] = float(a[i])
+    return arr

@@ -1,0 +1,226 @@
+"""memsurfer_b200.Membrane -- drop-in for memsurfer.Membrane on the per-frame hot path.
+
+Mirrors memsurfer/membrane.py:27-345: same constructor kwargs, attributes, method names, return
+dtypes and memoisation.  compute_pnormals / compute_properties / compute_density(-ies) run on the
+B200 through the C ABI; the surface PRODUCER (Poisson reconstruction + CGAL parameterisation /
+projection / Delaunay, membrane.py:160-234) stays a host step: here `compute_membrane_surface`
+is a documented stand-in (planar projection + scipy Delaunay) because pypoisson/CGAL are not
+available in this image; real producers can inject their arrays with `set_membrane_surface`.
+"""
+import logging
+
+import numpy as np
+import torch
+
+from . import _lib
+from .trimesh import TriMesh
+
+LOGGER = logging.getLogger(__name__)
+
+
+def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1, keep=None):
+    """Device pipeline of Membrane.compute_pnormals (membrane.py:124-157).
+
+    points_dev: (n,3) float32 CUDA tensor.  Returns (pnormals f32 (n,3), pnormals f64 (n,3), info)
+    with info = dict(m=#points incl. ghosts, n_unoriented=...).  If `keep` is a dict the
+    intermediate device buffers (points_all, nbr, normals_all) are stored in it for tests.
+    """
+    _lib.require_cuda()
+    L = _lib.lib()
+    dev = points_dev.device
+    st = _lib.stream_ptr(dev)
+    n = int(points_dev.shape[0])
+    k1 = int(knbrs) + 1
+    cap = int(L.ms_pointset_capacity(n, int(bool(periodic))))
+    import ctypes as C
+    pts_all = torch.empty((cap, 3), dtype=torch.float32, device=dev)
+    gsrc = torch.empty(cap, dtype=torch.int32, device=dev)
+    m_out = C.c_int64(0)
+    ws = _lib.workspace(L.ms_ghosts_workspace_bytes(n), dev)
+    box = _lib.box6(np.asarray(bbox, np.float32).reshape(-1)) if periodic else None
+    _lib.check(L.ms_ghosts(points_dev.data_ptr(), n, int(bool(periodic)), box, float(blayer) if periodic else 0.0,
+                           pts_all.data_ptr(), gsrc.data_ptr(), C.byref(m_out), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
+    m = int(m_out.value)
+    nbr = torch.empty((m, k1), dtype=torch.int32, device=dev)
+    ws = _lib.workspace(max(L.ms_knn_workspace_bytes(m, k1), L.ms_orient_workspace_bytes(m, k1)), dev)
+    _lib.check(L.ms_knn(pts_all.data_ptr(), m, k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    nrm = torch.empty((m, 3), dtype=torch.float64, device=dev)
+    _lib.check(L.ms_pca_normals(pts_all.data_ptr(), m, nbr.data_ptr(), k1, nrm.data_ptr(), st), 'ms_pca_normals')
+    if keep is not None:
+        keep['normals_pca'] = nrm.clone()
+    bad = C.c_int64(0)
+    _lib.check(L.ms_orient_normals(pts_all.data_ptr(), m, nbr.data_ptr(), k1, nrm.data_ptr(), C.byref(bad),
+                                   ws.data_ptr(), ws.numel(), st), 'ms_orient_normals')
+    o32 = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    o64 = torch.empty((n, 3), dtype=torch.float64, device=dev)
+    _lib.check(L.ms_finish_pnormals(nrm.data_ptr(), n, int(ndir_hint), o32.data_ptr(), o64.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), st), 'ms_finish_pnormals')
+    if keep is not None:
+        keep.update(points_all=pts_all[:m], ghost_src=gsrc[:m], nbr=nbr, normals_all=nrm)
+    return o32, o64, dict(m=m, n_unoriented=int(bad.value))
+
+
+class Membrane(object):
+    """Create and analyse membrane surfaces (GPU hot path, host surface producer)."""
+
+    def __init__(self, points, **kwargs):
+        points = np.asarray(points)
+        if points.ndim != 2 or points.shape[1] != 3:
+            raise ValueError(f'Membrane needs 3D points: got {points.shape}')
+        self.points = points
+        self.npoints = self.points.shape[0]
+
+        self.periodic = kwargs.get('periodic', False)
+        if self.periodic:
+            self.blayer = kwargs.get('boundary_layer', 0.2)
+            if 'bbox' not in kwargs:
+                raise ValueError('Periodic membrane needs 3D bounding box: ndarray (2 ,3)')
+        if 'bbox' in kwargs:
+            self.bbox = np.asarray(kwargs['bbox'])
+            if self.bbox.shape[0] not in [2, 3]:
+                raise ValueError('Membrane needs 3D bounding box: ndarray (2 ,3)')
+        else:
+            # the reference fails with AttributeError at membrane.py:80 when bbox is missing;
+            # a non-periodic membrane simply does not need one here
+            self.bbox = np.stack([points.min(axis=0), points.max(axis=0)])
+
+        if 'labels' in kwargs and kwargs['labels'] is not None:
+            self.labels = np.asarray(kwargs['labels'])
+            if self.labels.shape[0] != self.npoints or len(self.labels.shape) > 1:
+                raise ValueError('Membrane expects one label per point')
+        else:
+            self.labels = None
+
+        self.device = torch.device(kwargs.get('device', 'cuda:0'))
+        self.points = self.points.astype(np.float32)
+        self.bbox = self.bbox.astype(np.float32)
+        # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
+        # later fit_points_to_box_xy(): normals are computed on these coordinates
+        self._pset_points = self.points.copy()
+
+        self.pnormals = None
+        self.pnormals_f64 = None
+        self.spoints = None
+        self.ppoints = None
+        self.surf_poisson = None
+        self.memb_planar = None
+        self.memb_smooth = None
+        self.memb_exact = None
+        self.attributes = {}
+        self.properties = {}
+        self.info = {}
+
+    # ---------------------------------------------------------------------- host helpers
+    def fit_points_to_box_xy(self):
+        """Wrap x,y into the box (membrane.py:100-121); returns the number of adjusted coordinates."""
+        nadjusted = 0
+        boxw = self.bbox[1, :] - self.bbox[0, :]
+        for d in range(2):
+            lo = self.points[:, d] < self.bbox[0, d]
+            self.points[lo, d] += boxw[d]
+            hi = self.points[:, d] > self.bbox[1, d]
+            self.points[hi, d] -= boxw[d]
+            nadjusted += int(lo.sum()) + int(hi.sum())
+        return nadjusted
+
+    # ---------------------------------------------------------------------- point normals (GPU)
+    def compute_pnormals(self, knbrs=18, ndir_hint=+1):
+        """(npoints,3) float32 normals by (k+1)-NN PCA + MST orientation (membrane.py:124-157)."""
+        if self.pnormals is not None:
+            return self.pnormals
+        _lib.require_cuda()
+        pts = torch.from_numpy(np.ascontiguousarray(self._pset_points)).to(self.device)
+        o32, o64, info = point_normals_device(pts, self.bbox, self.periodic,
+                                              getattr(self, 'blayer', 0.2), knbrs, ndir_hint)
+        self.info['pnormals'] = info
+        if info['n_unoriented'] > 0:
+            # the reference silently returns a permuted array here (PointSet.cpp:176-193)
+            LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
+                           "Some normals may be incorrectly oriented!")
+        self.pnormals = o32.cpu().numpy()
+        self.pnormals_f64 = o64.cpu().numpy()
+        if self.pnormals.shape != (self.npoints, 3):
+            raise ValueError(f'PointSet computed incorrect normals (got {self.pnormals.size} values')
+        return self.pnormals
+
+    # ---------------------------------------------------------------------- surface producer (host)
+    def compute_approx_surface(self, exactness_level=10):
+        """Reference: screened Poisson reconstruction via pypoisson (membrane.py:160-183), a host
+        producer that is unavailable in this image.  Kept as an explicit no-op stage: the point
+        normals it would consume are computed, the smooth surface falls back to the points."""
+        self.compute_pnormals()
+        self.surf_poisson = None
+
+    def set_membrane_surface(self, spoints, ppoints, planar_bbox):
+        """Inject a producer's output: points projected on the smooth surface and on the plane."""
+        self.spoints = np.asarray(spoints, np.float32)
+        self.ppoints = np.asarray(ppoints, np.float32)
+        self._planar_bbox = (np.asarray(planar_bbox[0], np.float32), np.asarray(planar_bbox[1], np.float32))
+        self._build_meshes()
+
+    def compute_membrane_surface(self):
+        """Stand-in for membrane.py:186-234 without Poisson/CGAL: spoints = points, ppoints = their
+        (x,y); planar bbox = the periodic box.  Everything after that follows the reference."""
+        self.spoints = self.points.copy()
+        self.ppoints = self.points[:, :2].copy()
+        self._planar_bbox = (self.bbox[0, :2].copy(), self.bbox[1, :2].copy())
+        self._build_meshes()
+
+    def _build_meshes(self):
+        dev = self.device
+        self.memb_planar = TriMesh(self.ppoints, periodic=self.periodic, label='memb_planar', device=dev)
+        self.memb_smooth = TriMesh(self.spoints, periodic=self.periodic, label='memb_smooth', device=dev)
+        self.memb_exact = TriMesh(self.points, periodic=self.periodic, label='memb_exact', device=dev)
+        if self.periodic:
+            self.memb_planar.set_bbox(*self._planar_bbox)
+            self.memb_smooth.set_bbox(self.spoints.min(axis=0), self.spoints.max(axis=0))
+            self.memb_exact.set_bbox(self.points.min(axis=0), self.points.max(axis=0))
+        self.memb_planar.compute_delaunay()
+        self.memb_smooth.copy_triangulation(self.memb_planar)
+        self.memb_exact.copy_triangulation(self.memb_planar)
+        if self.periodic:
+            self.memb_planar.set_bbox(self.ppoints.min(axis=0), self.ppoints.max(axis=0))
+
+    # ---------------------------------------------------------------------- properties / densities (GPU)
+    def compute_properties(self, mtype='smooth'):
+        assert mtype == 'smooth' or mtype == 'exact'
+        mesh = self.memb_exact if mtype == 'exact' else self.memb_smooth
+        mesh.compute_normals()
+        mesh.compute_pointareas()
+        mesh.compute_curvatures()
+
+    def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=0.0):
+        if type < 1 or type > 3:
+            raise ValueError(f'Invalid density type, {type}. Should be 1 (geodesic), 2 (2D) or 3 (3D)')
+        if len(labels) == 0:
+            self.attributes[name] = self.memb_smooth.compute_density(type, sigma, name, get_nlipdis,
+                                                                     np.empty([0]), cutoff_sigmas)
+            return
+        if self.labels is None:
+            raise ValueError('Cannot compute density of selected labels, because point labels are not available')
+        lidxs = np.where(np.isin(self.labels, labels))[0]
+        self.attributes[name] = self.memb_smooth.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas)
+
+    @staticmethod
+    def compute_thickness(a, b, mtype='smooth'):
+        raise NotImplementedError('leaflet thickness (mesh-to-mesh distance, TriMesh_cgal.cpp:390-425) is outside '
+                                  'the GPU hot path (SURVEY.md section 8(f), rank 1)')
+
+    @staticmethod
+    def compute_densities(membranes, types, sigmas, get_nlipdis, l):
+        labels = [] if l == 'all' else [l]
+        for t in types:
+            for s in sigmas:
+                name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)
+                for m in membranes:
+                    m.compute_density(t, s, name, get_nlipdis, labels)
+
+    @staticmethod
+    def compute(positions, labels, bbox, periodic):
+        knbrs = 18
+        m = Membrane(positions, labels=labels, periodic=periodic, bbox=bbox)
+        m.fit_points_to_box_xy()
+        m.compute_pnormals(knbrs)
+        m.compute_approx_surface()
+        m.compute_membrane_surface()
+        return m

@@ -1,0 +1,299 @@
+"""memsurfer_b200.TriMesh -- drop-in for memsurfer.trimesh.TriMesh on the hot path.
+
+Same constructor, attribute names, method names, return dtypes and memoisation as the reference
+class (memsurfer/trimesh.py:27-361); the arithmetic runs in hand-written sm_100a kernels through
+the C ABI (include/memsurfer_b200.h).  What stays on the host, as in the reference design, is the
+mesh PRODUCER: `compute_delaunay` here is a scipy stand-in for the CGAL call
+(memsurfer/src/TriMesh_cgal.cpp:160-281) and `copy_triangulation` re-trims with this mesh's own
+bbox exactly like TriMesh.hpp:301-304 + TriMesh.cpp:493-575.
+
+Extras that the reference does not have: `attributes_f64` (fp64 twins of the float32 results),
+`to_device()` (pre-stage inputs in HBM) and `*_device` accessors returning torch tensors.
+"""
+import logging
+
+import numpy as np
+import torch
+
+from . import _lib, synth
+
+LOGGER = logging.getLogger(__name__)
+
+
+class TriMesh(object):
+    """Triangular mesh (2D or 3D vertices) with GPU-computed per-vertex properties."""
+
+    KNOWN_ATTRIBUTES = ['pnormal', 'parea', 'mean_curv', 'gaus_curv', 'shell']
+
+    # ---------------------------------------------------------------------- constructor
+    def __init__(self, vertices, **kwargs):
+        vertices = np.asarray(vertices)
+        if vertices.ndim != 2 or vertices.shape[1] not in [2, 3]:
+            raise ValueError(f'TriMesh needs 2D or 3D vertices: got {vertices.shape}')
+        self.vertices = vertices.astype(np.float32)
+
+        if 'faces' in kwargs and kwargs['faces'] is not None:
+            faces = np.asarray(kwargs['faces'])
+            if faces.ndim != 2 or faces.shape[1] != 3:
+                raise ValueError(f'TriMesh needs triangles: got {faces.shape}')
+            self.faces = faces.astype(np.uint32)
+        else:
+            self.faces = None
+
+        self.periodic = kwargs.get('periodic', False)
+        self.label = kwargs.get('label', 'TriMeshPeriodic' if self.periodic else 'TriMesh')
+        self.device = torch.device(kwargs.get('device', 'cuda:0'))
+
+        self.bbox = None
+        self.bboxl = None
+        self._periodic_faces = None
+        self._trimmed_faces = None
+        self._duplicated_vidxs = None
+        self._duplicated_verts = None
+        self._parameterized_verts = None
+        self._delaunay = None            # (dfaces, doffs) of the periodic Delaunay (host producer)
+
+        self.attributes = {}
+        self.attributes_f64 = {}
+        self._fields = {}                # KDE fields cached by name (TriMesh_kde.cpp:455-460)
+        self._dev = {}                   # device-resident buffers
+
+    def tag(self):
+        return f'[{self.label}, periodic={self.periodic}]'
+
+    def __str__(self):
+        nf = self.faces.shape[0] if self.faces is not None else 0
+        return f'{self.tag()}: {self.vertices.shape[0]} verts, {nf} faces. ' \
+               f'bbox = {self.vertices.min(axis=0)}, {self.vertices.max(axis=0)}'
+
+    __repr__ = __str__
+
+    # ---------------------------------------------------------------------- bbox / triangulation (host producer side)
+    def set_bbox(self, bb0, bb1):
+        bb0, bb1 = np.asarray(bb0), np.asarray(bb1)
+        if bb0.shape[0] == 2 and bb1.shape[0] == 2:
+            self.bboxl = np.array([bb0[0], bb0[1], bb1[0], bb1[1]])
+            self.bbox = np.array([[bb0[0], bb0[1], 0.], [bb1[0], bb1[1], 0.]])
+        elif bb0.shape[0] == 3 and bb1.shape[0] == 3:
+            self.bboxl = np.array([bb0[0], bb0[1], bb0[2], bb1[0], bb1[1], bb1[2]])
+            self.bbox = np.array([[bb0[0], bb0[1], bb0[2]], [bb1[0], bb1[1], bb1[2]]])
+        else:
+            raise ValueError(f'TriMesh got incorrect bbox: {bb0}, {bb1}')
+        self.bbox = self.bbox.astype(np.float32)
+        self.bboxl = self.bboxl.astype(np.float32)     # memsurfer.i takes float32 (INPLACE_ARRAY1)
+        self._invalidate()
+
+    def _invalidate(self):
+        self._dev.clear()
+
+    def set_periodic_triangulation(self, faces, periodic_faces, trimmed_faces, duplicated_vidxs, duplicated_verts):
+        """Inject the arrays `_fetch_faces` (trimesh.py:421-436) would fetch from the C++ object."""
+        self.faces = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
+        self._periodic_faces = np.ascontiguousarray(periodic_faces, dtype=np.uint32).reshape(-1, 3)
+        self._trimmed_faces = np.ascontiguousarray(trimmed_faces, dtype=np.uint32).reshape(-1, 3)
+        self._duplicated_vidxs = np.ascontiguousarray(duplicated_vidxs, dtype=np.uint32)
+        self._duplicated_verts = np.ascontiguousarray(duplicated_verts, dtype=np.float32) \
+            .reshape(-1, self.vertices.shape[1])
+        self._invalidate()
+
+    def _retrim(self):
+        dfaces, doffs = self._delaunay
+        if self.bbox is None:
+            raise ValueError(f'{self.tag()} periodic mesh needs a bbox (set_bbox) before triangulation')
+        t = synth.trim_periodic(self.vertices, dfaces, doffs,
+                                self.bbox[0, :self.vertices.shape[1]], self.bbox[1, :self.vertices.shape[1]])
+        self.set_periodic_triangulation(t['faces'], t['periodic_faces'], t['trimmed_faces'],
+                                        t['duplicated_vidxs'], t['duplicated_verts'])
+
+    def compute_delaunay(self):
+        """HOST stand-in for TriMesh::delaunay / periodicDelaunay (CGAL is the reference producer)."""
+        if self.faces is not None:
+            return
+        if not self.periodic:
+            self.faces = synth.planar_delaunay(self.vertices[:, :2])
+            self._invalidate()
+            return
+        if self.bbox is None:
+            raise ValueError(f'{self.tag()} periodic Delaunay needs a bbox')
+        self._delaunay = synth.periodic_delaunay(self.vertices[:, :2], self.bbox[0], self.bbox[1])
+        self._retrim()
+
+    def copy_triangulation(self, mesh):
+        if self.periodic != mesh.periodic:
+            raise ValueError(f'Cannot copy a (periodic={self.periodic}) mesh into ({mesh.periodic})')
+        if not self.periodic:
+            self.faces = mesh.faces.copy()
+            self._invalidate()
+            return
+        self._delaunay = mesh._delaunay
+        self._retrim()
+
+    # ---------------------------------------------------------------------- device staging
+    def _concat_host(self):
+        include_periodic = self.periodic and (self._duplicated_vidxs is not None)
+        verts = self.vertices
+        if verts.shape[1] == 2:
+            verts = np.concatenate([verts, np.zeros((verts.shape[0], 1), np.float32)], axis=1)
+        faces = self.faces
+        if include_periodic:
+            dv = self._duplicated_verts
+            if dv.shape[1] == 2:
+                dv = np.concatenate([dv, np.zeros((dv.shape[0], 1), np.float32)], axis=1)
+            verts = np.concatenate((verts, dv), axis=0)
+            faces = np.concatenate((self.faces, self._trimmed_faces), axis=0)
+        return np.ascontiguousarray(verts, np.float32), np.ascontiguousarray(faces, np.uint32)
+
+    def to_device(self, pinned=None):
+        """Stage verts ++ dup verts and faces ++ trimmed faces in HBM (TriMesh.hpp:360-364 layout)."""
+        _lib.require_cuda()
+        if 'verts' in self._dev:
+            return self._dev
+        if self.faces is None:
+            raise ValueError(f'{self.tag()} has no faces (call compute_delaunay or pass faces=)')
+        verts, faces = self._concat_host()
+        d = self._dev
+        d['verts'] = torch.from_numpy(verts).to(self.device, non_blocking=True)
+        d['faces'] = torch.from_numpy(faces.view(np.int32)).to(self.device, non_blocking=True)
+        d['nv'] = self.vertices.shape[0]
+        return d
+
+    def _half_box(self):
+        include_periodic = self.periodic and (self._duplicated_vidxs is not None)
+        if not include_periodic:
+            return -1.0, -1.0
+        # trimesh.py:484-485 : float32 arithmetic on the float32 bbox
+        xw = np.float32(0.5) * (self.bbox[1, 0] - self.bbox[0, 0])
+        yw = np.float32(0.5) * (self.bbox[1, 1] - self.bbox[0, 1])
+        return float(xw), float(yw)
+
+    def _topology_device(self):
+        d = self.to_device()
+        if 'csr_off' in d:
+            return d
+        L = _lib.lib()
+        nv_all, nv, nf = d['verts'].shape[0], d['nv'], d['faces'].shape[0]
+        dev = self.device
+        d['csr_off'] = torch.empty(nv + 1, dtype=torch.int32, device=dev)
+        d['csr_adj'] = torch.empty(max(3 * nf, 1), dtype=torch.int32, device=dev)
+        d['keep'] = torch.empty(max(nf, 1), dtype=torch.uint8, device=dev)
+        ws = _lib.workspace(L.ms_mesh_topology_workspace_bytes(nv, nf), dev)
+        xw, yw = self._half_box()
+        _lib.check(L.ms_mesh_topology(d['verts'].data_ptr(), nv_all, nv, d['faces'].data_ptr(), nf, xw, yw,
+                                      d['csr_off'].data_ptr(), d['csr_adj'].data_ptr(), d['keep'].data_ptr(),
+                                      ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_mesh_topology')
+        return d
+
+    def properties_device(self):
+        """One fused launch: vertex normals, point areas, mean and Gaussian curvature (device tensors)."""
+        d = self._topology_device()
+        if 'vn64' in d:
+            return d
+        L = _lib.lib()
+        nv_all, nv, nf = d['verts'].shape[0], d['nv'], d['faces'].shape[0]
+        dev = self.device
+        d['vn64'] = torch.empty((nv, 3), dtype=torch.float64, device=dev)
+        d['vn32'] = torch.empty((nv, 3), dtype=torch.float32, device=dev)
+        d['pa64'] = torch.empty(nv, dtype=torch.float64, device=dev)
+        d['pa32'] = torch.empty(nv, dtype=torch.float32, device=dev)
+        d['H'] = torch.empty(nv, dtype=torch.float64, device=dev)
+        d['K'] = torch.empty(nv, dtype=torch.float64, device=dev)
+        _lib.check(L.ms_mesh_properties(d['verts'].data_ptr(), nv_all, nv, d['faces'].data_ptr(), nf,
+                                        d['csr_off'].data_ptr(), d['csr_adj'].data_ptr(), d['keep'].data_ptr(),
+                                        d['vn64'].data_ptr(), d['vn32'].data_ptr(), d['pa64'].data_ptr(),
+                                        d['pa32'].data_ptr(), d['H'].data_ptr(), d['K'].data_ptr(),
+                                        _lib.stream_ptr(dev)), 'ms_mesh_properties')
+        return d
+
+    # ---------------------------------------------------------------------- computation of attributes
+    def compute_normals(self):
+        """(V,3) float32 vertex normals (trimesh.py:244-261 -> TriMesh.cpp:99-133)."""
+        key = 'pnormal'
+        if key in self.attributes:
+            return self.attributes[key]
+        d = self.properties_device()
+        self.attributes[key] = d['vn32'].cpu().numpy()
+        self.attributes_f64[key] = d['vn64'].cpu().numpy()
+        return self.attributes[key]
+
+    def compute_pointareas(self):
+        """(V,) float32 mixed Voronoi vertex areas (trimesh.py:264-281 -> TriMesh.cpp:140-190)."""
+        key = 'parea'
+        if key in self.attributes:
+            return self.attributes[key]
+        d = self.properties_device()
+        self.attributes[key] = d['pa32'].cpu().numpy()
+        self.attributes_f64[key] = d['pa64'].cpu().numpy()
+        return self.attributes[key]
+
+    def compute_curvatures(self):
+        """((V,) f64 mean, (V,) f64 Gaussian) as vtkCurvatures gives them (trimesh.py:284-316)."""
+        keys = ['mean_curv', 'gaus_curv']
+        if keys[0] in self.attributes and keys[1] in self.attributes:
+            return self.attributes[keys[0]], self.attributes[keys[1]]
+        d = self.properties_device()
+        self.attributes[keys[0]] = d['H'].cpu().numpy()
+        self.attributes[keys[1]] = d['K'].cpu().numpy()
+        self.attributes_f64[keys[0]] = self.attributes[keys[0]]
+        self.attributes_f64[keys[1]] = self.attributes[keys[1]]
+        return self.attributes[keys[0]], self.attributes[keys[1]]
+
+    def compute_distance_to_surface(self, other):
+        raise NotImplementedError('distance_to_other_mesh (TriMesh_cgal.cpp:390-425) is outside the GPU hot path '
+                                  '(SURVEY.md section 8(f), rank 1)')
+
+    # ---------------------------------------------------------------------- KDE
+    def density_device(self, type, sigma, get_nlipids, pidxs_dev=None, cutoff_sigmas=0.0):
+        """Run ms_kde on device-resident inputs; returns (f64 tensor, f32 tensor)."""
+        _lib.require_cuda()
+        L = _lib.lib()
+        dev = self.device
+        d = self._dev
+        if 'kverts' not in d:
+            v = self.vertices
+            if v.shape[1] == 2:
+                v = np.concatenate([v, np.zeros((v.shape[0], 1), np.float32)], axis=1)
+            d['kverts'] = torch.from_numpy(np.ascontiguousarray(v, np.float32)).to(dev)
+        nv = d['kverts'].shape[0]
+        nids = 0 if pidxs_dev is None else int(pidxs_dev.numel())
+        o64 = torch.empty(nv, dtype=torch.float64, device=dev)
+        o32 = torch.empty(nv, dtype=torch.float32, device=dev)
+        nbytes = L.ms_kde_workspace_bytes(nv, nids)
+        ws = d.get('kde_ws')
+        if ws is None or ws.numel() < nbytes:
+            ws = d['kde_ws'] = _lib.workspace(nbytes, dev)
+        box = None
+        if self.periodic:
+            if self.bboxl is None:
+                raise ValueError(f'{self.tag()} periodic density needs a bbox')
+            b = np.asarray(self.bboxl, np.float32)
+            if b.shape[0] == 4:
+                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
+            box = _lib.box6(b)
+        _lib.check(L.ms_kde(d['kverts'].data_ptr(), nv, _lib.ptr(pidxs_dev) if nids else None, nids,
+                            int(type), int(bool(self.periodic)), box, float(sigma), int(bool(get_nlipids)),
+                            float(cutoff_sigmas), o64.data_ptr(), o32.data_ptr(),
+                            ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_kde')
+        return o64, o32
+
+    def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0):
+        """(V,) float32 density (trimesh.py:324-361 -> TriMesh::kde TriMesh_kde.cpp:443-532).
+
+        type 2: 2-D Gaussian on (x,y); type 3: 3-D Gaussian.  type 1 (geodesic, Floyd-Warshall
+        O(V^3), TriMesh_kde.cpp:196-332) is not part of the GPU path.
+        """
+        if type < 1 or type > 3:
+            raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
+        if type == 1:
+            raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
+        if name in self._fields:                      # TriMesh_kde.cpp:455-460: name-keyed cache
+            return self._fields[name]
+        pidxs = np.asarray(pidxs)
+        pd = None
+        if pidxs.shape[0] > 0:
+            pd = torch.from_numpy(np.ascontiguousarray(pidxs, dtype=np.int32)).to(self.device)
+        o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
+        dens = o32.cpu().numpy()
+        self._fields[name] = dens
+        self.attributes_f64[name] = o64.cpu().numpy()
+        LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        return dens
