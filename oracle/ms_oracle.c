@@ -562,3 +562,24 @@ int64_t orc_mst_orient(const float *pts, int64_t m, const int32_t *nbr, int k1,
     free(E); free(par); free(deg); free(T); free(off); free(adj); free(queue);
     return m - qt;
 }
+
+/* raw pair sums for a SUBSET of targets (parity checks at sizes where all V^2 pairs are too slow on a CPU) */
+void orc_kde_raw_targets(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+                         const int32_t *targets, int64_t nt,
+                         int type, int periodic, const float *bbox, float sigma, double *density /* (nt,) */) {
+    float ef, sf; orc_kde_constants(sigma, type, &ef, &sf);
+    const double efactor = ef, sfactor = sf;
+    double boxw[2] = { 0.0, 0.0 };
+    if (periodic) { boxw[0] = (double)(float)(bbox[3] - bbox[0]); boxw[1] = (double)(float)(bbox[4] - bbox[1]); }
+    const int64_t ns = nids > 0 ? nids : nv;
+#pragma omp parallel for schedule(static)
+    for (int64_t t = 0; t < nt; t++) {
+        const int64_t j = targets[t];
+        double acc = 0.0;
+        for (int64_t i = 0; i < ns; i++) {
+            const int64_t s = nids > 0 ? ids[i] : i;
+            acc += sfactor * exp(orc_dist2(verts + 3*s, verts + 3*j, type, periodic, boxw) * efactor);
+        }
+        density[t] = acc;
+    }
+}

@@ -44,6 +44,7 @@ def lib():
         L.orc_face_keep.argtypes = [_f32p, _u32p, C.c_int64, C.c_double, C.c_double, _u8p]
         L.orc_kde.argtypes = [_f32p, C.c_int64, _i32p, C.c_int64, C.c_int, C.c_int, _f32p, C.c_float, C.c_int, _f64p]
         L.orc_kde_raw.argtypes = [_f32p, C.c_int64, _i32p, C.c_int64, C.c_int, C.c_int, _f32p, C.c_float, _f64p]
+        L.orc_kde_raw_targets.argtypes = [_f32p, C.c_int64, _i32p, C.c_int64, _i32p, C.c_int64, C.c_int, C.c_int, _f32p, C.c_float, _f64p]
         L.orc_knn_brute.argtypes = [_f32p, C.c_int64, C.c_int, _i32p, C.c_void_p]
         L.orc_knn_grid.argtypes = [_f32p, C.c_int64, C.c_int, _i32p, C.c_void_p]
         L.orc_pca_normals.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p]
@@ -124,6 +125,18 @@ def kde(verts, ids, type, sigma, get_counts, bbox=None, raw=False):
         lib().orc_kde_raw(v, v.shape[0], ids, ids.shape[0], type, int(periodic), box, sigma, out)
     else:
         lib().orc_kde(v, v.shape[0], ids, ids.shape[0], type, int(periodic), box, sigma, int(get_counts), out)
+    return out
+
+
+def kde_raw_targets(verts, ids, targets, type, sigma, bbox=None):
+    """Un-normalised pair sums sfactor*sum_i exp(...) for the listed target vertices only."""
+    v = _f32(verts)
+    ids = np.ascontiguousarray(ids, dtype=np.int32).reshape(-1)
+    tg = np.ascontiguousarray(targets, dtype=np.int32).reshape(-1)
+    periodic = bbox is not None
+    box = _f32(np.asarray(bbox).reshape(-1)) if periodic else np.zeros(6, np.float32)
+    out = np.empty((tg.shape[0],), np.float64)
+    lib().orc_kde_raw_targets(v, v.shape[0], ids, ids.shape[0], tg, tg.shape[0], type, int(periodic), box, sigma, out)
     return out
 
 

@@ -110,18 +110,22 @@ def test_kde_vs_oracle(oracle, leaflet, typ, periodic, get_counts):
                 assert abs(mesh.attributes_f64[name].sum() - (len(ids) or pts.shape[0])) < 1e-6
 
 
-def test_kde_large_sources_multi_tile(oracle):
+def test_kde_large_register_blocked_path(oracle):
+    """V >= 148*1024 targets takes the R=4 register-blocked kernel; oracle on a target subset."""
     from memsurfer_b200 import TriMesh, synth
-    pts, labels, bbox = synth.make_leaflet(90000, seed=2)      # >= 148*1024 targets -> R=4 path
+    pts, labels, bbox = synth.make_leaflet(160000, seed=2)
+    V = pts.shape[0]
     mesh = TriMesh(pts, periodic=True)
     bb = np.concatenate([pts.min(0), pts.max(0)]).astype(np.float32)
     mesh.set_bbox(bb[:3], bb[3:])
-    d = mesh.compute_density(2, 20.0, "x", True, np.empty([0]))
-    sub = np.arange(0, pts.shape[0], 97)
-    import ctypes  # oracle on a target subset: all sources, selected targets
-    want = oracle.kde(pts, np.zeros(0, np.int32), 2, 20.0, False, bb, raw=True)
-    want = want / pts.shape[0]; want = want * (pts.shape[0] / want.sum())
-    assert close(mesh.attributes_f64["x"][sub], want[sub])[0]
+    ids = np.where(labels == 2)[0]
+    mesh.compute_density(2, 20.0, "all", False, np.empty([0]))
+    mesh.compute_density(3, 30.0, "sub", False, ids)
+    tg = np.arange(0, V, 397)
+    want = oracle.kde_raw_targets(pts, np.zeros(0, np.int32), tg, 2, 20.0, bb) / V
+    ok, err = close(mesh.attributes_f64["all"][tg], want); assert ok, err
+    want = oracle.kde_raw_targets(pts, ids.astype(np.int32), tg, 3, 30.0, bb) / V
+    ok, err = close(mesh.attributes_f64["sub"][tg], want); assert ok, err
 
 
 def test_pnormals_stages(oracle, golden):
