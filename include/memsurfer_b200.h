@@ -116,6 +116,24 @@ int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
  * every SM and returns the number of FLOP issued in *flop (host); time it with events.         */
 int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream);
 
+/* ---------------------------------------------------------------- per-frame summaries
+ * No reference counterpart: the reference analyses one frame per process (examples/ex_3lipid.py:78)
+ * and writes whole fields to .vtp (membrane.py:319-344).  When trajectory frames are sharded over
+ * GPUs, ranks exchange only this record per field: out4 (device, 4 doubles) = {sum, sum|x|, min,
+ * max} of x (n) f64, reduced in a fixed order (bit-reproducible).                               */
+size_t ms_field_summary_workspace_bytes(void);
+int ms_field_summary(const double *x, int64_t n, double *out4, void *ws, size_t ws_bytes, void *stream);
+
+/* ---------------------------------------------------------------- diagnostics
+ * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).
+ * ms_launch_count: kernels launched by the library since the last reset (process-wide).
+ * ms_profile_enable(1): from now on this thread records a CUDA event before every kernel it
+ * launches; ms_profile_report writes {"kernel": {"launches": n, "ms": t}, ...} (device time
+ * between consecutive marks, summed per kernel name) into buf (host) and clears the marks.   */
+int64_t ms_launch_count(int reset);
+int     ms_profile_enable(int on);
+int     ms_profile_report(char *buf, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

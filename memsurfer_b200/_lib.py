@@ -39,6 +39,11 @@ _SIGNATURES = {
     "ms_kde_workspace_bytes": (_sz, [_i64, _i64]),
     "ms_kde": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _i32, C.POINTER(_f32), _f32, _i32, _f64, _vp, _vp, _vp, _sz, _vp]),
     "ms_dfma_probe": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp]),
+    "ms_field_summary_workspace_bytes": (_sz, []),
+    "ms_field_summary": (C.c_int, [_vp, _i64, _vp, _vp, _sz, _vp]),
+    "ms_launch_count": (_i64, [_i32]),
+    "ms_profile_enable": (C.c_int, [_i32]),
+    "ms_profile_report": (C.c_int, [C.c_char_p, _sz]),
 }
 EXPORTS = tuple(_SIGNATURES.keys())
 
@@ -83,8 +88,47 @@ def workspace(nbytes, device):
     return torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=device)
 
 
+def pinned_empty(shape, dtype):
+    """numpy array backed by page-locked host memory when a CUDA device is present (so that
+    host<->device copies are direct DMA), plain numpy otherwise."""
+    import numpy as np
+    if not torch.cuda.is_available():
+        return np.empty(shape, dtype=dtype)
+    tdt = torch.from_numpy(np.empty(0, dtype=dtype)).dtype
+    return torch.empty(tuple(int(x) for x in np.atleast_1d(shape)), dtype=tdt, pin_memory=True).numpy()
+
+
+def pinned_copy(a, dtype):
+    import numpy as np
+    a = np.asarray(a)
+    out = pinned_empty(a.shape, dtype)
+    np.copyto(out, a, casting='unsafe')
+    return out
+
+
+def h2d(arr, device):
+    """Asynchronous host->device copy on the current stream (true DMA when arr is page-locked)."""
+    return torch.from_numpy(arr).to(device, non_blocking=True)
+
+
+def d2h(t):
+    """Device->host copy into page-locked memory; returns a numpy array (synchronises the stream)."""
+    out = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    out.copy_(t, non_blocking=True)
+    torch.cuda.current_stream(t.device).synchronize()
+    return out.numpy()
+
+
 def box6(a):
     arr = (C.c_float * 6)()
     for i in range(6):
         arr[i] = float(a[i])
     return arr
+
+
+def profile_report():
+    """{"kernel": {"launches": n, "ms": device time}} since ms_profile_enable(1); clears the marks."""
+    import json
+    buf = C.create_string_buffer(1 << 16)
+    check(lib().ms_profile_report(buf, len(buf)), 'ms_profile_report')
+    return json.loads(buf.value.decode())

@@ -1,6 +1,9 @@
 // ms_common.cu -- error string, version, exclusive scan, DFMA probe.
 #include "ms_common.cuh"
 #include <stdarg.h>
+#include <string.h>
+#include <atomic>
+#include <vector>
 
 static thread_local char g_err[512] = "";
 
@@ -8,8 +11,64 @@ void ms_set_error(const char *fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
 }
 
-extern "C" int ms_version(void) { return 100; }
+extern "C" int ms_version(void) { return 101; }
 extern "C" const char *ms_last_error(void) { return g_err; }
+
+// ------------------------------------------------------------------ launch accounting / profiling
+// Diagnostic state only (never read by a compute path): a process-wide launch counter and a
+// per-thread list of (name, event) marks.
+static std::atomic<long long> g_launches(0);
+struct ProfMark { const char *name; cudaEvent_t ev; };
+static thread_local bool g_prof_on = false;
+static thread_local std::vector<ProfMark> *g_marks = nullptr;
+
+void ms_prof_mark(const char *name, cudaStream_t s) {
+    if (name) g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!g_prof_on) return;
+    if (!g_marks) g_marks = new std::vector<ProfMark>();
+    if (!name && (g_marks->empty() || g_marks->back().name == nullptr)) return;
+    ProfMark m; m.name = name;
+    if (cudaEventCreate(&m.ev) != cudaSuccess) return;
+    cudaEventRecord(m.ev, s);
+    g_marks->push_back(m);
+}
+
+static void prof_clear() {
+    if (!g_marks) return;
+    for (auto &m : *g_marks) cudaEventDestroy(m.ev);
+    g_marks->clear();
+}
+
+extern "C" int ms_profile_enable(int on) { prof_clear(); g_prof_on = on != 0; return 0; }
+extern "C" int64_t ms_launch_count(int reset) {
+    return reset ? g_launches.exchange(0) : g_launches.load();
+}
+extern "C" int ms_profile_report(char *buf, size_t cap) {
+    MS_REQUIRE(buf && cap > 2, "ms_profile_report: need a buffer");
+    struct Agg { const char *name; long long n; double ms; };
+    std::vector<Agg> agg;
+    if (g_marks && !g_marks->empty()) {
+        MS_CUDA(cudaEventSynchronize(g_marks->back().ev));
+        for (size_t i = 0; i + 1 < g_marks->size(); i++) {
+            const ProfMark &a = (*g_marks)[i], &b = (*g_marks)[i + 1];
+            if (!a.name) continue;
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, a.ev, b.ev) != cudaSuccess) { cudaGetLastError(); continue; }
+            size_t k = 0;
+            for (; k < agg.size(); k++) if (!strcmp(agg[k].name, a.name)) break;
+            if (k == agg.size()) agg.push_back(Agg{ a.name, 0, 0.0 });
+            agg[k].n++; agg[k].ms += ms;
+        }
+    }
+    size_t o = 0;
+    o += snprintf(buf + o, cap - o, "{");
+    for (size_t k = 0; k < agg.size() && o < cap; k++)
+        o += snprintf(buf + o, cap - o, "%s\"%s\": {\"launches\": %lld, \"ms\": %.6f}", k ? ", " : "", agg[k].name, agg[k].n, agg[k].ms);
+    if (o < cap) o += snprintf(buf + o, cap - o, "}");
+    MS_REQUIRE(o < cap, "ms_profile_report: buffer too small");
+    prof_clear();
+    return 0;
+}
 
 // ------------------------------------------------------------------ exclusive scan
 #define SCAN_T 512
@@ -77,9 +136,10 @@ int ms_exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n, void *ws, 
     int32_t *bsum = (int32_t*)ws;
     if (n <= 0) { MS_CUDA(cudaMemsetAsync(out, 0, sizeof(int32_t), s)); return 0; }
     const int64_t nb = (n + SCAN_B - 1) / SCAN_B;
-    k_scan_blocksum<<<(unsigned)nb, SCAN_T, 0, s>>>(in, n, bsum);
-    k_scan_top<<<1, SCAN_T, 0, s>>>(bsum, nb);
-    k_scan_final<<<(unsigned)nb, SCAN_T, 0, s>>>(in, out, n, bsum);
+    MS_K("scan_blocksum", s); k_scan_blocksum<<<(unsigned)nb, SCAN_T, 0, s>>>(in, n, bsum);
+    MS_K("scan_top", s); k_scan_top<<<1, SCAN_T, 0, s>>>(bsum, nb);
+    MS_K("scan_final", s); k_scan_final<<<(unsigned)nb, SCAN_T, 0, s>>>(in, out, n, bsum);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }
@@ -100,8 +160,57 @@ __global__ void __launch_bounds__(256) k_dfma_probe(double *out, int64_t iters) 
 #define PROBE_BLOCKS (MS_SM_COUNT * 8)
 extern "C" int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream) {
     MS_REQUIRE(out != NULL && iters > 0, "ms_dfma_probe: out must hold %d doubles", PROBE_BLOCKS * 256);
-    k_dfma_probe<<<PROBE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(out, iters);
+    MS_K("dfma_probe", (cudaStream_t)stream); k_dfma_probe<<<PROBE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(out, iters);
+    MS_K(NULL, (cudaStream_t)stream);
     MS_LAUNCH_CHECK();
     if (flop) *flop = 2.0 * 8.0 * (double)iters * 256.0 * PROBE_BLOCKS;
+    return 0;
+}
+
+
+// ------------------------------------------------------------------ per-frame field summary
+// (sum, sum|x|, min, max) of an fp64 field in a fixed reduction order (deterministic): the record
+// that ranks exchange when trajectory frames are sharded across GPUs.
+#define SUM_T 256
+#define SUM_BLOCKS (MS_SM_COUNT * 4)
+struct Sum4 { double s, a, mn, mx; };
+__device__ __forceinline__ Sum4 sum4_merge(const Sum4 &x, const Sum4 &y) {
+    Sum4 r; r.s = x.s + y.s; r.a = x.a + y.a; r.mn = fmin(x.mn, y.mn); r.mx = fmax(x.mx, y.mx); return r;
+}
+__device__ __forceinline__ Sum4 sum4_block(Sum4 v, Sum4 *sm) {
+    sm[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = SUM_T / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sm[threadIdx.x] = sum4_merge(sm[threadIdx.x], sm[threadIdx.x + o]);
+        __syncthreads();
+    }
+    return sm[0];
+}
+__global__ void __launch_bounds__(SUM_T) k_summary_partial(const double *__restrict__ x, int64_t n, Sum4 *part) {
+    __shared__ Sum4 sm[SUM_T];
+    Sum4 v; v.s = 0.0; v.a = 0.0; v.mn = INFINITY; v.mx = -INFINITY;
+    for (int64_t i = (int64_t)blockIdx.x * SUM_T + threadIdx.x; i < n; i += (int64_t)gridDim.x * SUM_T) {
+        const double d = x[i]; v.s += d; v.a += fabs(d); v.mn = fmin(v.mn, d); v.mx = fmax(v.mx, d);
+    }
+    v = sum4_block(v, sm);
+    if (threadIdx.x == 0) part[blockIdx.x] = v;
+}
+__global__ void __launch_bounds__(SUM_T) k_summary_final(const Sum4 *__restrict__ part, int nb, double *out4) {
+    __shared__ Sum4 sm[SUM_T];
+    Sum4 v; v.s = 0.0; v.a = 0.0; v.mn = INFINITY; v.mx = -INFINITY;
+    for (int i = threadIdx.x; i < nb; i += SUM_T) v = sum4_merge(v, part[i]);
+    v = sum4_block(v, sm);
+    if (threadIdx.x == 0) { out4[0] = v.s; out4[1] = v.a; out4[2] = v.mn; out4[3] = v.mx; }
+}
+extern "C" size_t ms_field_summary_workspace_bytes(void) { return ms_align(SUM_BLOCKS * sizeof(Sum4)); }
+extern "C" int ms_field_summary(const double *x, int64_t n, double *out4, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(x && out4 && n > 0, "ms_field_summary: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_field_summary_workspace_bytes(), "ms_field_summary: workspace too small");
+    int nb = ms_blocks(n, SUM_T); if (nb > SUM_BLOCKS) nb = SUM_BLOCKS;
+    MS_K("summary_partial", s); k_summary_partial<<<nb, SUM_T, 0, s>>>(x, n, (Sum4*)ws);
+    MS_K("summary_final", s); k_summary_final<<<1, SUM_T, 0, s>>>((const Sum4*)ws, nb, out4);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
     return 0;
 }

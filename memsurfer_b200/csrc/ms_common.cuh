@@ -10,6 +10,14 @@
 
 void ms_set_error(const char *fmt, ...);
 
+// Launch accounting / optional per-kernel event timing (ms_profile_* in the C ABI).  Call
+// ms_prof_mark("kernel name", stream) right before every kernel launch and
+// ms_prof_mark(NULL, stream) after the last launch of an entry point.  With profiling off this
+// only bumps the launch counter; with it on, a cudaEvent is recorded at every mark and the span
+// up to the next mark on the same thread is attributed to the name.
+void ms_prof_mark(const char *name, cudaStream_t s);
+#define MS_K(name, s) ms_prof_mark(name, s)
+
 #define MS_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
     ms_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); return 2; } } while (0)
 #define MS_LAUNCH_CHECK() MS_CUDA(cudaGetLastError())

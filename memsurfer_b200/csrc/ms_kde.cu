@@ -222,13 +222,14 @@ static int kde_run(const float *verts, int64_t nv, const int32_t *ids, const Kde
     typedef typename SrcT<DIM>::type S;
     S *tgt = (S*)tgt_, *src = (S*)src_;
     const int64_t nstage = nv > p.ns_pad ? nv : p.ns_pad;
-    k_kde_stage<DIM><<<ms_blocks(nstage, 256), 256, 0, s>>>(verts, nv, ids, p.ns, p.ns_pad, scale, tgt, src);
+    MS_K("kde_stage", s); k_kde_stage<DIM><<<ms_blocks(nstage, 256), 256, 0, s>>>(verts, nv, ids, p.ns, p.ns_pad, scale, tgt, src);
     const int tile = KDE_TILE_BYTES / (int)sizeof(S);
     const int ntiles = (int)(p.ns_pad / tile);
     const int tps = (ntiles + p.nsplit - 1) / p.nsplit;
     dim3 grid((unsigned)p.blocks_x, (unsigned)p.nsplit);
-    if (p.R == 4) k_kde_pairs<DIM, PER, 128, 4><<<grid, 128, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial);
-    else          k_kde_pairs<DIM, PER, 64, 1><<<grid, 64, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial);
+    if (p.R == 4) { MS_K("kde_pairs", s); k_kde_pairs<DIM, PER, 128, 4><<<grid, 128, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial); }
+    else          { MS_K("kde_pairs", s); k_kde_pairs<DIM, PER, 64, 1><<<grid, 64, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial); }
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }
@@ -262,10 +263,11 @@ extern "C" int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_
                                  : kde_run<3, false>(verts, nv, nids > 0 ? ids : NULL, p, scale, wx, wy, tgt, src, partial, s);
     if (rc) return rc;
     const int nb = ms_blocks(nv, RED_T);
-    k_kde_combine<<<nb, RED_T, 0, s>>>(partial, nv, p.nsplit, (double)sfactor * (1.0 / (double)nv), dens, bsum);
+    MS_K("kde_combine", s); k_kde_combine<<<nb, RED_T, 0, s>>>(partial, nv, p.nsplit, (double)sfactor * (1.0 / (double)nv), dens, bsum);
     double *total = bsum + nb;
-    if (get_counts) k_kde_total<<<1, RED_T, 0, s>>>(bsum, nb, total);
-    k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(dens, nv, get_counts ? total : NULL, (double)p.ns, density_f64, density_f32);
+    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(bsum, nb, total); }
+    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(dens, nv, get_counts ? total : NULL, (double)p.ns, density_f64, density_f32);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }

@@ -65,7 +65,8 @@ extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const flo
     cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(n > 0 && m_out, "ms_ghosts: bad arguments");
     if (!periodic) {
-        k_copy_points<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, points_all, ghost_src);
+        MS_K("copy_points", s); k_copy_points<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, points_all, ghost_src);
+        MS_K(NULL, s);
         MS_LAUNCH_CHECK();
         *m_out = n;
         return 0;
@@ -81,9 +82,10 @@ extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const flo
     MsArena A(ws, ws_bytes);
     int32_t *cnt = A.take<int32_t>(n + 1), *off = A.take<int32_t>(n + 1);
     void *scan_ws = A.take<char>(ms_scan_ws_bytes(n));
-    k_ghost_count<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, cnt);
+    MS_K("ghost_count", s); k_ghost_count<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, cnt);
     if (ms_exclusive_scan_i32(cnt, off, n, scan_ws, s)) return 2;
-    k_ghost_fill<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, off, points_all, ghost_src);
+    MS_K("ghost_fill", s); k_ghost_fill<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, off, points_all, ghost_src);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     int32_t total = 0;
     MS_CUDA(cudaMemcpyAsync(&total, off + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
@@ -222,7 +224,7 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     unsigned *bb = (unsigned*)A.take<unsigned>(64);
     const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
     MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
-    k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, bb);
+    MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, bb);
     unsigned hb[4];
     MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
     MS_CUDA(cudaStreamSynchronize(s));
@@ -246,10 +248,11 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     const int64_t ncell = (int64_t)g.nx * g.ny;
     MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
     MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
-    k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, g, cell, cnt);
+    MS_K("cell_count", s); k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, g, cell, cnt);
     if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
-    k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
-    k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);
+    MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
+    MS_K("knn", s); k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }
@@ -316,7 +319,8 @@ __global__ void __launch_bounds__(128) k_pca(const float *__restrict__ pts, int6
 extern "C" int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
                               double *normals, void *stream) {
     MS_REQUIRE(m > 0 && k1 >= 1, "ms_pca_normals: bad arguments");
-    k_pca<<<ms_blocks(m, 128), 128, 0, (cudaStream_t)stream>>>(points_all, m, nbr, k1, normals);
+    MS_K("pca", (cudaStream_t)stream); k_pca<<<ms_blocks(m, 128), 128, 0, (cudaStream_t)stream>>>(points_all, m, nbr, k1, normals);
+    MS_K(NULL, (cudaStream_t)stream);
     MS_LAUNCH_CHECK();
     return 0;
 }

@@ -77,10 +77,11 @@ extern "C" int ms_mesh_topology(const float *verts_all, int64_t nv_all, int64_t 
     void *scan_ws = A.take<char>(ms_scan_ws_bytes(nv));
     MS_CUDA(cudaMemsetAsync(deg, 0, sizeof(int32_t) * (nv + 1), s));
     MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (nv + 1), s));
-    if (nf > 0) k_face_degree<<<ms_blocks(nf, 256), 256, 0, s>>>(verts_all, faces_all, nf, nv, half_xw, half_yw, deg, keep);
+    if (nf > 0) { MS_K("face_degree", s); k_face_degree<<<ms_blocks(nf, 256), 256, 0, s>>>(verts_all, faces_all, nf, nv, half_xw, half_yw, deg, keep); }
     if (ms_exclusive_scan_i32(deg, csr_off, nv, scan_ws, s)) return 2;
-    if (nf > 0) k_face_fill<<<ms_blocks(nf, 256), 256, 0, s>>>(faces_all, nf, nv, csr_off, cursor, csr_adj);
-    if (nv > 0) k_sort_lists<<<ms_blocks(nv, 256), 256, 0, s>>>(nv, csr_off, csr_adj);
+    if (nf > 0) { MS_K("face_fill", s); k_face_fill<<<ms_blocks(nf, 256), 256, 0, s>>>(faces_all, nf, nv, csr_off, cursor, csr_adj); }
+    if (nv > 0) { MS_K("sort_lists", s); k_sort_lists<<<ms_blocks(nv, 256), 256, 0, s>>>(nv, csr_off, csr_adj); }
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }
@@ -238,9 +239,10 @@ extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_
     MS_REQUIRE(nv >= 0 && nv <= nv_all && nf >= 0, "ms_mesh_properties: bad sizes");
     MS_REQUIRE(csr_off && csr_adj && keep, "ms_mesh_properties: topology missing (call ms_mesh_topology first)");
     if (nv == 0) return 0;
-    k_mesh_properties<<<ms_blocks(nv, MESH_T), MESH_T, 0, (cudaStream_t)stream>>>(
+    MS_K("mesh_properties", (cudaStream_t)stream); k_mesh_properties<<<ms_blocks(nv, MESH_T), MESH_T, 0, (cudaStream_t)stream>>>(
         verts_all, faces_all, nv, csr_off, csr_adj, keep,
         vnormals_f64, vnormals_f32, pareas_f64, pareas_f32, mean_curv, gaus_curv);
+    MS_K(NULL, (cudaStream_t)stream);
     MS_LAUNCH_CHECK();
     return 0;
 }

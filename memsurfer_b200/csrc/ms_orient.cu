@@ -174,24 +174,27 @@ extern "C" int ms_orient_normals(const float *points_all, int64_t m, const int32
     int *counters = (int*)(srckey + 2);                               // [0] hooks this round, [1] unoriented
     MS_CUDA(cudaMemsetAsync(srckey, 0, 4 * sizeof(unsigned long long), s));
     const int nb = ms_blocks(m, 256);
-    k_edge_weights<<<ms_blocks(m * k1, 256), 256, 0, s>>>(nbr, m, k1, normals, wkey);
-    k_orient_init<<<nb, 256, 0, s>>>(m, link, best, hook);
-    k_find_source<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, srckey);
-    k_source_flip<<<1, 1, 0, s>>>(srckey, normals, flip0);
+    MS_K("edge_weights", s); k_edge_weights<<<ms_blocks(m * k1, 256), 256, 0, s>>>(nbr, m, k1, normals, wkey);
+    MS_K("orient_init", s); k_orient_init<<<nb, 256, 0, s>>>(m, link, best, hook);
+    MS_K("find_source", s); k_find_source<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, srckey);
+    MS_K("source_flip", s); k_source_flip<<<1, 1, 0, s>>>(srckey, normals, flip0);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     for (int round = 0; round < 40; round++) {
         MS_CUDA(cudaMemsetAsync(counters, 0, sizeof(int), s));
-        k_min_edge<<<nb, 256, 0, s>>>(nbr, m, k1, wkey, link, best);
-        k_hook<<<nb, 256, 0, s>>>(nbr, m, k1, normals, link, best, hook, counters);
-        k_apply_hooks<<<nb, 256, 0, s>>>(m, link, hook, best);
-        k_compress<<<nb, 256, 0, s>>>(m, link);
+        MS_K("min_edge", s); k_min_edge<<<nb, 256, 0, s>>>(nbr, m, k1, wkey, link, best);
+        MS_K("hook", s); k_hook<<<nb, 256, 0, s>>>(nbr, m, k1, normals, link, best, hook, counters);
+        MS_K("apply_hooks", s); k_apply_hooks<<<nb, 256, 0, s>>>(m, link, hook, best);
+        MS_K("compress", s); k_compress<<<nb, 256, 0, s>>>(m, link);
+        MS_K(NULL, s);
         MS_LAUNCH_CHECK();
         int nh = 0;
         MS_CUDA(cudaMemcpyAsync(&nh, counters, sizeof(int), cudaMemcpyDeviceToHost, s));
         MS_CUDA(cudaStreamSynchronize(s));
         if (nh == 0) break;
     }
-    k_apply_orientation<<<nb, 256, 0, s>>>(m, link, srckey, normals, counters + 1);
+    MS_K("apply_orientation", s); k_apply_orientation<<<nb, 256, 0, s>>>(m, link, srckey, normals, counters + 1);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     int bad = 0;
     MS_CUDA(cudaMemcpyAsync(&bad, counters + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -238,8 +241,9 @@ extern "C" int ms_finish_pnormals(const double *normals, int64_t n, int ndir_hin
     MS_REQUIRE(pnormals_f64 != normals, "ms_finish_pnormals: output must not alias the input");
     unsigned long long *key = (unsigned long long*)ws;
     MS_CUDA(cudaMemsetAsync(key, 0, 8, s));
-    k_argmax_absz<<<MS_SM_COUNT * 4, 256, 0, s>>>(normals, n, key);
-    k_emit_pnormals<<<ms_blocks(n, 256), 256, 0, s>>>(normals, n, key, ndir_hint, pnormals_f32, pnormals_f64);
+    MS_K("argmax_absz", s); k_argmax_absz<<<MS_SM_COUNT * 4, 256, 0, s>>>(normals, n, key);
+    MS_K("emit_pnormals", s); k_emit_pnormals<<<ms_blocks(n, 256), 256, 0, s>>>(normals, n, key, ndir_hint, pnormals_f32, pnormals_f64);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }

@@ -1,0 +1,160 @@
+"""Per-frame driver of the hot path on device-resident inputs, and frame sharding across GPUs.
+
+One *frame*  is, for each leaflet: `compute_pnormals(k=18)`
+(memsurfer/membrane.py:124-157), `compute_properties` (membrane.py:237-247) and
+`compute_densities(types=[2], sigmas, get_nlipdis=True)` for label 'all' and every lipid type
+(membrane.py:289-297, examples/ex_3lipid.py:169-175).  `LeafletFrame` keeps the inputs of one
+leaflet in HBM and issues exactly those C-ABI calls (include/memsurfer_b200.h) on the current
+stream; nothing is copied back except the small per-field summary records.
+
+Independent frames share no state (examples/ex_3lipid.py:142-182), so a trajectory is sharded as
+frame f -> rank f mod world_size with no data-path collective; ranks exchange only the summary
+records (one all_gather of a few hundred bytes per frame; NCCL on GPUs, gloo in the CPU tests).
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .membrane import point_normals_device
+
+SUMMARY_FIELDS = ("parea", "mean_curv", "gaus_curv")
+
+
+def shard_frames(nframes, rank, world_size):
+    """Frame ids owned by `rank`: round-robin f = rank, rank + W, ... (contract of section 8(e))."""
+    return list(range(int(rank), int(nframes), int(world_size)))
+
+
+class LeafletFrame(object):
+    """Device-resident working set of one leaflet of one frame."""
+
+    def __init__(self, points, labels, bbox, mesh, device="cuda:0", blayer=0.2):
+        """points (N,3) f32, labels (N,), bbox (2,3): the Membrane inputs; mesh: a TriMesh whose
+        (periodic) triangulation is already set by the host producer."""
+        _lib.require_cuda()
+        self.device = torch.device(device)
+        self.bbox = np.asarray(bbox, np.float32)
+        self.blayer = float(blayer)
+        self.periodic = bool(mesh.periodic)
+        self.mesh = mesh
+        self.n = int(points.shape[0])
+        verts, faces = mesh._concat_host()
+        self.nv, self.nv_all, self.nf = int(mesh.vertices.shape[0]), int(verts.shape[0]), int(faces.shape[0])
+        self.h2d_bytes = 0
+        self.points = self._up(np.ascontiguousarray(points, np.float32))
+        self.verts = self._up(verts)
+        self.faces = self._up(faces.view(np.int32))
+        self.kverts = self.verts[:self.nv]
+        self.half_box = mesh._half_box()
+        self.bboxl = None if mesh.bboxl is None else np.asarray(mesh.bboxl, np.float32)
+        self.label_ids = {}
+        if labels is not None:
+            labels = np.asarray(labels)
+            for l in np.unique(labels):
+                ids = np.where(labels == l)[0].astype(np.int32)
+                self.label_ids[l.item() if hasattr(l, "item") else l] = self._up(ids)
+        dev = self.device
+        L = _lib.lib()
+        nv, nf = self.nv, self.nf
+        self.csr_off = torch.empty(nv + 1, dtype=torch.int32, device=dev)
+        self.csr_adj = torch.empty(max(3 * nf, 1), dtype=torch.int32, device=dev)
+        self.keep = torch.empty(max(nf, 1), dtype=torch.uint8, device=dev)
+        self.topo_ws = _lib.workspace(L.ms_mesh_topology_workspace_bytes(nv, nf), dev)
+        self.vn64 = torch.empty((nv, 3), dtype=torch.float64, device=dev)
+        self.vn32 = torch.empty((nv, 3), dtype=torch.float32, device=dev)
+        self.pa64 = torch.empty(nv, dtype=torch.float64, device=dev)
+        self.pa32 = torch.empty(nv, dtype=torch.float32, device=dev)
+        self.H = torch.empty(nv, dtype=torch.float64, device=dev)
+        self.K = torch.empty(nv, dtype=torch.float64, device=dev)
+        self.kde_ws = _lib.workspace(L.ms_kde_workspace_bytes(nv, 0), dev)
+        self.sum_ws = _lib.workspace(L.ms_field_summary_workspace_bytes(), dev)
+        self.densities = {}
+        self.pnormals32 = self.pnormals64 = None
+        self.info = {}
+
+    def _up(self, arr):
+        self.h2d_bytes += arr.nbytes
+        return torch.from_numpy(arr).to(self.device, non_blocking=True)
+
+    # ------------------------------------------------------------------ the three stages
+    def run_pnormals(self, knbrs=18, ndir_hint=+1):
+        self.pnormals32, self.pnormals64, self.info = point_normals_device(
+            self.points, self.bbox, self.periodic, self.blayer, knbrs, ndir_hint)
+
+    def run_properties(self):
+        L = _lib.lib()
+        st = _lib.stream_ptr(self.device)
+        xw, yw = self.half_box
+        _lib.check(L.ms_mesh_topology(self.verts.data_ptr(), self.nv_all, self.nv, self.faces.data_ptr(), self.nf,
+                                      xw, yw, self.csr_off.data_ptr(), self.csr_adj.data_ptr(), self.keep.data_ptr(),
+                                      self.topo_ws.data_ptr(), self.topo_ws.numel(), st), 'ms_mesh_topology')
+        _lib.check(L.ms_mesh_properties(self.verts.data_ptr(), self.nv_all, self.nv, self.faces.data_ptr(), self.nf,
+                                        self.csr_off.data_ptr(), self.csr_adj.data_ptr(), self.keep.data_ptr(),
+                                        self.vn64.data_ptr(), self.vn32.data_ptr(), self.pa64.data_ptr(),
+                                        self.pa32.data_ptr(), self.H.data_ptr(), self.K.data_ptr(), st),
+                   'ms_mesh_properties')
+
+    def run_density(self, name, type, sigma, get_nlipids, ids_dev=None, cutoff_sigmas=0.0):
+        L = _lib.lib()
+        nids = 0 if ids_dev is None else int(ids_dev.numel())
+        out = self.densities.get(name)
+        if out is None:
+            out = self.densities[name] = (torch.empty(self.nv, dtype=torch.float64, device=self.device),
+                                          torch.empty(self.nv, dtype=torch.float32, device=self.device))
+        box = None
+        if self.periodic:
+            b = self.bboxl
+            if b.shape[0] == 4:
+                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
+            box = _lib.box6(b)
+        _lib.check(L.ms_kde(self.kverts.data_ptr(), self.nv, _lib.ptr(ids_dev) if nids else None, nids, int(type),
+                            int(self.periodic), box, float(sigma), int(bool(get_nlipids)), float(cutoff_sigmas),
+                            out[0].data_ptr(), out[1].data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(),
+                            _lib.stream_ptr(self.device)), 'ms_kde')
+        return out
+
+    def run_densities(self, sigmas, types=(2,), get_nlipids=True, cutoff_sigmas=0.0):
+        """'all' + one field per label, named as Membrane.compute_densities names them."""
+        for t in types:
+            for s in sigmas:
+                self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, 'all', s), t, s, get_nlipids, None, cutoff_sigmas)
+                for l, ids in self.label_ids.items():
+                    self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, l, s), t, s, get_nlipids, ids, cutoff_sigmas)
+
+    def run(self, sigmas, knbrs=18, cutoff_sigmas=0.0):
+        self.run_pnormals(knbrs)
+        self.run_properties()
+        self.run_densities(sigmas, cutoff_sigmas=cutoff_sigmas)
+
+    def pairs_per_run(self, sigmas, types=(2,)):
+        """All-pairs-equivalent KDE pair count of run_densities."""
+        per_sigma = self.nv * self.nv + sum(self.nv * int(i.numel()) for i in self.label_ids.values())
+        return per_sigma * len(sigmas) * len(types)
+
+    # ------------------------------------------------------------------ summary record
+    def summary(self):
+        """(F,4) f64 device tensor: {sum, sum|x|, min, max} of parea, mean_curv, gaus_curv and every
+        density field (sorted by name)."""
+        L = _lib.lib()
+        st = _lib.stream_ptr(self.device)
+        fields = [self.pa64, self.H, self.K] + [self.densities[k][0] for k in sorted(self.densities)]
+        out = torch.empty((len(fields), 4), dtype=torch.float64, device=self.device)
+        for i, f in enumerate(fields):
+            _lib.check(L.ms_field_summary(f.data_ptr(), f.numel(), out[i].data_ptr(), self.sum_ws.data_ptr(),
+                                          self.sum_ws.numel(), st), 'ms_field_summary')
+        return out
+
+    def summary_names(self):
+        return list(SUMMARY_FIELDS) + sorted(self.densities)
+
+
+def gather_summaries(local, group=None):
+    """all_gather of one rank's summary tensor (any shape, same on every rank) -> (W, ...) tensor.
+    With torch.distributed not initialised this is the identity (W = 1)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return local.unsqueeze(0)
+    W = dist.get_world_size(group)
+    out = [torch.empty_like(local) for _ in range(W)]
+    dist.all_gather(out, local.contiguous(), group=group)
+    return torch.stack(out)

@@ -92,11 +92,11 @@ class Membrane(object):
             self.labels = None
 
         self.device = torch.device(kwargs.get('device', 'cuda:0'))
-        self.points = self.points.astype(np.float32)
+        self.points = _lib.pinned_copy(self.points, np.float32)
         self.bbox = self.bbox.astype(np.float32)
         # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
         # later fit_points_to_box_xy(): normals are computed on these coordinates
-        self._pset_points = self.points.copy()
+        self._pset_points = _lib.pinned_copy(self.points, np.float32)
 
         self.pnormals = None
         self.pnormals_f64 = None
@@ -129,7 +129,7 @@ class Membrane(object):
         if self.pnormals is not None:
             return self.pnormals
         _lib.require_cuda()
-        pts = torch.from_numpy(np.ascontiguousarray(self._pset_points)).to(self.device)
+        pts = _lib.h2d(self._pset_points, self.device)
         o32, o64, info = point_normals_device(pts, self.bbox, self.periodic,
                                               getattr(self, 'blayer', 0.2), knbrs, ndir_hint)
         self.info['pnormals'] = info
@@ -137,8 +137,8 @@ class Membrane(object):
             # the reference silently returns a permuted array here (PointSet.cpp:176-193)
             LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
                            "Some normals may be incorrectly oriented!")
-        self.pnormals = o32.cpu().numpy()
-        self.pnormals_f64 = o64.cpu().numpy()
+        self.pnormals = _lib.d2h(o32)
+        self.pnormals_f64 = _lib.d2h(o64)
         if self.pnormals.shape != (self.npoints, 3):
             raise ValueError(f'PointSet computed incorrect normals (got {self.pnormals.size} values')
         return self.pnormals

@@ -30,7 +30,7 @@ class TriMesh(object):
         vertices = np.asarray(vertices)
         if vertices.ndim != 2 or vertices.shape[1] not in [2, 3]:
             raise ValueError(f'TriMesh needs 2D or 3D vertices: got {vertices.shape}')
-        self.vertices = vertices.astype(np.float32)
+        self.vertices = _lib.pinned_copy(vertices, np.float32)
 
         if 'faces' in kwargs and kwargs['faces'] is not None:
             faces = np.asarray(kwargs['faces'])
@@ -130,18 +130,22 @@ class TriMesh(object):
 
     # ---------------------------------------------------------------------- device staging
     def _concat_host(self):
+        """verts ++ dup verts (z = 0 for planar meshes) and faces ++ trimmed faces, page-locked."""
         include_periodic = self.periodic and (self._duplicated_vidxs is not None)
-        verts = self.vertices
-        if verts.shape[1] == 2:
-            verts = np.concatenate([verts, np.zeros((verts.shape[0], 1), np.float32)], axis=1)
-        faces = self.faces
+        V, dim = self.vertices.shape
+        Vd = self._duplicated_verts.shape[0] if include_periodic else 0
+        F0 = self.faces.shape[0]
+        Ft = self._trimmed_faces.shape[0] if include_periodic else 0
+        verts = _lib.pinned_empty((V + Vd, 3), np.float32)
+        faces = _lib.pinned_empty((F0 + Ft, 3), np.uint32)
+        if dim == 2:
+            verts[:, 2] = 0.0
+        verts[:V, :dim] = self.vertices
+        faces[:F0] = self.faces
         if include_periodic:
-            dv = self._duplicated_verts
-            if dv.shape[1] == 2:
-                dv = np.concatenate([dv, np.zeros((dv.shape[0], 1), np.float32)], axis=1)
-            verts = np.concatenate((verts, dv), axis=0)
-            faces = np.concatenate((self.faces, self._trimmed_faces), axis=0)
-        return np.ascontiguousarray(verts, np.float32), np.ascontiguousarray(faces, np.uint32)
+            verts[V:, :dim] = self._duplicated_verts
+            faces[F0:] = self._trimmed_faces
+        return verts, faces
 
     def to_device(self, pinned=None):
         """Stage verts ++ dup verts and faces ++ trimmed faces in HBM (TriMesh.hpp:360-364 layout)."""
@@ -152,8 +156,9 @@ class TriMesh(object):
             raise ValueError(f'{self.tag()} has no faces (call compute_delaunay or pass faces=)')
         verts, faces = self._concat_host()
         d = self._dev
-        d['verts'] = torch.from_numpy(verts).to(self.device, non_blocking=True)
-        d['faces'] = torch.from_numpy(faces.view(np.int32)).to(self.device, non_blocking=True)
+        d['verts'] = _lib.h2d(verts, self.device)
+        d['faces'] = _lib.h2d(faces.view(np.int32), self.device)
+        d['_host'] = (verts, faces)          # keep the page-locked staging alive until the copy is done
         d['nv'] = self.vertices.shape[0]
         return d
 
@@ -211,8 +216,8 @@ class TriMesh(object):
         if key in self.attributes:
             return self.attributes[key]
         d = self.properties_device()
-        self.attributes[key] = d['vn32'].cpu().numpy()
-        self.attributes_f64[key] = d['vn64'].cpu().numpy()
+        self.attributes[key] = _lib.d2h(d['vn32'])
+        self.attributes_f64[key] = _lib.d2h(d['vn64'])
         return self.attributes[key]
 
     def compute_pointareas(self):
@@ -221,8 +226,8 @@ class TriMesh(object):
         if key in self.attributes:
             return self.attributes[key]
         d = self.properties_device()
-        self.attributes[key] = d['pa32'].cpu().numpy()
-        self.attributes_f64[key] = d['pa64'].cpu().numpy()
+        self.attributes[key] = _lib.d2h(d['pa32'])
+        self.attributes_f64[key] = _lib.d2h(d['pa64'])
         return self.attributes[key]
 
     def compute_curvatures(self):
@@ -231,8 +236,8 @@ class TriMesh(object):
         if keys[0] in self.attributes and keys[1] in self.attributes:
             return self.attributes[keys[0]], self.attributes[keys[1]]
         d = self.properties_device()
-        self.attributes[keys[0]] = d['H'].cpu().numpy()
-        self.attributes[keys[1]] = d['K'].cpu().numpy()
+        self.attributes[keys[0]] = _lib.d2h(d['H'])
+        self.attributes[keys[1]] = _lib.d2h(d['K'])
         self.attributes_f64[keys[0]] = self.attributes[keys[0]]
         self.attributes_f64[keys[1]] = self.attributes[keys[1]]
         return self.attributes[keys[0]], self.attributes[keys[1]]
@@ -249,10 +254,15 @@ class TriMesh(object):
         dev = self.device
         d = self._dev
         if 'kverts' not in d:
-            v = self.vertices
-            if v.shape[1] == 2:
-                v = np.concatenate([v, np.zeros((v.shape[0], 1), np.float32)], axis=1)
-            d['kverts'] = torch.from_numpy(np.ascontiguousarray(v, np.float32)).to(dev)
+            if 'verts' in d:
+                d['kverts'] = d['verts'][:self.vertices.shape[0]]      # already resident (first V rows)
+            elif self.vertices.shape[1] == 3:
+                d['kverts'] = _lib.h2d(self.vertices, dev)
+            else:
+                v = _lib.pinned_empty((self.vertices.shape[0], 3), np.float32)
+                v[:, :2] = self.vertices; v[:, 2] = 0.0
+                d['kverts'] = _lib.h2d(v, dev)
+                d['_khost'] = v
         nv = d['kverts'].shape[0]
         nids = 0 if pidxs_dev is None else int(pidxs_dev.numel())
         o64 = torch.empty(nv, dtype=torch.float64, device=dev)
@@ -290,10 +300,10 @@ class TriMesh(object):
         pidxs = np.asarray(pidxs)
         pd = None
         if pidxs.shape[0] > 0:
-            pd = torch.from_numpy(np.ascontiguousarray(pidxs, dtype=np.int32)).to(self.device)
+            pd = _lib.h2d(_lib.pinned_copy(pidxs, np.int32), self.device)
         o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
-        dens = o32.cpu().numpy()
+        dens = _lib.d2h(o32)
         self._fields[name] = dens
-        self.attributes_f64[name] = o64.cpu().numpy()
+        self.attributes_f64[name] = _lib.d2h(o64)
         LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         return dens

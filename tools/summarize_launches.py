@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list per kernel name."""
+import collections
+import csv
+import sys
+
+
+def main(path):
+    with open(path) as f:
+        lines = [l for l in f if l.startswith('"')]
+    agg = collections.OrderedDict()
+    for row in csv.DictReader(lines):
+        a = agg.setdefault(row["Kernel Name"], [0, 0.0])
+        a[0] += 1
+        a[1] += float(row["Metric Value"].replace(",", ""))
+    tot = sum(a[1] for a in agg.values())
+    print(f"# {path}: {sum(a[0] for a in agg.values())} launches, {tot / 1e6:.3f} ms device time (cold-cache, serialised)")
+    print(f"{'kernel':70s} {'launches':>8s} {'total_ms':>12s} {'avg_us':>10s} {'share':>8s}")
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print(f"{k[:70]:70s} {a[0]:8d} {a[1] / 1e6:12.3f} {a[1] / a[0] / 1e3:10.1f} {a[1] / tot:8.4f}")
+
+
+if __name__ == "__main__":
+    main(sys.argv[1])
