@@ -104,13 +104,23 @@ int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
  * DistancePeriodicXYSquared (DistanceKernels.hpp:75-136) fused in.
  * verts (nv,3) f32 = the mesh's own vertices (targets: all of them); ids (nids) i32 = source
  * vertex ids, nids == 0 -> all.  type 2|3.  periodic: box6 (host) = bboxl.  cutoff_sigmas <= 0:
- * all pairs (the reference's sum); > 0: pairs beyond cutoff_sigmas*sigma are dropped through a
- * cell list (relative tail mass exp(-c^2/2)).  get_counts as TriMesh_kde.cpp:515-524.          */
+ * all pairs (the reference's sum); > 0: only pairs inside a window of cells that covers every pair
+ * closer than cutoff_sigmas*sigma are evaluated (cell list; dropped relative tail mass
+ * <= exp(-cutoff_sigmas^2/2); needs box6 -- for a non-periodic mesh pass the vertex extent -- and
+ * falls back to all pairs when the window would not fit the period).  get_counts as
+ * TriMesh_kde.cpp:515-524.                                                                     */
 size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids);
 int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
            int type, int periodic, const float *box6, float sigma, int get_counts,
            double cutoff_sigmas, double *density_f64, float *density_f32,
            void *ws, size_t ws_bytes, void *stream);
+
+/* Diagnostic (roofline accounting): the number of pairs ms_kde evaluates for the same arguments --
+ * nv*n_ids for the all-pairs kernel, the sum over cells of targets x window sources for the cell
+ * list.  *pairs is a host double.  Syncs the stream.                                            */
+int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+                           int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                           double *pairs, void *ws, size_t ws_bytes, void *stream);
 
 /* fp64 FMA peak probe used for the KDE roofline: runs `iters` dependent-chain DFMA rounds on
  * every SM and returns the number of FLOP issued in *flop (host); time it with events.         */

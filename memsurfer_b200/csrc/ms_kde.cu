@@ -5,24 +5,42 @@
 // TriMesh::kde TriMesh_kde.cpp:504-524, GaussianKernel2D/3D DensityKernels.hpp:44-84 and
 // DistanceSquared / DistancePeriodicXYSquared DistanceKernels.hpp:75-136 (fused in).
 //
-// Design (not a contraction -> no tensor cores; bound = fp64 FMA pipe):
-//   * coordinates are pre-scaled by sqrt(-efactor*log2(e)) once per field, so the pair term is
-//     2^-(dx^2+dy^2[+dz^2]): no per-pair multiply by efactor, sfactor is applied once per target;
-//   * single-wrap minimum image: the reference adds boxw to the smaller coordinate when
-//     |dx| >= boxw/2; (|dx|-boxw)^2 == min(|dx|, boxw-|dx|)^2, which is branch-free;
-//   * software exp2: round-to-nearest split with the 1.5*2^52 trick, degree-11 polynomial on
-//     [-1/2,1/2] (truncation 6e-15 relative), scale 2^-n built from integer bits and folded into
-//     the accumulating DFMA;
-//   * source tiles are staged into shared memory by the TMA engine (cp.async.bulk + mbarrier,
-//     double buffered); every thread keeps R targets in registers so one broadcast LDS.128
-//     feeds R independent DFMA chains.
+// Design (not a contraction -> no tensor cores; bound = the fp64 pipe, 64 DFMA/clk/SM):
+//   * coordinates are pre-scaled by sqrt(-efactor*log2(e)*256) once per field, so the pair term is
+//     2^-(r/256) with r = dx^2+dy^2[+dz^2]: no per-pair multiply by efactor; sfactor is applied
+//     once per target;
+//   * software exp2 in 7 fp64 instructions: round-to-nearest split of r with the 1.5*2^52 trick
+//     (n = round(r), f = r - n in [-1/2,1/2]), 2^-(f/256) by a degree-3 near-minimax polynomial
+//     (3.5e-14 relative), 2^-((n&255)/256) from a 256-entry shared-memory table, 2^-(n>>8) by an
+//     integer subtraction from the table value's exponent field, all folded into the accumulating
+//     DFMA;
+//   * two pair-sum kernels share that core:
+//       k_kde_pairs  all V x n_ids pairs (the reference's sum).  Single-wrap minimum image as
+//                    min(|dx|, boxw-|dx|): the reference adds boxw to the smaller coordinate when
+//                    |dx| >= boxw/2, and (|dx|-boxw)^2 == min(|dx|, boxw-|dx|)^2;
+//       k_kde_cells  pairs inside a window of (2m+1)^2 cells of a uniform xy cell list (covers every
+//                    pair closer than cutoff_sigmas*sigma; dropped relative tail mass
+//                    <= exp(-cutoff_sigmas^2/2)); the periodic image shift is applied once per staged
+//                    row segment, so there is no per-pair wrap arithmetic at all;
+//   * source points are staged into shared memory by the TMA engine (cp.async.bulk + mbarrier,
+//     double buffered); every thread keeps R targets in registers so one broadcast LDS.128 feeds R
+//     independent DFMA chains.
 #include "ms_common.cuh"
+#include <math.h>
 
-#define KDE_TILE 1024           // source padding granule (entries)
-#define KDE_TILE_BYTES 16384     // bytes per shared-memory stage: 1024 double2 / 512 double4
+#define KDE_STAGE_BYTES 16384    // all-pairs: bytes per shared-memory stage (1024 double2 / 512 double4)
+#define CELL_STAGE_BYTES 8192    // cell list: bytes per stage
 #define KDE_MAGIC 6755399441055744.0   // 1.5 * 2^52
-#define KDE_CLAMP 1000.0
-#define KDE_PAD 1e100
+#define KDE_TAB 256
+#define KDE_RMAX 2147483000.0    // the scaled r must stay below 2^31 (host check or in-kernel clamp)
+
+__device__ const double c_exp2_tab[KDE_TAB] = {
+#include "ms_exp2_table.inc"
+};
+// 2^(-f/256) on [-1/2,1/2], near-minimax, relative error 3.5e-14 (tools/gen_exp2_table.py)
+#define KDE_C1 (-0x1.62e42fefa39dap-9)
+#define KDE_C2 (0x1.ebfbe3a9ac803p-19)
+#define KDE_C3 (-0x1.c6b0902b2f6c8p-29)
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -43,119 +61,298 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
-// 2^-r for r >= 0 (clamped), returned as (scale, poly) so the caller can fold scale*poly into an FMA
-__device__ __forceinline__ void exp2neg_split(double r, double &scale, double &poly) {
-    r = fmin(r, KDE_CLAMP);
+// acc += 2^-(r/256), r in [0, 2^31)
+__device__ __forceinline__ void kde_term(double r, const double *__restrict__ tab, double &acc) {
     const double t = r + KDE_MAGIC;
     const int n = __double2loint(t);
     const double f = r - (t - KDE_MAGIC);             // in [-1/2, 1/2]
-    // 2^-f = sum_k (-ln2)^k / k! f^k, k = 0..11 (truncation < 6.3e-15 on |f| <= 1/2)
-    double p =            -4.44553827187081162e-10;
-    p = fma(p, f,          7.05491162080112336e-09);
-    p = fma(p, f,         -1.01780860092396999e-07);
-    p = fma(p, f,          1.32154867901443095e-06);
-    p = fma(p, f,         -1.52527338040598411e-05);
-    p = fma(p, f,          1.54035303933816088e-04);
-    p = fma(p, f,         -1.33335581464284433e-03);
-    p = fma(p, f,          9.61812910762847688e-03);
-    p = fma(p, f,         -5.55041086648215831e-02);
-    p = fma(p, f,          2.40226506959100722e-01);
-    p = fma(p, f,         -6.93147180559945286e-01);
-    p = fma(p, f,          1.0);
-    poly = p; scale = __hiloint2double((1023 - n) << 20, 0);
+    double p = fma(KDE_C3, f, KDE_C2);
+    p = fma(p, f, KDE_C1);
+    p = fma(p, f, 1.0);
+    const double T = tab[n & (KDE_TAB - 1)];          // (1/2, 1]
+    const int e = min(n >> 8, 1021);                  // beyond 2^-1021 the term is held at ~1e-308 (i.e. dropped)
+    const double sc = __hiloint2double(__double2hiint(T) - (e << 20), __double2loint(T));
+    acc = fma(sc, p, acc);
 }
 
-// ------------------------------------------------------------------ staging of scaled coordinates
 template <int DIM> struct SrcT;
 template <> struct SrcT<2> { typedef double2 type; };
 template <> struct SrcT<3> { typedef double4 type; };
 
-// tgt[j] = scaled vertex j (all vertices); src[i] = scaled vertex ids[i] (or i), padded to a
-// multiple of KDE_TILE with far-away sentinels whose contribution underflows to ~2^-1000.
-template <int DIM>
-__global__ void __launch_bounds__(256) k_kde_stage(const float *__restrict__ verts, int64_t nv,
-                                                   const int32_t *__restrict__ ids, int64_t ns, int64_t ns_pad,
-                                                   double scale, typename SrcT<DIM>::type *tgt,
-                                                   typename SrcT<DIM>::type *src) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    typename SrcT<DIM>::type o;
-    if (i < nv) {
-        o.x = ms_ld_f(verts + 3*i) * scale; o.y = ms_ld_f(verts + 3*i + 1) * scale;
-        if (DIM == 3) { ((double*)&o)[2] = ms_ld_f(verts + 3*i + 2) * scale; ((double*)&o)[3] = 0.0; }
-        tgt[i] = o;
-    }
-    if (i < ns_pad) {
-        if (i < ns) {
-            const int64_t s = ids ? (int64_t)__ldg(ids + i) : i;
-            o.x = ms_ld_f(verts + 3*s) * scale; o.y = ms_ld_f(verts + 3*s + 1) * scale;
-            if (DIM == 3) { ((double*)&o)[2] = ms_ld_f(verts + 3*s + 2) * scale; ((double*)&o)[3] = 0.0; }
-        } else {
-            o.x = KDE_PAD; o.y = KDE_PAD;
-            if (DIM == 3) { ((double*)&o)[2] = 0.0; ((double*)&o)[3] = 0.0; }
+// all threads of the CTA: accumulate cnt staged sources into R register targets
+template <int DIM, bool WRAP, bool CLAMP, int R>
+__device__ __forceinline__ void kde_accumulate(const typename SrcT<DIM>::type *__restrict__ T, int cnt,
+                                               const double *__restrict__ tab, const double (&tx)[R], const double (&ty)[R],
+                                               const double (&tz)[R], double (&acc)[R], double wx, double wy) {
+    typedef typename SrcT<DIM>::type S;
+#pragma unroll 2
+    for (int i = 0; i < cnt; i++) {
+        const S sp = T[i];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            double dx = sp.x - tx[r], dy = sp.y - ty[r];
+            if (WRAP) {
+                // plain compare-select (fmin() would add NaN-quieting instructions per pair)
+                // (only the square is used, so the sign of the kept value does not matter)
+                const double bx = wx - fabs(dx), by = wy - fabs(dy);
+                dx = fabs(dx) < bx ? dx : bx; dy = fabs(dy) < by ? dy : by;
+            }
+            double r2 = fma(dy, dy, dx * dx);
+            if (DIM == 3) { const double dz = ((const double*)&sp)[2] - tz[r]; r2 = fma(dz, dz, r2); }
+            if (CLAMP) r2 = r2 < KDE_RMAX ? r2 : KDE_RMAX;
+            kde_term(r2, tab, acc[r]);
         }
-        src[i] = o;
     }
 }
 
-// ------------------------------------------------------------------ the pair-sum
+// ------------------------------------------------------------------ staging of scaled coordinates
+// dst[i] = scale * vertex (ids ? ids[i] : i)
+template <int DIM>
+__global__ void __launch_bounds__(256) k_kde_stage(const float *__restrict__ verts, const int32_t *__restrict__ ids, int64_t n,
+                                                   double scale, typename SrcT<DIM>::type *dst) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t s = ids ? (int64_t)__ldg(ids + i) : i;
+    typename SrcT<DIM>::type o;
+    o.x = ms_ld_f(verts + 3*s) * scale; o.y = ms_ld_f(verts + 3*s + 1) * scale;
+    if (DIM == 3) { ((double*)&o)[2] = ms_ld_f(verts + 3*s + 2) * scale; ((double*)&o)[3] = 0.0; }
+    dst[i] = o;
+}
+
+// ------------------------------------------------------------------ all pairs
 // grid.x: target blocks (THREADS*R targets each); grid.y: source splits (tiles [y*tps,(y+1)*tps)).
-// partial[y*nv + j] = sum over the split's sources of 2^-(scaled distance^2).
-template <int DIM, bool PERIODIC, int THREADS, int R>
+// partial[y*nv + j] = sum over the split's sources of 2^-(scaled distance^2 / 256).
+template <int DIM, bool PERIODIC, bool CLAMP, int THREADS, int R>
 __global__ void __launch_bounds__(THREADS) k_kde_pairs(const typename SrcT<DIM>::type *__restrict__ tgt, int64_t nv,
-                                                       const typename SrcT<DIM>::type *__restrict__ src, int ntiles, int tiles_per_split,
+                                                       const typename SrcT<DIM>::type *__restrict__ src, int64_t ns,
+                                                       int ntiles, int tiles_per_split,
                                                        double wx, double wy, double *__restrict__ partial) {
     typedef typename SrcT<DIM>::type S;
-    constexpr int TILE = KDE_TILE_BYTES / (int)sizeof(S);
+    constexpr int TILE = KDE_STAGE_BYTES / (int)sizeof(S);
     __shared__ __align__(128) S tile[2][TILE];
+    __shared__ __align__(16) double tab[KDE_TAB];
     __shared__ __align__(8) uint64_t bar[2];
     const int tid = threadIdx.x;
     const int t_begin = blockIdx.y * tiles_per_split;
     const int t_end = min(ntiles, t_begin + tiles_per_split);
     const int64_t j0 = (int64_t)blockIdx.x * (THREADS * R) + tid;
+    for (int i = tid; i < KDE_TAB; i += THREADS) tab[i] = c_exp2_tab[i];
 
     double tx[R], ty[R], tz[R], acc[R];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int64_t j = j0 + (int64_t)r * THREADS;
-        S q; q.x = KDE_PAD * 4; q.y = KDE_PAD * 4; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
+        S q; q.x = 0.0; q.y = 0.0; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
         if (j < nv) q = tgt[j];
         tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0; acc[r] = 0.0;
     }
     if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncthreads();
-    const uint32_t tile_bytes = KDE_TILE_BYTES;
-    if (tid == 0 && t_begin < t_end) { mbar_expect_tx(&bar[0], tile_bytes); bulk_g2s(tile[0], src + (size_t)t_begin * TILE, tile_bytes, &bar[0]); }
-    uint32_t phase[2] = { 0u, 0u };
+    auto tile_count = [&](int t) { return (int)min((int64_t)TILE, ns - (int64_t)t * TILE); };
+    if (tid == 0 && t_begin < t_end) {
+        const uint32_t bytes = (uint32_t)tile_count(t_begin) * (uint32_t)sizeof(S);
+        mbar_expect_tx(&bar[0], bytes); bulk_g2s(tile[0], src + (size_t)t_begin * TILE, bytes, &bar[0]);
+    }
+    uint32_t phase = 0u;                  // bit s = parity to wait for on stage s
     for (int t = t_begin; t < t_end; t++) {
         const int s = (t - t_begin) & 1;
         if (tid == 0 && t + 1 < t_end) {   // buffer s^1 was released by the __syncthreads closing iteration t-1
-            mbar_expect_tx(&bar[s ^ 1], tile_bytes);
-            bulk_g2s(tile[s ^ 1], src + (size_t)(t + 1) * TILE, tile_bytes, &bar[s ^ 1]);
+            const uint32_t bytes = (uint32_t)tile_count(t + 1) * (uint32_t)sizeof(S);
+            mbar_expect_tx(&bar[s ^ 1], bytes);
+            bulk_g2s(tile[s ^ 1], src + (size_t)(t + 1) * TILE, bytes, &bar[s ^ 1]);
         }
-        mbar_wait(&bar[s], phase[s]); phase[s] ^= 1u;
-        const S *T = tile[s];
-#pragma unroll 2
-        for (int i = 0; i < TILE; i++) {
-            const S sp = T[i];
-#pragma unroll
-            for (int r = 0; r < R; r++) {
-                double dx = sp.x - tx[r], dy = sp.y - ty[r];
-                if (PERIODIC) {
-                    const double ax = fabs(dx), ay = fabs(dy);
-                    dx = fmin(ax, wx - ax); dy = fmin(ay, wy - ay);
-                }
-                double r2 = fma(dy, dy, dx * dx);
-                if (DIM == 3) { const double dz = ((const double*)&sp)[2] - tz[r]; r2 = fma(dz, dz, r2); }
-                double sc, po; exp2neg_split(r2, sc, po);
-                acc[r] = fma(sc, po, acc[r]);
-            }
-        }
+        mbar_wait(&bar[s], (phase >> s) & 1u); phase ^= 1u << s;
+        kde_accumulate<DIM, PERIODIC, CLAMP, R>(tile[s], tile_count(t), tab, tx, ty, tz, acc, wx, wy);
         __syncthreads();
     }
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int64_t j = j0 + (int64_t)r * THREADS;
         if (j < nv) partial[(size_t)blockIdx.y * nv + j] = acc[r];
+    }
+}
+
+// ------------------------------------------------------------------ cell list (cut-off variant)
+struct KdeGrid {
+    double b0x, b0y;          // scaled origin of the grid
+    double inv_cx, inv_cy;    // 1 / scaled cell size per axis
+    double wx, wy;            // scaled extent (the period when periodic): ncx*cell_x, ncy*cell_y
+    int ncx, ncy, m, periodic;
+};
+
+template <int DIM>
+__device__ __forceinline__ int kde_cell_of(const KdeGrid &g, const typename SrcT<DIM>::type &p) {
+    int cx = (int)floor((p.x - g.b0x) * g.inv_cx), cy = (int)floor((p.y - g.b0y) * g.inv_cy);
+    if (g.periodic) {            // points on / beyond a face fold back: the cells tile the period exactly
+        cx %= g.ncx; if (cx < 0) cx += g.ncx;
+        cy %= g.ncy; if (cy < 0) cy += g.ncy;
+    } else {
+        cx = max(0, min(g.ncx - 1, cx)); cy = max(0, min(g.ncy - 1, cy));
+    }
+    return cy * g.ncx + cx;
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(256) k_kde_cell_count(const typename SrcT<DIM>::type *__restrict__ pts, int64_t n, KdeGrid g,
+                                                        int32_t *cell, int32_t *cnt) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = kde_cell_of<DIM>(g, pts[i]);
+    cell[i] = c; atomicAdd(cnt + c, 1);
+}
+__global__ void __launch_bounds__(256) k_kde_cell_scatter(int64_t n, const int32_t *__restrict__ cell, const int32_t *__restrict__ start,
+                                                          int32_t *cursor, int32_t *perm) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = cell[i];
+    perm[start[c] + atomicAdd(cursor + c, 1)] = (int32_t)i;
+}
+// ascending element order inside every cell => the summation order (and the result) is reproducible.
+// One warp per cell: every lane ranks its elements against the whole cell (counting sort by
+// comparison, all in registers); cells with more than 256 elements fall back to a serial sort.
+#define SORT_K 8
+__global__ void __launch_bounds__(128) k_kde_cell_sort(int ncell, const int32_t *__restrict__ start, int32_t *perm) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (c >= ncell) return;
+    const int b = start[c], e = start[c + 1], n = e - b;
+    if (n <= 1) return;
+    if (n > 32 * SORT_K) {
+        if (lane == 0)
+            for (int i = b + 1; i < e; i++) {
+                const int32_t key = perm[i]; int j = i - 1;
+                while (j >= b && perm[j] > key) { perm[j + 1] = perm[j]; j--; }
+                perm[j + 1] = key;
+            }
+        return;
+    }
+    int32_t v[SORT_K]; int rank[SORT_K];
+#pragma unroll
+    for (int k = 0; k < SORT_K; k++) { const int i = lane + 32 * k; v[k] = i < n ? perm[b + i] : 0x7fffffff; rank[k] = 0; }
+    const int rounds = (n + 31) >> 5;
+#pragma unroll
+    for (int k2 = 0; k2 < SORT_K; k2++) {
+        if (k2 < rounds) {
+            for (int l = 0; l < 32; l++) {
+                const int32_t o = __shfl_sync(0xffffffffu, v[k2], l);
+#pragma unroll
+                for (int k = 0; k < SORT_K; k++) rank[k] += o < v[k];
+            }
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < SORT_K; k++) if (lane + 32 * k < n) perm[b + rank[k]] = v[k];      // indices are distinct
+}
+
+// sorted[i] = point perm[i], folded into the canonical period [b0, b0+w) when the grid is periodic so
+// that its coordinates agree with the cell it was binned into
+template <int DIM>
+__global__ void __launch_bounds__(256) k_kde_cell_gather(const typename SrcT<DIM>::type *__restrict__ pts, int64_t n, KdeGrid g,
+                                                         const int32_t *__restrict__ perm, typename SrcT<DIM>::type *sorted) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typename SrcT<DIM>::type p = pts[perm[i]];
+    if (g.periodic) {
+        const int cx = (int)floor((p.x - g.b0x) * g.inv_cx), cy = (int)floor((p.y - g.b0y) * g.inv_cy);
+        const int kx = (cx >= 0 ? cx : cx - g.ncx + 1) / g.ncx, ky = (cy >= 0 ? cy : cy - g.ncy + 1) / g.ncy;
+        p.x -= (double)kx * g.wx; p.y -= (double)ky * g.wy;
+    }
+    sorted[i] = p;
+}
+
+// Enumerates the source window of one target cell as contiguous ranges of the cell-sorted source
+// array (one per row of cells, two when the row wraps around the period), cut into stage-sized
+// chunks, each with the periodic image shift to ADD TO THE TARGET coordinates.
+struct KdeWindow {
+    int dy, piece, np, row, o, e;
+    int xa[2], xb[2];
+    double shx[2], shy;
+};
+__device__ __forceinline__ void kde_window_init(KdeWindow &w, const KdeGrid &g) { w.dy = -g.m - 1; w.piece = 0; w.np = 0; w.o = w.e = 0; }
+__device__ __forceinline__ bool kde_window_next(KdeWindow &w, const KdeGrid &g, int cx, int cy, const int32_t *__restrict__ sstart,
+                                                int cap, int &off, int &cnt, double &shx, double &shy) {
+    for (;;) {
+        if (w.o < w.e) { off = w.o; cnt = min(cap, w.e - w.o); w.o += cnt; shx = w.shx[w.piece]; shy = w.shy; return true; }
+        w.piece++;
+        if (w.piece >= w.np) {
+            w.dy++; w.piece = 0; w.np = 0;
+            if (w.dy > g.m) return false;
+            int row = cy + w.dy; w.shy = 0.0;
+            if (row < 0) { if (!g.periodic) { w.piece = 0; continue; } row += g.ncy; w.shy = g.wy; }
+            else if (row >= g.ncy) { if (!g.periodic) { w.piece = 0; continue; } row -= g.ncy; w.shy = -g.wy; }
+            w.row = row; w.np = 1;
+            w.xa[0] = cx - g.m; w.xb[0] = cx + g.m; w.shx[0] = 0.0;
+            if (!g.periodic) { w.xa[0] = max(w.xa[0], 0); w.xb[0] = min(w.xb[0], g.ncx - 1); }
+            else if (w.xa[0] < 0) { w.xa[1] = 0; w.xb[1] = w.xb[0]; w.shx[1] = 0.0; w.xa[0] += g.ncx; w.xb[0] = g.ncx - 1; w.shx[0] = g.wx; w.np = 2; }
+            else if (w.xb[0] >= g.ncx) { w.xa[1] = 0; w.xb[1] = w.xb[0] - g.ncx; w.shx[1] = -g.wx; w.xb[0] = g.ncx - 1; w.np = 2; }
+        }
+        w.o = __ldg(sstart + w.row * g.ncx + w.xa[w.piece]);
+        w.e = __ldg(sstart + w.row * g.ncx + w.xb[w.piece] + 1);
+    }
+}
+
+// One CTA per target cell; 64 threads x 2 register targets (chunks of 128 targets).
+#define CELL_T 64
+template <int DIM, bool CLAMP>
+__global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::type *__restrict__ tgt, const int32_t *__restrict__ tstart,
+                                                      const int32_t *__restrict__ tperm,
+                                                      const typename SrcT<DIM>::type *__restrict__ src, const int32_t *__restrict__ sstart,
+                                                      KdeGrid g, double *__restrict__ out) {
+    typedef typename SrcT<DIM>::type S;
+    constexpr int CAP = CELL_STAGE_BYTES / (int)sizeof(S);
+    __shared__ __align__(128) S buf[2][CAP];
+    __shared__ __align__(16) double tab[KDE_TAB];
+    __shared__ __align__(8) uint64_t bar[2];
+    const int tid = threadIdx.x;
+    const int cell = blockIdx.x, cx = cell % g.ncx, cy = cell / g.ncx;
+    const int t0 = __ldg(tstart + cell), t1 = __ldg(tstart + cell + 1);
+    if (t0 == t1) return;
+    for (int i = tid; i < KDE_TAB; i += CELL_T) tab[i] = c_exp2_tab[i];
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    uint32_t phase = 0u;                  // bit s = parity to wait for on stage s
+    int stage = 0;
+    for (int c0 = t0; c0 < t1; c0 += CELL_T * 2) {
+        double tx[2], ty[2], tz[2], acc[2];
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const int j = c0 + tid + r * CELL_T;
+            S q; q.x = 0.0; q.y = 0.0; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
+            if (j < t1) q = tgt[j];
+            tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0; acc[r] = 0.0;
+        }
+        const bool two = c0 + (tid & ~31) + CELL_T < t1;     // warp-uniform: any target in this warp's second slot?
+        KdeWindow w; kde_window_init(w, g);
+        int off, cnt, noff, ncnt; double shx, shy, nshx, nshy;
+        bool have = kde_window_next(w, g, cx, cy, sstart, CAP, off, cnt, shx, shy);
+        if (have && tid == 0) {
+            mbar_expect_tx(&bar[stage], (uint32_t)cnt * (uint32_t)sizeof(S));
+            bulk_g2s(buf[stage], src + off, (uint32_t)cnt * (uint32_t)sizeof(S), &bar[stage]);
+        }
+        while (have) {
+            const bool more = kde_window_next(w, g, cx, cy, sstart, CAP, noff, ncnt, nshx, nshy);
+            if (more && tid == 0) {          // the other stage was released by the __syncthreads of the previous round
+                mbar_expect_tx(&bar[stage ^ 1], (uint32_t)ncnt * (uint32_t)sizeof(S));
+                bulk_g2s(buf[stage ^ 1], src + noff, (uint32_t)ncnt * (uint32_t)sizeof(S), &bar[stage ^ 1]);
+            }
+            mbar_wait(&bar[stage], (phase >> stage) & 1u); phase ^= 1u << stage;
+            if (two) {
+                const double sx[2] = { tx[0] + shx, tx[1] + shx }, sy[2] = { ty[0] + shy, ty[1] + shy };
+                kde_accumulate<DIM, false, CLAMP, 2>(buf[stage], cnt, tab, sx, sy, tz, acc, 0.0, 0.0);
+            } else {
+                const double sx[1] = { tx[0] + shx }, sy[1] = { ty[0] + shy }, tz1[1] = { tz[0] };
+                double a1[1] = { acc[0] };
+                kde_accumulate<DIM, false, CLAMP, 1>(buf[stage], cnt, tab, sx, sy, tz1, a1, 0.0, 0.0);
+                acc[0] = a1[0];
+            }
+            __syncthreads();
+            stage ^= 1; have = more; off = noff; cnt = ncnt; shx = nshx; shy = nshy;
+        }
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const int j = c0 + tid + r * CELL_T;
+            if (j < t1) out[__ldg(tperm + j)] = acc[r];
+        }
     }
 }
 
@@ -195,42 +392,177 @@ __global__ void __launch_bounds__(256) k_kde_emit(const double *__restrict__ den
     if (o32) o32[j] = (float)d;
 }
 
-struct KdePlan { int64_t ns, ns_pad; int threads, R, nsplit; int64_t blocks_x; };
+// ------------------------------------------------------------------ host side
+struct KdePlan { int64_t ns; int threads, R, nsplit; int64_t blocks_x; };
 static KdePlan kde_plan(int64_t nv, int64_t nids) {
     KdePlan p;
     p.ns = nids > 0 ? nids : nv;
-    p.ns_pad = (p.ns + KDE_TILE - 1) / KDE_TILE * KDE_TILE;
     const bool big = nv >= (int64_t)MS_SM_COUNT * 128 * 4 * 2;
     p.threads = big ? 128 : 64; p.R = big ? 4 : 1;
     p.blocks_x = (nv + p.threads * p.R - 1) / (p.threads * p.R);
-    const int64_t ntiles = p.ns_pad / 512;                      // smallest tile (3-D)
-    int64_t want = (MS_SM_COUNT * 8 + p.blocks_x - 1) / (p.blocks_x > 0 ? p.blocks_x : 1);
+    // enough CTAs for >= 16 full waves (6 resident CTAs per SM) so that the last, partial wave costs
+    // a few percent at most; the splits are combined by k_kde_combine
+    const int64_t ntiles = (p.ns + 511) / 512;                      // smallest tile (3-D)
+    int64_t want = ((int64_t)MS_SM_COUNT * 6 * 16 + p.blocks_x - 1) / (p.blocks_x > 0 ? p.blocks_x : 1);
     if (want < 1) want = 1; if (want > 64) want = 64; if (want > ntiles) want = ntiles > 0 ? ntiles : 1;
     p.nsplit = (int)want;
     return p;
 }
+static int64_t kde_max_cells(int64_t nv) { return nv / 16 + 4096; }
 
 extern "C" size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids) {
     const KdePlan p = kde_plan(nv, nids);
-    return ms_align((size_t)nv * 32) + ms_align((size_t)p.ns_pad * 32) + ms_align((size_t)p.nsplit * nv * 8)
-         + ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8) + 4096;
+    const size_t nc = (size_t)kde_max_cells(nv) + 2;
+    return 2 * ms_align((size_t)nv * 32) + 2 * ms_align((size_t)p.ns * 32)       // staged + cell-sorted targets, sources
+         + ms_align((size_t)p.nsplit * nv * 8) + ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8)
+         + 2 * ms_align((size_t)nv * 4) + 2 * ms_align((size_t)p.ns * 4)         // cell ids, permutations
+         + 4 * ms_align(nc * 4) + ms_scan_ws_bytes((int64_t)nc) + 8192;
 }
 
-template <int DIM, bool PER>
-static int kde_run(const float *verts, int64_t nv, const int32_t *ids, const KdePlan &p, double scale, double wx, double wy,
-                   void *tgt_, void *src_, double *partial, cudaStream_t s) {
+template <int DIM, bool PER, bool CLAMP>
+static int kde_run_pairs(const KdePlan &p, int64_t nv, double wx, double wy, void *tgt_, void *src_, double *partial, cudaStream_t s) {
     typedef typename SrcT<DIM>::type S;
     S *tgt = (S*)tgt_, *src = (S*)src_;
-    const int64_t nstage = nv > p.ns_pad ? nv : p.ns_pad;
-    MS_K("kde_stage", s); k_kde_stage<DIM><<<ms_blocks(nstage, 256), 256, 0, s>>>(verts, nv, ids, p.ns, p.ns_pad, scale, tgt, src);
-    const int tile = KDE_TILE_BYTES / (int)sizeof(S);
-    const int ntiles = (int)(p.ns_pad / tile);
+    const int tile = KDE_STAGE_BYTES / (int)sizeof(S);
+    const int ntiles = (int)((p.ns + tile - 1) / tile);
     const int tps = (ntiles + p.nsplit - 1) / p.nsplit;
     dim3 grid((unsigned)p.blocks_x, (unsigned)p.nsplit);
-    if (p.R == 4) { MS_K("kde_pairs", s); k_kde_pairs<DIM, PER, 128, 4><<<grid, 128, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial); }
-    else          { MS_K("kde_pairs", s); k_kde_pairs<DIM, PER, 64, 1><<<grid, 64, 0, s>>>(tgt, nv, src, ntiles, tps, wx, wy, partial); }
-    MS_K(NULL, s);
+    MS_K("kde_pairs", s);
+    if (p.R == 4) k_kde_pairs<DIM, PER, CLAMP, 128, 4><<<grid, 128, 0, s>>>(tgt, nv, src, p.ns, ntiles, tps, wx, wy, partial);
+    else          k_kde_pairs<DIM, PER, CLAMP, 64, 1><<<grid, 64, 0, s>>>(tgt, nv, src, p.ns, ntiles, tps, wx, wy, partial);
     MS_LAUNCH_CHECK();
+    return 0;
+}
+
+// cell-sort n staged points: start (ncell+1), perm (n), sorted (n)
+template <int DIM>
+static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, int32_t *cell, int32_t *cnt, int32_t *cursor,
+                   int32_t *start, int32_t *perm, void *sorted_, void *scan_ws, cudaStream_t s) {
+    typedef typename SrcT<DIM>::type S;
+    const S *pts = (const S*)pts_; S *sorted = (S*)sorted_;
+    const int ncell = g.ncx * g.ncy;
+    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
+    MS_K("kde_cell_count", s); k_kde_cell_count<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, cell, cnt);
+    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
+    MS_K("kde_cell_scatter", s); k_kde_cell_scatter<<<ms_blocks(n, 256), 256, 0, s>>>(n, cell, start, cursor, perm);
+    MS_K("kde_cell_sort", s); k_kde_cell_sort<<<ms_blocks((int64_t)ncell * 32, 128), 128, 0, s>>>(ncell, start, perm);
+    MS_K("kde_cell_gather", s); k_kde_cell_gather<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, perm, sorted);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+// pairs the cell-list kernel evaluates: sum over cells of (#targets) x (#sources in the window)
+template <int DUMMY>
+__global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart,
+                                                         KdeGrid g, unsigned long long *total) {
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long mine = 0ull;
+    if (cell < g.ncx * g.ncy) {
+        const int nt = tstart[cell + 1] - tstart[cell];
+        if (nt > 0) {
+            KdeWindow w; kde_window_init(w, g);
+            int off, cnt; double shx, shy; unsigned long long nsrc = 0ull;
+            while (kde_window_next(w, g, cell % g.ncx, cell / g.ncx, sstart, 1 << 30, off, cnt, shx, shy)) nsrc += (unsigned long long)cnt;
+            mine = nsrc * (unsigned long long)nt;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(total, mine);
+}
+
+struct KdeCtx {
+    KdePlan p; bool cells; KdeGrid g; int type, periodic, nsplit; bool clamp;
+    double wx, wy; float sfactor;
+    void *tgt, *tgt_sorted, *src, *src_sorted; const void *ssorted; const int32_t *sst;
+    double *partial, *dens, *bsum; int32_t *tperm, *tstart; unsigned long long *counter;
+};
+
+// validation, staging of the scaled coordinates, choice between all pairs and the cell list, binning
+static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, int type, int periodic,
+                     const float *box6, float sigma, double cutoff_sigmas, void *ws, size_t ws_bytes, cudaStream_t s, KdeCtx &c) {
+    MS_REQUIRE(type == 2 || type == 3, "ms_kde: invalid density type %d (should be 2 (2D) or 3 (3D); geodesic type 1 is not on the GPU path)", type);
+    MS_REQUIRE(nv > 0 && nids >= 0 && sigma > 0.0f, "ms_kde: bad arguments nv=%lld nids=%lld sigma=%g", (long long)nv, (long long)nids, (double)sigma);
+    MS_REQUIRE(nv < ((int64_t)1 << 31) && nids < ((int64_t)1 << 31), "ms_kde: too many points");
+    MS_REQUIRE(!periodic || box6 != NULL, "ms_kde: periodic KDE needs the 6-float bbox");
+    MS_REQUIRE(ws_bytes >= ms_kde_workspace_bytes(nv, nids), "ms_kde: workspace too small");
+    const KdePlan p = kde_plan(nv, nids);
+    c.p = p; c.type = type; c.periodic = periodic;
+    if (nids == 0) ids = NULL;
+    // constants rounded through float32 exactly as DensityKernels.hpp:47-48 stores them
+    const double sg = (double)sigma;
+    const float efactor = (float)(-1.0 / (2.0 * sg * sg));
+    c.sfactor = type == 3 ? (float)(1.0 / pow(sqrt(2.0 * M_PI) * sg, 3.0)) : (float)(1.0 / (2.0 * M_PI * sg * sg));
+    const double scale = sqrt(-(double)efactor * 1.4426950408889634074 * (double)KDE_TAB);
+    double wx = 0.0, wy = 0.0;
+    if (box6) {      // float32 widths as DistanceKernels.hpp:46-68 forms them
+        wx = (double)(float)(box6[3] - box6[0]) * scale; wy = (double)(float)(box6[4] - box6[1]) * scale;
+    }
+    MS_REQUIRE(!periodic || (wx > 0.0 && wy > 0.0), "ms_kde: periodic bbox has no extent");
+    c.wx = wx; c.wy = wy;
+    MsArena A(ws, ws_bytes);
+    const size_t nc = (size_t)kde_max_cells(nv) + 2;
+    void *tgt = A.take<char>((size_t)nv * 32), *tgt_sorted = A.take<char>((size_t)nv * 32);
+    void *src = A.take<char>((size_t)p.ns * 32), *src_sorted = A.take<char>((size_t)p.ns * 32);
+    c.partial = A.take<double>((size_t)p.nsplit * nv); c.dens = A.take<double>(nv);
+    c.bsum = A.take<double>(nv / RED_T + 2);
+    int32_t *tcell = A.take<int32_t>(nv), *tperm = A.take<int32_t>(nv), *scell = A.take<int32_t>(p.ns), *sperm = A.take<int32_t>(p.ns);
+    int32_t *cnt = A.take<int32_t>(nc), *cursor = A.take<int32_t>(nc), *tstart = A.take<int32_t>(nc), *sstart = A.take<int32_t>(nc);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes((int64_t)nc));
+    c.counter = (unsigned long long*)A.take<unsigned long long>(4);
+
+    MS_K("kde_stage", s);
+    if (type == 2) k_kde_stage<2><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, NULL, nv, scale, (double2*)tgt);
+    else           k_kde_stage<3><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, NULL, nv, scale, (double4*)tgt);
+    if (ids) {
+        MS_K("kde_stage", s);
+        if (type == 2) k_kde_stage<2><<<ms_blocks(p.ns, 256), 256, 0, s>>>(verts, ids, p.ns, scale, (double2*)src);
+        else           k_kde_stage<3><<<ms_blocks(p.ns, 256), 256, 0, s>>>(verts, ids, p.ns, scale, (double4*)src);
+    } else src = tgt;
+    MS_LAUNCH_CHECK();
+    c.tgt = tgt; c.src = src; c.tgt_sorted = tgt_sorted; c.src_sorted = src_sorted; c.tperm = tperm; c.tstart = tstart;
+
+    // ---- cell-list plan: needs the grid extent (box6); periodic grids must tile the period
+    bool cells = false; KdeGrid g; double rwin = 0.0;
+    if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
+        const double rcut = cutoff_sigmas * sg * scale;                      // scaled cut-off radius
+        double cs = rcut / 4.0;
+        const double cmin = sqrt(56.0 * wx * wy / (double)nv);               // ~56 targets per cell
+        if (cs < cmin) cs = cmin;
+        const double nxd = floor(wx / cs), nyd = floor(wy / cs);
+        if (nxd >= 1.0 && nyd >= 1.0 && nxd * nyd <= (double)kde_max_cells(nv)) {
+            const int ncx = (int)nxd, ncy = (int)nyd;
+            const double cxs = wx / ncx, cys = wy / ncy;
+            const int m = (int)ceil(rcut / (cxs < cys ? cxs : cys));
+            const bool fits = periodic ? (2 * m + 1 <= ncx && 2 * m + 1 <= ncy) : (ncx * ncy >= 4);
+            if (fits) {
+                cells = true;
+                g.b0x = (double)box6[0] * scale; g.b0y = (double)box6[1] * scale;
+                g.inv_cx = 1.0 / cxs; g.inv_cy = 1.0 / cys; g.wx = wx; g.wy = wy;
+                g.ncx = ncx; g.ncy = ncy; g.m = m; g.periodic = periodic ? 1 : 0;
+                rwin = (m + 1) * (m + 1) * (cxs * cxs + cys * cys);           // largest in-window xy distance^2
+            }
+        }
+    }
+    c.cells = cells; c.g = g; c.nsplit = cells ? 1 : p.nsplit;
+    if (cells) {
+        c.clamp = type == 3 || !periodic || !(rwin < KDE_RMAX);
+        int rc;
+        if (type == 2) rc = kde_bin<2>(tgt, nv, g, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
+        else           rc = kde_bin<3>(tgt, nv, g, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
+        if (rc) return rc;
+        c.ssorted = tgt_sorted; c.sst = tstart;
+        if (ids) {
+            if (type == 2) rc = kde_bin<2>(src, p.ns, g, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+            else           rc = kde_bin<3>(src, p.ns, g, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+            if (rc) return rc;
+            c.ssorted = src_sorted; c.sst = sstart;
+        }
+    } else {
+        // r = scaled distance^2 must stay below 2^31 for the integer split of the exponent: periodic 2-D
+        // pairs are bounded by the half box (checked here), everything else clamps in the kernel
+        c.clamp = type == 3 || !periodic || !(0.25 * (wx * wx + wy * wy) < KDE_RMAX);
+    }
     return 0;
 }
 
@@ -239,35 +571,54 @@ extern "C" int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_
                       double cutoff_sigmas, double *density_f64, float *density_f32,
                       void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(type == 2 || type == 3, "ms_kde: invalid density type %d (should be 2 (2D) or 3 (3D); geodesic type 1 is not on the GPU path)", type);
-    MS_REQUIRE(nv > 0 && nids >= 0 && sigma > 0.0f, "ms_kde: bad arguments nv=%lld nids=%lld sigma=%g", (long long)nv, (long long)nids, (double)sigma);
-    MS_REQUIRE(!periodic || box6 != NULL, "ms_kde: periodic KDE needs the 6-float bbox");
-    MS_REQUIRE(!(cutoff_sigmas > 0.0), "ms_kde: cut-off variant not built yet; pass cutoff_sigmas <= 0");
-    MS_REQUIRE(ws_bytes >= ms_kde_workspace_bytes(nv, nids), "ms_kde: workspace too small");
-    const KdePlan p = kde_plan(nv, nids);
-    // constants rounded through float32 exactly as DensityKernels.hpp:47-48 stores them
-    const double sg = (double)sigma;
-    const float efactor = (float)(-1.0 / (2.0 * sg * sg));
-    const float sfactor = type == 3 ? (float)(1.0 / pow(sqrt(2.0 * M_PI) * sg, 3.0)) : (float)(1.0 / (2.0 * M_PI * sg * sg));
-    const double scale = sqrt(-(double)efactor * 1.4426950408889634074);
-    double wx = 0.0, wy = 0.0;
-    if (periodic) { wx = (double)(float)(box6[3] - box6[0]) * scale; wy = (double)(float)(box6[4] - box6[1]) * scale; }
-    MsArena A(ws, ws_bytes);
-    void *tgt = A.take<char>((size_t)nv * 32), *src = A.take<char>((size_t)p.ns_pad * 32);
-    double *partial = A.take<double>((size_t)p.nsplit * nv), *dens = A.take<double>(nv);
-    double *bsum = A.take<double>(nv / RED_T + 2);
-    int rc;
-    if (type == 2) rc = periodic ? kde_run<2, true>(verts, nv, nids > 0 ? ids : NULL, p, scale, wx, wy, tgt, src, partial, s)
-                                 : kde_run<2, false>(verts, nv, nids > 0 ? ids : NULL, p, scale, wx, wy, tgt, src, partial, s);
-    else           rc = periodic ? kde_run<3, true>(verts, nv, nids > 0 ? ids : NULL, p, scale, wx, wy, tgt, src, partial, s)
-                                 : kde_run<3, false>(verts, nv, nids > 0 ? ids : NULL, p, scale, wx, wy, tgt, src, partial, s);
+    KdeCtx c;
+    int rc = kde_front(verts, nv, ids, nids, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
+    const KdePlan &p = c.p;
+    if (c.cells) {
+        const int ncell = c.g.ncx * c.g.ncy;
+        MS_K("kde_cells", s);
+        if (type == 2) {
+            if (c.clamp) k_kde_cells<2, true><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.g, c.partial);
+            else         k_kde_cells<2, false><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.g, c.partial);
+        } else           k_kde_cells<3, true><<<ncell, CELL_T, 0, s>>>((const double4*)c.tgt_sorted, c.tstart, c.tperm, (const double4*)c.ssorted, c.sst, c.g, c.partial);
+        MS_LAUNCH_CHECK();
+    } else {
+        if (type == 2) {
+            if (periodic) rc = c.clamp ? kde_run_pairs<2, true, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s)
+                                       : kde_run_pairs<2, true, false>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
+            else          rc = kde_run_pairs<2, false, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
+        } else            rc = periodic ? kde_run_pairs<3, true, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s)
+                                        : kde_run_pairs<3, false, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
+        if (rc) return rc;
+    }
     const int nb = ms_blocks(nv, RED_T);
-    MS_K("kde_combine", s); k_kde_combine<<<nb, RED_T, 0, s>>>(partial, nv, p.nsplit, (double)sfactor * (1.0 / (double)nv), dens, bsum);
-    double *total = bsum + nb;
-    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(bsum, nb, total); }
-    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(dens, nv, get_counts ? total : NULL, (double)p.ns, density_f64, density_f32);
+    MS_K("kde_combine", s); k_kde_combine<<<nb, RED_T, 0, s>>>(c.partial, nv, c.nsplit, (double)c.sfactor * (1.0 / (double)nv), c.dens, c.bsum);
+    double *total = c.bsum + nb;
+    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(c.bsum, nb, total); }
+    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(c.dens, nv, get_counts ? total : NULL, (double)p.ns, density_f64, density_f32);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+                                      int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                                      double *pairs, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(pairs != NULL, "ms_kde_evaluated_pairs: need an output");
+    KdeCtx c;
+    int rc = kde_front(verts, nv, ids, nids, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
+    if (rc) return rc;
+    if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); *pairs = (double)nv * (double)c.p.ns; return 0; }
+    MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
+    const int ncell = c.g.ncx * c.g.ncy;
+    MS_K("kde_cells_count", s); k_kde_cells_count<0><<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.g, c.counter);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    unsigned long long h = 0ull;
+    MS_CUDA(cudaMemcpyAsync(&h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *pairs = (double)h;
     return 0;
 }

@@ -101,12 +101,7 @@ class LeafletFrame(object):
         if out is None:
             out = self.densities[name] = (torch.empty(self.nv, dtype=torch.float64, device=self.device),
                                           torch.empty(self.nv, dtype=torch.float32, device=self.device))
-        box = None
-        if self.periodic:
-            b = self.bboxl
-            if b.shape[0] == 4:
-                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
-            box = _lib.box6(b)
+        box = self._box(cutoff_sigmas)
         _lib.check(L.ms_kde(self.kverts.data_ptr(), self.nv, _lib.ptr(ids_dev) if nids else None, nids, int(type),
                             int(self.periodic), box, float(sigma), int(bool(get_nlipids)), float(cutoff_sigmas),
                             out[0].data_ptr(), out[1].data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(),
@@ -125,6 +120,36 @@ class LeafletFrame(object):
         self.run_pnormals(knbrs)
         self.run_properties()
         self.run_densities(sigmas, cutoff_sigmas=cutoff_sigmas)
+
+    def _box(self, cutoff_sigmas):
+        if self.periodic:
+            b = self.bboxl
+            if b.shape[0] == 4:
+                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
+            return _lib.box6(b)
+        if cutoff_sigmas > 0:
+            v = self.mesh.vertices
+            lo, hi = v.min(axis=0), v.max(axis=0)
+            return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
+        return None
+
+    def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0):
+        """Pairs the KDE kernels actually evaluate in run_densities (diagnostic; synchronises)."""
+        import ctypes as C
+        L = _lib.lib()
+        total = 0.0
+        out = C.c_double(0)
+        for t in types:
+            for s in sigmas:
+                for ids in [None] + list(self.label_ids.values()):
+                    nids = 0 if ids is None else int(ids.numel())
+                    _lib.check(L.ms_kde_evaluated_pairs(self.kverts.data_ptr(), self.nv, _lib.ptr(ids) if nids else None, nids,
+                                                        int(t), int(self.periodic), self._box(cutoff_sigmas), float(s),
+                                                        float(cutoff_sigmas), C.byref(out), self.kde_ws.data_ptr(),
+                                                        self.kde_ws.numel(), _lib.stream_ptr(self.device)),
+                               'ms_kde_evaluated_pairs')
+                    total += out.value
+        return total
 
     def pairs_per_run(self, sigmas, types=(2,)):
         """All-pairs-equivalent KDE pair count of run_densities."""

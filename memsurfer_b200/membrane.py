@@ -63,6 +63,13 @@ def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1
 class Membrane(object):
     """Create and analyse membrane surfaces (GPU hot path, host surface producer)."""
 
+    # KDE cut-off in sigmas used by compute_density / compute_densities.  The reference sums all
+    # V x n_ids pairs (TriMesh_kde.cpp:344-392); beyond 8 sigma a Gaussian term is below
+    # exp(-32) = 1.3e-14 of the peak, three orders under the 1e-9 parity bar, so the default skips
+    # those pairs through a cell list (the C ABI falls back to all pairs when the window does not
+    # fit the box).  Set to 0 for the reference's full sum.
+    KDE_CUTOFF_SIGMAS = 8.0
+
     def __init__(self, points, **kwargs):
         points = np.asarray(points)
         if points.ndim != 2 or points.shape[1] != 3:
@@ -189,7 +196,9 @@ class Membrane(object):
         mesh.compute_pointareas()
         mesh.compute_curvatures()
 
-    def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=0.0):
+    def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=None):
+        if cutoff_sigmas is None:
+            cutoff_sigmas = self.KDE_CUTOFF_SIGMAS
         if type < 1 or type > 3:
             raise ValueError(f'Invalid density type, {type}. Should be 1 (geodesic), 2 (2D) or 3 (3D)')
         if len(labels) == 0:

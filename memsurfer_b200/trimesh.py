@@ -279,6 +279,10 @@ class TriMesh(object):
             if b.shape[0] == 4:
                 b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
             box = _lib.box6(b)
+        elif cutoff_sigmas > 0:
+            # non-periodic cut-off: the cell list only needs the extent of the vertices
+            lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
+            box = _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
         _lib.check(L.ms_kde(d['kverts'].data_ptr(), nv, _lib.ptr(pidxs_dev) if nids else None, nids,
                             int(type), int(bool(self.periodic)), box, float(sigma), int(bool(get_nlipids)),
                             float(cutoff_sigmas), o64.data_ptr(), o32.data_ptr(),

@@ -110,6 +110,49 @@ def test_kde_vs_oracle(oracle, leaflet, typ, periodic, get_counts):
                 assert abs(mesh.attributes_f64[name].sum() - (len(ids) or pts.shape[0])) < 1e-6
 
 
+@pytest.mark.parametrize("typ", [2, 3])
+@pytest.mark.parametrize("periodic", [True, False])
+def test_kde_cutoff_cell_list_vs_oracle(oracle, leaflet, typ, periodic):
+    """Cut-off (cell list) variant against the oracle's ALL-PAIRS sum: the dropped tail is below
+    exp(-7^2/2) = 2.3e-11 relative, far inside the 1e-9 bar."""
+    from memsurfer_b200 import TriMesh
+    pts, labels, bbox = leaflet
+    mesh = TriMesh(pts, periodic=periodic)
+    bb = np.concatenate([pts.min(0), pts.max(0)]).astype(np.float32)
+    if periodic:
+        mesh.set_bbox(bb[:3], bb[3:])
+    for sigma in (10.0, 25.0, 40.0):
+        for ids in (np.empty([0]), np.where(labels == 1)[0], np.array([17, 4000])):
+            name = f"c{sigma}_{len(ids)}"
+            mesh.compute_density(typ, sigma, name, False, ids, cutoff_sigmas=7.0)
+            want = oracle.kde(pts, ids.astype(np.int32), typ, sigma, False, bb if periodic else None)
+            got = mesh.attributes_f64[name]
+            scale = want.max()
+            err = np.abs(got - want)
+            assert (err <= 1e-12 * scale + 1e-9 * want + 3e-11 * scale).all(), \
+                f"type {typ} periodic {periodic} sigma {sigma} nids {len(ids)}: max err {err.max()} (scale {scale})"
+            if len(ids) != 2:
+                assert close(got, want)[0]
+
+
+def test_kde_cutoff_matches_all_pairs_at_full_size():
+    """BASELINE configs[2] leaflet size (499 849 vertices): cell list vs the all-pairs kernel."""
+    from memsurfer_b200 import TriMesh, synth
+    pts, labels, bbox = synth.make_leaflet(500000, seed=1234, ntypes=3, fractions=[0.4, 0.3, 0.3])
+    mesh = TriMesh(pts, periodic=True)
+    bb = np.concatenate([pts.min(0), pts.max(0)]).astype(np.float32)
+    mesh.set_bbox(bb[:3], bb[3:])
+    ids = np.where(labels == 2)[0]
+    for sigma, sel, nm in ((10.0, np.empty([0]), "a"), (40.0, ids, "b")):
+        full = mesh.compute_density(2, sigma, nm + "_full", True, sel) * 1.0
+        f64 = mesh.attributes_f64[nm + "_full"]
+        mesh.compute_density(2, sigma, nm + "_cut", True, sel, cutoff_sigmas=7.0)
+        c64 = mesh.attributes_f64[nm + "_cut"]
+        ok, err = close(c64, f64)
+        assert ok, f"sigma {sigma}: max abs err {err}"
+        assert abs(c64.sum() - (len(sel) or pts.shape[0])) < 1e-5
+
+
 def test_kde_large_register_blocked_path(oracle):
     """V >= 148*1024 targets takes the R=4 register-blocked kernel; oracle on a target subset."""
     from memsurfer_b200 import TriMesh, synth
