@@ -115,10 +115,30 @@ int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
            double cutoff_sigmas, double *density_f64, float *density_f32,
            void *ws, size_t ws_bytes, void *stream);
 
-/* Diagnostic (roofline accounting): the number of pairs ms_kde evaluates for the same arguments --
- * nv*n_ids for the all-pairs kernel, the sum over cells of targets x window sources for the cell
- * list.  *pairs is a host double.  Syncs the stream.                                            */
+/* Label-fused KDE.  Membrane.compute_densities (membrane.py:289-297) asks for one field per lipid
+ * type plus 'all' (examples/ex_3lipid.py:169-175); the reference runs kde() once per field, i.e.
+ * every vertex pair is evaluated twice.  ms_kde_labels evaluates each pair once and keeps the sums
+ * apart by the SOURCE's label: labels (nv) i32 in [0, nlabels) (negative: not a source),
+ * raw (nlabels, nv) f64 with raw[l*nv + j] = sfactor * sum_{i: labels[i]==l} exp(efactor*dist2(v_i, v_j))
+ * (TriMesh_kde.cpp:344-392 before its normalisations).  nlabels <= 64.                           */
+size_t ms_kde_labels_workspace_bytes(int64_t nv, int nlabels);
+int ms_kde_labels(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                  int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                  double *raw, void *ws, size_t ws_bytes, void *stream);
+/* The normalisations of TriMesh::kde (TriMesh_kde.cpp:504-524) for the union of the labels with
+ * select[l] != 0 (host, nlabels bytes): density = sum_l raw[l] / nv; get_counts: * n_selected /
+ * sum(density), n_selected = number of source vertices of the selected labels.                  */
+size_t ms_kde_select_workspace_bytes(int64_t nv);
+int ms_kde_select(const double *raw, int64_t nv, int nlabels, const uint8_t *select, double n_selected,
+                  int get_counts, double *density_f64, float *density_f32,
+                  void *ws, size_t ws_bytes, void *stream);
+
+/* Diagnostic (roofline accounting): the number of pairs ms_kde (labels == NULL) or ms_kde_labels
+ * evaluates for the same arguments -- nv*n_sources for the all-pairs kernel, the sum over cells of
+ * targets x window sources for the cell list.  *pairs is a host double; ws sized by the matching
+ * *_workspace_bytes.  Syncs the stream.                                                          */
 int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+                           const int32_t *labels, int nlabels,
                            int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                            double *pairs, void *ws, size_t ws_bytes, void *stream);
 

@@ -192,20 +192,24 @@ __device__ __forceinline__ int kde_cell_of(const KdeGrid &g, const typename SrcT
     return cy * g.ncx + cx;
 }
 
+// bin id of every point: cell (labels == NULL) or label*ncell + cell; points with a negative label
+// are no sources (bin -1)
 template <int DIM>
 __global__ void __launch_bounds__(256) k_kde_cell_count(const typename SrcT<DIM>::type *__restrict__ pts, int64_t n, KdeGrid g,
-                                                        int32_t *cell, int32_t *cnt) {
+                                                        const int32_t *__restrict__ labels, int nlabels, int32_t *cell, int32_t *cnt) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int c = kde_cell_of<DIM>(g, pts[i]);
-    cell[i] = c; atomicAdd(cnt + c, 1);
+    int c = kde_cell_of<DIM>(g, pts[i]);
+    if (labels) { const int l = __ldg(labels + i); c = (l >= 0 && l < nlabels) ? l * (g.ncx * g.ncy) + c : -1; }
+    cell[i] = c;
+    if (c >= 0) atomicAdd(cnt + c, 1);
 }
 __global__ void __launch_bounds__(256) k_kde_cell_scatter(int64_t n, const int32_t *__restrict__ cell, const int32_t *__restrict__ start,
                                                           int32_t *cursor, int32_t *perm) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int c = cell[i];
-    perm[start[c] + atomicAdd(cursor + c, 1)] = (int32_t)i;
+    if (c >= 0) perm[start[c] + atomicAdd(cursor + c, 1)] = (int32_t)i;
 }
 // ascending element order inside every cell => the summation order (and the result) is reproducible.
 // One warp per cell: every lane ranks its elements against the whole cell (counting sort by
@@ -216,7 +220,7 @@ __global__ void __launch_bounds__(128) k_kde_cell_sort(int ncell, const int32_t 
     if (c >= ncell) return;
     const int b = start[c], e = start[c + 1], n = e - b;
     if (n <= 1) return;
-    if (n > 32 * SORT_K) {
+    if (n > 32 * SORT_K) {            // crowded cell (strongly clustered input): serial insertion sort, correct but slow
         if (lane == 0)
             for (int i = b + 1; i < e; i++) {
                 const int32_t key = perm[i]; int j = i - 1;
@@ -248,9 +252,10 @@ __global__ void __launch_bounds__(128) k_kde_cell_sort(int ncell, const int32_t 
 // that its coordinates agree with the cell it was binned into
 template <int DIM>
 __global__ void __launch_bounds__(256) k_kde_cell_gather(const typename SrcT<DIM>::type *__restrict__ pts, int64_t n, KdeGrid g,
-                                                         const int32_t *__restrict__ perm, typename SrcT<DIM>::type *sorted) {
+                                                         const int32_t *__restrict__ nbinned, const int32_t *__restrict__ perm,
+                                                         typename SrcT<DIM>::type *sorted) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= n || i >= (int64_t)__ldg(nbinned)) return;
     typename SrcT<DIM>::type p = pts[perm[i]];
     if (g.periodic) {
         const int cx = (int)floor((p.x - g.b0x) * g.inv_cx), cy = (int)floor((p.y - g.b0y) * g.inv_cy);
@@ -291,13 +296,15 @@ __device__ __forceinline__ bool kde_window_next(KdeWindow &w, const KdeGrid &g, 
     }
 }
 
-// One CTA per target cell; 64 threads x 2 register targets (chunks of 128 targets).
+// One CTA per target cell; 64 threads x 2 register targets (chunks of 128 targets).  The sources are
+// sorted by (label, cell): sstart holds nlabels*ncell+1 offsets and out[l*out_stride + vertex] receives
+// the sum over the sources of label l (nlabels == 1: a plain source set).
 #define CELL_T 64
 template <int DIM, bool CLAMP>
 __global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::type *__restrict__ tgt, const int32_t *__restrict__ tstart,
                                                       const int32_t *__restrict__ tperm,
-                                                      const typename SrcT<DIM>::type *__restrict__ src, const int32_t *__restrict__ sstart,
-                                                      KdeGrid g, double *__restrict__ out) {
+                                                      const typename SrcT<DIM>::type *__restrict__ src, const int32_t *__restrict__ sstart_all,
+                                                      int nlabels, int64_t out_stride, KdeGrid g, double *__restrict__ out_all) {
     typedef typename SrcT<DIM>::type S;
     constexpr int CAP = CELL_STAGE_BYTES / (int)sizeof(S);
     __shared__ __align__(128) S buf[2][CAP];
@@ -312,7 +319,11 @@ __global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::
     __syncthreads();
     uint32_t phase = 0u;                  // bit s = parity to wait for on stage s
     int stage = 0;
-    for (int c0 = t0; c0 < t1; c0 += CELL_T * 2) {
+    const int ncell = g.ncx * g.ncy;
+    for (int c0 = t0; c0 < t1; c0 += CELL_T * 2)
+    for (int lab = 0; lab < nlabels; lab++) {
+        const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
+        double *__restrict__ out = out_all + (size_t)lab * out_stride;
         double tx[2], ty[2], tz[2], acc[2];
 #pragma unroll
         for (int r = 0; r < 2; r++) {
@@ -392,11 +403,48 @@ __global__ void __launch_bounds__(256) k_kde_emit(const double *__restrict__ den
     if (o32) o32[j] = (float)d;
 }
 
+__global__ void __launch_bounds__(256) k_kde_scale(double *x, int64_t n, double f) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] *= f;
+}
+
+// stable partition by label (all-pairs, label-fused): flag -> exclusive scan -> scatter, one label at a time
+__global__ void __launch_bounds__(256) k_kde_label_flag(const int32_t *__restrict__ labels, int64_t n, int l, int32_t *flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = __ldg(labels + i) == l;
+}
+__global__ void __launch_bounds__(256) k_kde_label_scatter(const int32_t *__restrict__ labels, int64_t n, int l, const int32_t *__restrict__ pos,
+                                                           int32_t *start, int32_t *perm) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int base = start[l];
+    if (__ldg(labels + i) == l) perm[base + pos[i]] = (int32_t)i;
+    if (i == 0) start[l + 1] = base + pos[n];
+}
+
+// ------------------------------------------------------------------ label-fused normalisation
+// dens[j] = factor * sum_{l in mask} raw[l*nv + j]  (+ block sums for the get_counts total)
+__global__ void __launch_bounds__(RED_T) k_kde_select(const double *__restrict__ raw, int64_t nv, int nlabels, unsigned long long mask,
+                                                      double factor, double *__restrict__ dens, double *__restrict__ bsum) {
+    __shared__ double sm[RED_T];
+    const int64_t j = (int64_t)blockIdx.x * RED_T + threadIdx.x;
+    double d = 0.0;
+    if (j < nv) {
+        for (int l = 0; l < nlabels; l++) if ((mask >> l) & 1ull) d += raw[(size_t)l * nv + j];
+        d *= factor;
+        dens[j] = d;
+    }
+    sm[threadIdx.x] = d;
+    __syncthreads();
+    for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) bsum[blockIdx.x] = sm[0];
+}
+
 // ------------------------------------------------------------------ host side
 struct KdePlan { int64_t ns; int threads, R, nsplit; int64_t blocks_x; };
-static KdePlan kde_plan(int64_t nv, int64_t nids) {
+static KdePlan kde_plan(int64_t nv, int64_t ns) {
     KdePlan p;
-    p.ns = nids > 0 ? nids : nv;
+    p.ns = ns;
     const bool big = nv >= (int64_t)MS_SM_COUNT * 128 * 4 * 2;
     p.threads = big ? 128 : 64; p.R = big ? 4 : 1;
     p.blocks_x = (nv + p.threads * p.R - 1) / (p.threads * p.R);
@@ -409,20 +457,23 @@ static KdePlan kde_plan(int64_t nv, int64_t nids) {
     return p;
 }
 static int64_t kde_max_cells(int64_t nv) { return nv / 16 + 4096; }
+#define KDE_MAX_LABELS 64
 
-extern "C" size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids) {
-    const KdePlan p = kde_plan(nv, nids);
-    const size_t nc = (size_t)kde_max_cells(nv) + 2;
-    return 2 * ms_align((size_t)nv * 32) + 2 * ms_align((size_t)p.ns * 32)       // staged + cell-sorted targets, sources
+static size_t kde_ws_bytes(int64_t nv, int64_t ns, int nlabels) {
+    const KdePlan p = kde_plan(nv, ns);
+    const size_t nc = (size_t)kde_max_cells(nv) * (size_t)nlabels + 2;
+    return 2 * ms_align((size_t)nv * 32) + 2 * ms_align((size_t)ns * 32)         // staged + cell-sorted targets, sources
          + ms_align((size_t)p.nsplit * nv * 8) + ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8)
-         + 2 * ms_align((size_t)nv * 4) + 2 * ms_align((size_t)p.ns * 4)         // cell ids, permutations
+         + 2 * ms_align((size_t)(nv + 1) * 4) + 2 * ms_align((size_t)(ns + 1) * 4) // bin ids, permutations
          + 4 * ms_align(nc * 4) + ms_scan_ws_bytes((int64_t)nc) + 8192;
 }
+extern "C" size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids) { return kde_ws_bytes(nv, nids > 0 ? nids : nv, 1); }
+extern "C" size_t ms_kde_labels_workspace_bytes(int64_t nv, int nlabels) { return kde_ws_bytes(nv, nv, nlabels < 1 ? 1 : nlabels); }
 
 template <int DIM, bool PER, bool CLAMP>
-static int kde_run_pairs(const KdePlan &p, int64_t nv, double wx, double wy, void *tgt_, void *src_, double *partial, cudaStream_t s) {
+static int kde_run_pairs(const KdePlan &p, int64_t nv, double wx, double wy, const void *tgt_, const void *src_, double *partial, cudaStream_t s) {
     typedef typename SrcT<DIM>::type S;
-    S *tgt = (S*)tgt_, *src = (S*)src_;
+    const S *tgt = (const S*)tgt_, *src = (const S*)src_;
     const int tile = KDE_STAGE_BYTES / (int)sizeof(S);
     const int ntiles = (int)((p.ns + tile - 1) / tile);
     const int tps = (ntiles + p.nsplit - 1) / p.nsplit;
@@ -433,37 +484,51 @@ static int kde_run_pairs(const KdePlan &p, int64_t nv, double wx, double wy, voi
     MS_LAUNCH_CHECK();
     return 0;
 }
+static int kde_pairs_dispatch(int type, int periodic, bool clamp, const KdePlan &p, int64_t nv, double wx, double wy,
+                              const void *tgt, const void *src, double *partial, cudaStream_t s) {
+    if (type == 2) {
+        if (periodic) return clamp ? kde_run_pairs<2, true, true>(p, nv, wx, wy, tgt, src, partial, s)
+                                   : kde_run_pairs<2, true, false>(p, nv, wx, wy, tgt, src, partial, s);
+        return kde_run_pairs<2, false, true>(p, nv, wx, wy, tgt, src, partial, s);
+    }
+    return periodic ? kde_run_pairs<3, true, true>(p, nv, wx, wy, tgt, src, partial, s)
+                    : kde_run_pairs<3, false, true>(p, nv, wx, wy, tgt, src, partial, s);
+}
 
-// cell-sort n staged points: start (ncell+1), perm (n), sorted (n)
+// sort n staged points into bins (cell, or label*ncell + cell): start (nbins+1), perm, sorted
 template <int DIM>
-static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, int32_t *cell, int32_t *cnt, int32_t *cursor,
-                   int32_t *start, int32_t *perm, void *sorted_, void *scan_ws, cudaStream_t s) {
+static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, const int32_t *labels, int nlabels, int32_t *cell, int32_t *cnt,
+                   int32_t *cursor, int32_t *start, int32_t *perm, void *sorted_, void *scan_ws, cudaStream_t s) {
     typedef typename SrcT<DIM>::type S;
     const S *pts = (const S*)pts_; S *sorted = (S*)sorted_;
-    const int ncell = g.ncx * g.ncy;
-    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_K("kde_cell_count", s); k_kde_cell_count<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, cell, cnt);
-    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
+    const int nbins = g.ncx * g.ncy * (labels ? nlabels : 1);
+    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (nbins + 1), s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (nbins + 1), s));
+    MS_K("kde_cell_count", s); k_kde_cell_count<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, labels, nlabels, cell, cnt);
+    if (ms_exclusive_scan_i32(cnt, start, nbins, scan_ws, s)) return 2;
     MS_K("kde_cell_scatter", s); k_kde_cell_scatter<<<ms_blocks(n, 256), 256, 0, s>>>(n, cell, start, cursor, perm);
-    MS_K("kde_cell_sort", s); k_kde_cell_sort<<<ms_blocks((int64_t)ncell * 32, 128), 128, 0, s>>>(ncell, start, perm);
-    MS_K("kde_cell_gather", s); k_kde_cell_gather<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, perm, sorted);
+    MS_K("kde_cell_sort", s); k_kde_cell_sort<<<ms_blocks((int64_t)nbins * 32, 128), 128, 0, s>>>(nbins, start, perm);
+    MS_K("kde_cell_gather", s); k_kde_cell_gather<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, start + nbins, perm, sorted);
     MS_LAUNCH_CHECK();
     return 0;
 }
 
-// pairs the cell-list kernel evaluates: sum over cells of (#targets) x (#sources in the window)
-template <int DUMMY>
-__global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart,
-                                                         KdeGrid g, unsigned long long *total) {
+// pairs the cell-list kernel evaluates: sum over cells of (#targets) x (#sources of every label in the window)
+__global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart_all,
+                                                         int nlabels, KdeGrid g, unsigned long long *total) {
     const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ncell = g.ncx * g.ncy;
     unsigned long long mine = 0ull;
-    if (cell < g.ncx * g.ncy) {
+    if (cell < ncell) {
         const int nt = tstart[cell + 1] - tstart[cell];
         if (nt > 0) {
-            KdeWindow w; kde_window_init(w, g);
-            int off, cnt; double shx, shy; unsigned long long nsrc = 0ull;
-            while (kde_window_next(w, g, cell % g.ncx, cell / g.ncx, sstart, 1 << 30, off, cnt, shx, shy)) nsrc += (unsigned long long)cnt;
+            unsigned long long nsrc = 0ull;
+            for (int l = 0; l < nlabels; l++) {
+                KdeWindow w; kde_window_init(w, g);
+                int off, cnt; double shx, shy;
+                while (kde_window_next(w, g, cell % g.ncx, cell / g.ncx, sstart_all + (size_t)l * ncell, 1 << 30, off, cnt, shx, shy))
+                    nsrc += (unsigned long long)cnt;
+            }
             mine = nsrc * (unsigned long long)nt;
         }
     }
@@ -472,23 +537,28 @@ __global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restri
 }
 
 struct KdeCtx {
-    KdePlan p; bool cells; KdeGrid g; int type, periodic, nsplit; bool clamp;
+    KdePlan p; bool cells; KdeGrid g; int type, periodic, nsplit, nlabels; bool clamp;
     double wx, wy; float sfactor;
     void *tgt, *tgt_sorted, *src, *src_sorted; const void *ssorted; const int32_t *sst;
-    double *partial, *dens, *bsum; int32_t *tperm, *tstart; unsigned long long *counter;
+    double *partial, *dens, *bsum; int32_t *tperm, *tstart, *sstart; unsigned long long *counter;
 };
 
-// validation, staging of the scaled coordinates, choice between all pairs and the cell list, binning
-static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, int type, int periodic,
-                     const float *box6, float sigma, double cutoff_sigmas, void *ws, size_t ws_bytes, cudaStream_t s, KdeCtx &c) {
+// validation, staging of the scaled coordinates, choice between all pairs and the cell list, binning.
+// Sources: ids (nids > 0), every vertex (ids == NULL, labels == NULL), or every vertex grouped by label.
+static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, const int32_t *labels, int nlabels,
+                     int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                     void *ws, size_t ws_bytes, cudaStream_t s, KdeCtx &c) {
     MS_REQUIRE(type == 2 || type == 3, "ms_kde: invalid density type %d (should be 2 (2D) or 3 (3D); geodesic type 1 is not on the GPU path)", type);
     MS_REQUIRE(nv > 0 && nids >= 0 && sigma > 0.0f, "ms_kde: bad arguments nv=%lld nids=%lld sigma=%g", (long long)nv, (long long)nids, (double)sigma);
     MS_REQUIRE(nv < ((int64_t)1 << 31) && nids < ((int64_t)1 << 31), "ms_kde: too many points");
     MS_REQUIRE(!periodic || box6 != NULL, "ms_kde: periodic KDE needs the 6-float bbox");
-    MS_REQUIRE(ws_bytes >= ms_kde_workspace_bytes(nv, nids), "ms_kde: workspace too small");
-    const KdePlan p = kde_plan(nv, nids);
-    c.p = p; c.type = type; c.periodic = periodic;
+    MS_REQUIRE(!labels || (nlabels >= 1 && nlabels <= KDE_MAX_LABELS), "ms_kde_labels: need 1 <= nlabels <= %d", KDE_MAX_LABELS);
     if (nids == 0) ids = NULL;
+    if (!labels) nlabels = 1;
+    const int64_t ns = ids ? nids : nv;
+    MS_REQUIRE(ws_bytes >= kde_ws_bytes(nv, ns, nlabels), "ms_kde: workspace too small");
+    const KdePlan p = kde_plan(nv, ns);
+    c.p = p; c.type = type; c.periodic = periodic; c.nlabels = nlabels;
     // constants rounded through float32 exactly as DensityKernels.hpp:47-48 stores them
     const double sg = (double)sigma;
     const float efactor = (float)(-1.0 / (2.0 * sg * sg));
@@ -501,12 +571,12 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
     MS_REQUIRE(!periodic || (wx > 0.0 && wy > 0.0), "ms_kde: periodic bbox has no extent");
     c.wx = wx; c.wy = wy;
     MsArena A(ws, ws_bytes);
-    const size_t nc = (size_t)kde_max_cells(nv) + 2;
+    const size_t nc = (size_t)kde_max_cells(nv) * (size_t)nlabels + 2;
     void *tgt = A.take<char>((size_t)nv * 32), *tgt_sorted = A.take<char>((size_t)nv * 32);
-    void *src = A.take<char>((size_t)p.ns * 32), *src_sorted = A.take<char>((size_t)p.ns * 32);
+    void *src = A.take<char>((size_t)ns * 32), *src_sorted = A.take<char>((size_t)ns * 32);
     c.partial = A.take<double>((size_t)p.nsplit * nv); c.dens = A.take<double>(nv);
     c.bsum = A.take<double>(nv / RED_T + 2);
-    int32_t *tcell = A.take<int32_t>(nv), *tperm = A.take<int32_t>(nv), *scell = A.take<int32_t>(p.ns), *sperm = A.take<int32_t>(p.ns);
+    int32_t *tcell = A.take<int32_t>(nv + 1), *tperm = A.take<int32_t>(nv), *scell = A.take<int32_t>(ns + 1), *sperm = A.take<int32_t>(ns);
     int32_t *cnt = A.take<int32_t>(nc), *cursor = A.take<int32_t>(nc), *tstart = A.take<int32_t>(nc), *sstart = A.take<int32_t>(nc);
     void *scan_ws = A.take<char>(ms_scan_ws_bytes((int64_t)nc));
     c.counter = (unsigned long long*)A.take<unsigned long long>(4);
@@ -516,14 +586,15 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
     else           k_kde_stage<3><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, NULL, nv, scale, (double4*)tgt);
     if (ids) {
         MS_K("kde_stage", s);
-        if (type == 2) k_kde_stage<2><<<ms_blocks(p.ns, 256), 256, 0, s>>>(verts, ids, p.ns, scale, (double2*)src);
-        else           k_kde_stage<3><<<ms_blocks(p.ns, 256), 256, 0, s>>>(verts, ids, p.ns, scale, (double4*)src);
+        if (type == 2) k_kde_stage<2><<<ms_blocks(ns, 256), 256, 0, s>>>(verts, ids, ns, scale, (double2*)src);
+        else           k_kde_stage<3><<<ms_blocks(ns, 256), 256, 0, s>>>(verts, ids, ns, scale, (double4*)src);
     } else src = tgt;
     MS_LAUNCH_CHECK();
-    c.tgt = tgt; c.src = src; c.tgt_sorted = tgt_sorted; c.src_sorted = src_sorted; c.tperm = tperm; c.tstart = tstart;
+    c.tgt = tgt; c.src = src; c.tgt_sorted = tgt_sorted; c.src_sorted = src_sorted; c.tperm = tperm; c.tstart = tstart; c.sstart = sstart;
 
     // ---- cell-list plan: needs the grid extent (box6); periodic grids must tile the period
     bool cells = false; KdeGrid g; double rwin = 0.0;
+    g.ncx = g.ncy = 1; g.m = 0; g.periodic = periodic ? 1 : 0; g.b0x = g.b0y = 0.0; g.inv_cx = g.inv_cy = 0.0; g.wx = wx; g.wy = wy;
     if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
         const double rcut = cutoff_sigmas * sg * scale;                      // scaled cut-off radius
         double cs = rcut / 4.0;
@@ -538,31 +609,59 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             if (fits) {
                 cells = true;
                 g.b0x = (double)box6[0] * scale; g.b0y = (double)box6[1] * scale;
-                g.inv_cx = 1.0 / cxs; g.inv_cy = 1.0 / cys; g.wx = wx; g.wy = wy;
-                g.ncx = ncx; g.ncy = ncy; g.m = m; g.periodic = periodic ? 1 : 0;
+                g.inv_cx = 1.0 / cxs; g.inv_cy = 1.0 / cys;
+                g.ncx = ncx; g.ncy = ncy; g.m = m;
                 rwin = (m + 1) * (m + 1) * (cxs * cxs + cys * cys);           // largest in-window xy distance^2
             }
         }
     }
-    c.cells = cells; c.g = g; c.nsplit = cells ? 1 : p.nsplit;
-    if (cells) {
-        c.clamp = type == 3 || !periodic || !(rwin < KDE_RMAX);
-        int rc;
-        if (type == 2) rc = kde_bin<2>(tgt, nv, g, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
-        else           rc = kde_bin<3>(tgt, nv, g, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
-        if (rc) return rc;
-        c.ssorted = tgt_sorted; c.sst = tstart;
-        if (ids) {
-            if (type == 2) rc = kde_bin<2>(src, p.ns, g, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
-            else           rc = kde_bin<3>(src, p.ns, g, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
-            if (rc) return rc;
-            c.ssorted = src_sorted; c.sst = sstart;
-        }
-    } else {
+    c.cells = cells; c.nsplit = cells ? 1 : p.nsplit;
+    if (!cells) {
         // r = scaled distance^2 must stay below 2^31 for the integer split of the exponent: periodic 2-D
         // pairs are bounded by the half box (checked here), everything else clamps in the kernel
         c.clamp = type == 3 || !periodic || !(0.25 * (wx * wx + wy * wy) < KDE_RMAX);
+        c.g = g;
+        if (!labels) return 0;
+        // all pairs per label: stable partition of the staged vertices by label (sstart = nlabels+1 offsets)
+        MS_CUDA(cudaMemsetAsync(sstart, 0, sizeof(int32_t), s));
+        for (int l = 0; l < nlabels; l++) {
+            MS_K("kde_label_flag", s); k_kde_label_flag<<<ms_blocks(nv, 256), 256, 0, s>>>(labels, nv, l, scell);
+            if (ms_exclusive_scan_i32(scell, tcell, nv, scan_ws, s)) return 2;      // tcell (nv+1 <= workspace slack) holds positions
+            MS_K("kde_label_scatter", s); k_kde_label_scatter<<<ms_blocks(nv, 256), 256, 0, s>>>(labels, nv, l, tcell, sstart, sperm);
+        }
+        KdeGrid g1 = g; g1.periodic = 0;
+        MS_K("kde_cell_gather", s);
+        if (type == 2) k_kde_cell_gather<2><<<ms_blocks(nv, 256), 256, 0, s>>>((const double2*)src, nv, g1, sstart + nlabels, sperm, (double2*)src_sorted);
+        else           k_kde_cell_gather<3><<<ms_blocks(nv, 256), 256, 0, s>>>((const double4*)src, nv, g1, sstart + nlabels, sperm, (double4*)src_sorted);
+        MS_LAUNCH_CHECK();
+        c.ssorted = src_sorted; c.sst = sstart;
+        return 0;
+    } else c.clamp = type == 3 || !periodic || !(rwin < KDE_RMAX);
+    c.g = g;
+    int rc;
+    if (cells) {
+        if (type == 2) rc = kde_bin<2>(tgt, nv, g, NULL, 1, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
+        else           rc = kde_bin<3>(tgt, nv, g, NULL, 1, tcell, cnt, cursor, tstart, tperm, tgt_sorted, scan_ws, s);
+        if (rc) return rc;
+        c.ssorted = tgt_sorted; c.sst = tstart;
     }
+    if (ids || labels) {
+        if (type == 2) rc = kde_bin<2>(src, ns, g, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+        else           rc = kde_bin<3>(src, ns, g, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+        if (rc) return rc;
+        c.ssorted = src_sorted; c.sst = sstart;
+    }
+    return 0;
+}
+
+static int kde_launch_cells(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s) {
+    const int ncell = c.g.ncx * c.g.ncy;
+    MS_K("kde_cells", s);
+    if (c.type == 2) {
+        if (c.clamp) k_kde_cells<2, true><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
+        else         k_kde_cells<2, false><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
+    } else           k_kde_cells<3, true><<<ncell, CELL_T, 0, s>>>((const double4*)c.tgt_sorted, c.tstart, c.tperm, (const double4*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
+    MS_LAUNCH_CHECK();
     return 0;
 }
 
@@ -572,48 +671,89 @@ extern "C" int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_
                       void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
     KdeCtx c;
-    int rc = kde_front(verts, nv, ids, nids, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
+    int rc = kde_front(verts, nv, ids, nids, NULL, 1, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
-    const KdePlan &p = c.p;
-    if (c.cells) {
-        const int ncell = c.g.ncx * c.g.ncy;
-        MS_K("kde_cells", s);
-        if (type == 2) {
-            if (c.clamp) k_kde_cells<2, true><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.g, c.partial);
-            else         k_kde_cells<2, false><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.g, c.partial);
-        } else           k_kde_cells<3, true><<<ncell, CELL_T, 0, s>>>((const double4*)c.tgt_sorted, c.tstart, c.tperm, (const double4*)c.ssorted, c.sst, c.g, c.partial);
-        MS_LAUNCH_CHECK();
-    } else {
-        if (type == 2) {
-            if (periodic) rc = c.clamp ? kde_run_pairs<2, true, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s)
-                                       : kde_run_pairs<2, true, false>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
-            else          rc = kde_run_pairs<2, false, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
-        } else            rc = periodic ? kde_run_pairs<3, true, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s)
-                                        : kde_run_pairs<3, false, true>(p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
-        if (rc) return rc;
-    }
+    if (c.cells) rc = kde_launch_cells(c, nv, c.partial, s);
+    else         rc = kde_pairs_dispatch(type, periodic, c.clamp, c.p, nv, c.wx, c.wy, c.tgt, c.src, c.partial, s);
+    if (rc) return rc;
     const int nb = ms_blocks(nv, RED_T);
     MS_K("kde_combine", s); k_kde_combine<<<nb, RED_T, 0, s>>>(c.partial, nv, c.nsplit, (double)c.sfactor * (1.0 / (double)nv), c.dens, c.bsum);
     double *total = c.bsum + nb;
     if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(c.bsum, nb, total); }
-    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(c.dens, nv, get_counts ? total : NULL, (double)p.ns, density_f64, density_f32);
+    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(c.dens, nv, get_counts ? total : NULL, (double)c.p.ns, density_f64, density_f32);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }
 
-extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
+extern "C" int ms_kde_labels(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                             int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                             double *raw, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(labels != NULL && raw != NULL, "ms_kde_labels: labels and raw are required");
+    KdeCtx c;
+    int rc = kde_front(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
+    if (rc) return rc;
+    if (c.cells) {
+        rc = kde_launch_cells(c, nv, raw, s);
+        if (rc) return rc;
+        MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(raw, nv * nlabels, (double)c.sfactor);
+        MS_K(NULL, s);
+        MS_LAUNCH_CHECK();
+        return 0;
+    }
+    // all pairs: the label-sorted source array is cut into one range per label (offsets read back)
+    int32_t h[KDE_MAX_LABELS + 1];
+    MS_CUDA(cudaMemcpyAsync(h, c.sstart, sizeof(int32_t) * (nlabels + 1), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    const size_t esz = type == 2 ? sizeof(double2) : sizeof(double4);
+    for (int l = 0; l < nlabels; l++) {
+        const int64_t nsl = h[l + 1] - h[l];
+        double *out = raw + (size_t)l * nv;
+        if (nsl <= 0) { MS_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * nv, s)); continue; }
+        KdePlan p = kde_plan(nv, nsl);
+        if (p.nsplit > c.p.nsplit) p.nsplit = c.p.nsplit;          // partial buffer was sized for the whole source set
+        rc = kde_pairs_dispatch(type, periodic, c.clamp, p, nv, c.wx, c.wy, c.tgt, (const char*)c.src_sorted + (size_t)h[l] * esz, c.partial, s);
+        if (rc) return rc;
+        MS_K("kde_combine", s); k_kde_combine<<<ms_blocks(nv, RED_T), RED_T, 0, s>>>(c.partial, nv, p.nsplit, (double)c.sfactor, out, c.bsum);
+    }
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" size_t ms_kde_select_workspace_bytes(int64_t nv) { return ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8) + 1024; }
+extern "C" int ms_kde_select(const double *raw, int64_t nv, int nlabels, const uint8_t *select, double n_selected, int get_counts,
+                             double *density_f64, float *density_f32, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(raw && select && nv > 0 && nlabels >= 1 && nlabels <= KDE_MAX_LABELS, "ms_kde_select: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_kde_select_workspace_bytes(nv), "ms_kde_select: workspace too small");
+    unsigned long long mask = 0ull;
+    for (int l = 0; l < nlabels; l++) if (select[l]) mask |= 1ull << l;
+    MsArena A(ws, ws_bytes);
+    double *dens = A.take<double>(nv), *bsum = A.take<double>(nv / RED_T + 2);
+    const int nb = ms_blocks(nv, RED_T);
+    MS_K("kde_select", s); k_kde_select<<<nb, RED_T, 0, s>>>(raw, nv, nlabels, mask, 1.0 / (double)nv, dens, bsum);
+    double *total = bsum + nb;
+    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(bsum, nb, total); }
+    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(dens, nv, get_counts ? total : NULL, n_selected, density_f64, density_f32);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, const int32_t *labels, int nlabels,
                                       int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                                       double *pairs, void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(pairs != NULL, "ms_kde_evaluated_pairs: need an output");
     KdeCtx c;
-    int rc = kde_front(verts, nv, ids, nids, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
+    int rc = kde_front(verts, nv, ids, nids, labels, nlabels, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
     if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); *pairs = (double)nv * (double)c.p.ns; return 0; }
     MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
     const int ncell = c.g.ncx * c.g.ncy;
-    MS_K("kde_cells_count", s); k_kde_cells_count<0><<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.g, c.counter);
+    MS_K("kde_cells_count", s); k_kde_cells_count<<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.nlabels, c.g, c.counter);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     unsigned long long h = 0ull;

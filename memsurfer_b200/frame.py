@@ -48,9 +48,13 @@ class LeafletFrame(object):
         self.half_box = mesh._half_box()
         self.bboxl = None if mesh.bboxl is None else np.asarray(mesh.bboxl, np.float32)
         self.label_ids = {}
+        self.label_values, self.label_index, self.label_counts = None, None, None
         if labels is not None:
             labels = np.asarray(labels)
-            for l in np.unique(labels):
+            self.label_values, inv = np.unique(labels, return_inverse=True)
+            self.label_counts = np.bincount(inv, minlength=self.label_values.shape[0])
+            self.label_index = self._up(np.ascontiguousarray(inv, np.int32))
+            for l in self.label_values:
                 ids = np.where(labels == l)[0].astype(np.int32)
                 self.label_ids[l.item() if hasattr(l, "item") else l] = self._up(ids)
         dev = self.device
@@ -66,7 +70,10 @@ class LeafletFrame(object):
         self.pa32 = torch.empty(nv, dtype=torch.float32, device=dev)
         self.H = torch.empty(nv, dtype=torch.float64, device=dev)
         self.K = torch.empty(nv, dtype=torch.float64, device=dev)
-        self.kde_ws = _lib.workspace(L.ms_kde_workspace_bytes(nv, 0), dev)
+        nl = 1 if self.label_values is None else int(self.label_values.shape[0])
+        self.kde_ws = _lib.workspace(max(L.ms_kde_workspace_bytes(nv, 0), L.ms_kde_labels_workspace_bytes(nv, nl)), dev)
+        self.kde_sel_ws = _lib.workspace(L.ms_kde_select_workspace_bytes(nv), dev)
+        self.kde_raw = torch.empty((nl, nv), dtype=torch.float64, device=dev)
         self.sum_ws = _lib.workspace(L.ms_field_summary_workspace_bytes(), dev)
         self.densities = {}
         self.pnormals32 = self.pnormals64 = None
@@ -108,18 +115,40 @@ class LeafletFrame(object):
                             _lib.stream_ptr(self.device)), 'ms_kde')
         return out
 
-    def run_densities(self, sigmas, types=(2,), get_nlipids=True, cutoff_sigmas=0.0):
-        """'all' + one field per label, named as Membrane.compute_densities names them."""
+    def run_densities(self, sigmas, types=(2,), get_nlipids=True, cutoff_sigmas=0.0, fused=True):
+        """'all' + one field per label, named as Membrane.compute_densities names them.  fused: one
+        ms_kde_labels pass per (type, sigma) + one ms_kde_select per field; else one ms_kde per field."""
+        L = _lib.lib()
+        st = _lib.stream_ptr(self.device)
+        fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
         for t in types:
             for s in sigmas:
-                self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, 'all', s), t, s, get_nlipids, None, cutoff_sigmas)
-                for l, ids in self.label_ids.items():
-                    self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, l, s), t, s, get_nlipids, ids, cutoff_sigmas)
+                if not fused:
+                    self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, 'all', s), t, s, get_nlipids, None, cutoff_sigmas)
+                    for l, ids in self.label_ids.items():
+                        self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, l, s), t, s, get_nlipids, ids, cutoff_sigmas)
+                    continue
+                nl = int(self.label_values.shape[0])
+                _lib.check(L.ms_kde_labels(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(), nl, int(t),
+                                           int(self.periodic), self._box(cutoff_sigmas), float(s), float(cutoff_sigmas),
+                                           self.kde_raw.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
+                           'ms_kde_labels')
+                for li, l in enumerate(['all'] + [v.item() for v in self.label_values]):
+                    name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)
+                    out = self.densities.get(name)
+                    if out is None:
+                        out = self.densities[name] = (torch.empty(self.nv, dtype=torch.float64, device=self.device),
+                                                      torch.empty(self.nv, dtype=torch.float32, device=self.device))
+                    sel = np.ones(nl, np.uint8) if li == 0 else np.eye(nl, dtype=np.uint8)[li - 1]
+                    nsel = float(self.nv if li == 0 else self.label_counts[li - 1])
+                    _lib.check(L.ms_kde_select(self.kde_raw.data_ptr(), self.nv, nl, sel.tobytes(), nsel, int(bool(get_nlipids)),
+                                               out[0].data_ptr(), out[1].data_ptr(), self.kde_sel_ws.data_ptr(),
+                                               self.kde_sel_ws.numel(), st), 'ms_kde_select')
 
-    def run(self, sigmas, knbrs=18, cutoff_sigmas=0.0):
+    def run(self, sigmas, knbrs=18, cutoff_sigmas=0.0, fused=True):
         self.run_pnormals(knbrs)
         self.run_properties()
-        self.run_densities(sigmas, cutoff_sigmas=cutoff_sigmas)
+        self.run_densities(sigmas, cutoff_sigmas=cutoff_sigmas, fused=fused)
 
     def _box(self, cutoff_sigmas):
         if self.periodic:
@@ -133,19 +162,23 @@ class LeafletFrame(object):
             return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
         return None
 
-    def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0):
+    def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0, fused=True):
         """Pairs the KDE kernels actually evaluate in run_densities (diagnostic; synchronises)."""
         import ctypes as C
         L = _lib.lib()
         total = 0.0
         out = C.c_double(0)
+        fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
         for t in types:
             for s in sigmas:
-                for ids in [None] + list(self.label_ids.values()):
-                    nids = 0 if ids is None else int(ids.numel())
+                if fused:
+                    sets = [(None, 0, self.label_index, int(self.label_values.shape[0]))]
+                else:
+                    sets = [(None, 0, None, 1)] + [(ids, int(ids.numel()), None, 1) for ids in self.label_ids.values()]
+                for ids, nids, lab, nl in sets:
                     _lib.check(L.ms_kde_evaluated_pairs(self.kverts.data_ptr(), self.nv, _lib.ptr(ids) if nids else None, nids,
-                                                        int(t), int(self.periodic), self._box(cutoff_sigmas), float(s),
-                                                        float(cutoff_sigmas), C.byref(out), self.kde_ws.data_ptr(),
+                                                        _lib.ptr(lab), nl, int(t), int(self.periodic), self._box(cutoff_sigmas),
+                                                        float(s), float(cutoff_sigmas), C.byref(out), self.kde_ws.data_ptr(),
                                                         self.kde_ws.numel(), _lib.stream_ptr(self.device)),
                                'ms_kde_evaluated_pairs')
                     total += out.value

@@ -196,19 +196,41 @@ class Membrane(object):
         mesh.compute_pointareas()
         mesh.compute_curvatures()
 
+    MAX_FUSED_LABELS = 64
+
+    def _label_table(self):
+        """Distinct label values and the per-point index into them (computed once)."""
+        if getattr(self, '_label_values', None) is None:
+            self._label_values, self._label_inverse = np.unique(self.labels, return_inverse=True)
+        return self._label_values, self._label_inverse
+
     def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=None):
+        """Density of the points carrying one of `labels` (all points if empty) on memb_smooth
+        (membrane.py:252-274).  With point labels available the label-fused kernel is used: the first
+        field of a given (type, sigma) evaluates every vertex pair once and later fields of other
+        labels are only a normalisation pass."""
         if cutoff_sigmas is None:
             cutoff_sigmas = self.KDE_CUTOFF_SIGMAS
         if type < 1 or type > 3:
             raise ValueError(f'Invalid density type, {type}. Should be 1 (geodesic), 2 (2D) or 3 (3D)')
-        if len(labels) == 0:
-            self.attributes[name] = self.memb_smooth.compute_density(type, sigma, name, get_nlipdis,
-                                                                     np.empty([0]), cutoff_sigmas)
-            return
-        if self.labels is None:
+        mesh = self.memb_smooth
+        if len(labels) > 0 and self.labels is None:
             raise ValueError('Cannot compute density of selected labels, because point labels are not available')
+        fused = self.labels is not None and type != 1
+        if fused:
+            values, inverse = self._label_table()
+            fused = values.shape[0] <= self.MAX_FUSED_LABELS
+        if fused:
+            if mesh._label_index is None:
+                mesh.set_vertex_labels(inverse, values.shape[0])
+            select = np.arange(values.shape[0]) if len(labels) == 0 else np.where(np.isin(values, labels))[0]
+            self.attributes[name] = mesh.compute_density_labels(type, sigma, name, get_nlipdis, select, cutoff_sigmas)
+            return
+        if len(labels) == 0:
+            self.attributes[name] = mesh.compute_density(type, sigma, name, get_nlipdis, np.empty([0]), cutoff_sigmas)
+            return
         lidxs = np.where(np.isin(self.labels, labels))[0]
-        self.attributes[name] = self.memb_smooth.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas)
+        self.attributes[name] = mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas)
 
     @staticmethod
     def compute_thickness(a, b, mtype='smooth'):

@@ -56,6 +56,8 @@ class TriMesh(object):
         self.attributes = {}
         self.attributes_f64 = {}
         self._fields = {}                # KDE fields cached by name (TriMesh_kde.cpp:455-460)
+        self._label_index = None         # optional per-vertex integer labels (label-fused KDE)
+        self._nlabels = 0
         self._dev = {}                   # device-resident buffers
 
     def tag(self):
@@ -247,13 +249,24 @@ class TriMesh(object):
                                   '(SURVEY.md section 8(f), rank 1)')
 
     # ---------------------------------------------------------------------- KDE
-    def density_device(self, type, sigma, get_nlipids, pidxs_dev=None, cutoff_sigmas=0.0):
-        """Run ms_kde on device-resident inputs; returns (f64 tensor, f32 tensor)."""
-        _lib.require_cuda()
-        L = _lib.lib()
-        dev = self.device
+    def _kde_box(self, cutoff_sigmas):
+        if self.periodic:
+            if self.bboxl is None:
+                raise ValueError(f'{self.tag()} periodic density needs a bbox')
+            b = np.asarray(self.bboxl, np.float32)
+            if b.shape[0] == 4:
+                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
+            return _lib.box6(b)
+        if cutoff_sigmas > 0:
+            # non-periodic cut-off: the cell list only needs the extent of the vertices
+            lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
+            return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
+        return None
+
+    def _kde_verts_device(self):
         d = self._dev
         if 'kverts' not in d:
+            dev = self.device
             if 'verts' in d:
                 d['kverts'] = d['verts'][:self.vertices.shape[0]]      # already resident (first V rows)
             elif self.vertices.shape[1] == 3:
@@ -263,31 +276,98 @@ class TriMesh(object):
                 v[:, :2] = self.vertices; v[:, 2] = 0.0
                 d['kverts'] = _lib.h2d(v, dev)
                 d['_khost'] = v
-        nv = d['kverts'].shape[0]
+        return d['kverts']
+
+    def _workspace(self, key, nbytes):
+        ws = self._dev.get(key)
+        if ws is None or ws.numel() < nbytes:
+            ws = self._dev[key] = _lib.workspace(nbytes, self.device)
+        return ws
+
+    def density_device(self, type, sigma, get_nlipids, pidxs_dev=None, cutoff_sigmas=0.0):
+        """Run ms_kde on device-resident inputs; returns (f64 tensor, f32 tensor)."""
+        _lib.require_cuda()
+        L = _lib.lib()
+        dev = self.device
+        kverts = self._kde_verts_device()
+        nv = kverts.shape[0]
         nids = 0 if pidxs_dev is None else int(pidxs_dev.numel())
         o64 = torch.empty(nv, dtype=torch.float64, device=dev)
         o32 = torch.empty(nv, dtype=torch.float32, device=dev)
-        nbytes = L.ms_kde_workspace_bytes(nv, nids)
-        ws = d.get('kde_ws')
-        if ws is None or ws.numel() < nbytes:
-            ws = d['kde_ws'] = _lib.workspace(nbytes, dev)
-        box = None
-        if self.periodic:
-            if self.bboxl is None:
-                raise ValueError(f'{self.tag()} periodic density needs a bbox')
-            b = np.asarray(self.bboxl, np.float32)
-            if b.shape[0] == 4:
-                b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
-            box = _lib.box6(b)
-        elif cutoff_sigmas > 0:
-            # non-periodic cut-off: the cell list only needs the extent of the vertices
-            lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
-            box = _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
-        _lib.check(L.ms_kde(d['kverts'].data_ptr(), nv, _lib.ptr(pidxs_dev) if nids else None, nids,
-                            int(type), int(bool(self.periodic)), box, float(sigma), int(bool(get_nlipids)),
-                            float(cutoff_sigmas), o64.data_ptr(), o32.data_ptr(),
+        ws = self._workspace('kde_ws', L.ms_kde_workspace_bytes(nv, nids))
+        _lib.check(L.ms_kde(kverts.data_ptr(), nv, _lib.ptr(pidxs_dev) if nids else None, nids,
+                            int(type), int(bool(self.periodic)), self._kde_box(cutoff_sigmas), float(sigma),
+                            int(bool(get_nlipids)), float(cutoff_sigmas), o64.data_ptr(), o32.data_ptr(),
                             ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_kde')
         return o64, o32
+
+    def set_vertex_labels(self, label_index, nlabels):
+        """Integer label in [0, nlabels) per vertex (negative: never a KDE source).  Enables the label-fused
+        KDE: one pass evaluates every vertex pair once and keeps the sums apart by the source's label."""
+        label_index = np.asarray(label_index)
+        if label_index.shape != (self.vertices.shape[0],):
+            raise ValueError(f'{self.tag()} expects one label per vertex')
+        self._label_index = _lib.pinned_copy(label_index, np.int32)
+        self._nlabels = int(nlabels)
+        self._label_counts = np.bincount(label_index[label_index >= 0], minlength=self._nlabels)
+        self._dev.pop('labels', None)
+        self._dev.pop('kde_raw', None)
+
+    def density_labels_device(self, type, sigma, cutoff_sigmas=0.0):
+        """(nlabels, V) f64 device tensor of raw per-label pair sums (cached per (type, sigma, cut-off))."""
+        _lib.require_cuda()
+        L = _lib.lib()
+        dev = self.device
+        d = self._dev
+        cache = d.setdefault('kde_raw', {})
+        key = (int(type), float(sigma), float(cutoff_sigmas))
+        if key in cache:
+            return cache[key]
+        kverts = self._kde_verts_device()
+        nv = kverts.shape[0]
+        if 'labels' not in d:
+            d['labels'] = _lib.h2d(self._label_index, dev)
+        raw = torch.empty((self._nlabels, nv), dtype=torch.float64, device=dev)
+        ws = self._workspace('kde_ws', L.ms_kde_labels_workspace_bytes(nv, self._nlabels))
+        _lib.check(L.ms_kde_labels(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
+                                   int(bool(self.periodic)), self._kde_box(cutoff_sigmas), float(sigma),
+                                   float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
+                                   _lib.stream_ptr(dev)), 'ms_kde_labels')
+        cache[key] = raw
+        return raw
+
+    def density_select_device(self, raw, select, get_nlipids):
+        """Normalised density of the union of the selected labels from the raw per-label sums."""
+        L = _lib.lib()
+        dev = self.device
+        nv = raw.shape[1]
+        sel = np.zeros(self._nlabels, np.uint8)
+        sel[np.asarray(select, dtype=np.int64)] = 1
+        nsel = float(self._label_counts[sel.astype(bool)].sum())
+        o64 = torch.empty(nv, dtype=torch.float64, device=dev)
+        o32 = torch.empty(nv, dtype=torch.float32, device=dev)
+        ws = self._workspace('kde_sel_ws', L.ms_kde_select_workspace_bytes(nv))
+        _lib.check(L.ms_kde_select(raw.data_ptr(), nv, self._nlabels, sel.tobytes(), nsel, int(bool(get_nlipids)),
+                                   o64.data_ptr(), o32.data_ptr(), ws.data_ptr(), ws.numel(),
+                                   _lib.stream_ptr(dev)), 'ms_kde_select')
+        return o64, o32
+
+    def compute_density_labels(self, type, sigma, name, get_nlipids, select, cutoff_sigmas=0.0):
+        """Label-fused twin of compute_density: `select` = label indices (set_vertex_labels) whose vertices
+        are the sources.  Same result as compute_density with the ids of those vertices."""
+        if type < 1 or type > 3:
+            raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
+        if type == 1:
+            raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
+        if name in self._fields:
+            return self._fields[name]
+        raw = self.density_labels_device(type, sigma, cutoff_sigmas)
+        o64, o32 = self.density_select_device(raw, select, get_nlipids)
+        dens = _lib.d2h(o32)
+        self._fields[name] = dens
+        self.attributes_f64[name] = _lib.d2h(o64)
+        LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        return dens
 
     def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0):
         """(V,) float32 density (trimesh.py:324-361 -> TriMesh::kde TriMesh_kde.cpp:443-532).

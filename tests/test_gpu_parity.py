@@ -153,6 +153,49 @@ def test_kde_cutoff_matches_all_pairs_at_full_size():
         assert abs(c64.sum() - (len(sel) or pts.shape[0])) < 1e-5
 
 
+@pytest.mark.parametrize("cutoff", [0.0, 8.0])
+@pytest.mark.parametrize("periodic", [True, False])
+def test_kde_label_fused_vs_oracle(oracle, leaflet, cutoff, periodic):
+    """ms_kde_labels + ms_kde_select (one pass for every label) against the oracle's per-field sums."""
+    from memsurfer_b200 import TriMesh
+    pts, labels, bbox = leaflet
+    labels = labels.copy(); labels[::97] = -1                      # some vertices are never a source
+    nl = int(labels.max()) + 1
+    mesh = TriMesh(pts, periodic=periodic)
+    bb = np.concatenate([pts.min(0), pts.max(0)]).astype(np.float32)
+    if periodic:
+        mesh.set_bbox(bb[:3], bb[3:])
+    mesh.set_vertex_labels(labels, nl)
+    for typ, sigma in ((2, 12.0), (3, 30.0)):
+        for sel in ([0], [1, 2], list(range(nl))):
+            for gc in (True, False):
+                name = f"f{typ}_{sigma}_{sel}_{gc}"
+                mesh.compute_density_labels(typ, sigma, name, gc, sel, cutoff_sigmas=cutoff)
+                ids = np.where(np.isin(labels, sel))[0].astype(np.int32)
+                want = oracle.kde(pts, ids, typ, sigma, gc, bb if periodic else None)
+                ok, err = close(mesh.attributes_f64[name], want)
+                assert ok, f"cutoff {cutoff} periodic {periodic} type {typ} sel {sel} counts {gc}: max abs err {err}"
+
+
+def test_membrane_fused_densities_match_unfused(leaflet):
+    from memsurfer_b200 import Membrane
+    pts, labels, bbox = leaflet
+    res = []
+    for lab in (labels, None):
+        m = Membrane(pts, labels=lab, periodic=True, bbox=bbox)
+        m.compute_membrane_surface()
+        Membrane.compute_densities([m], [2], [15.0], True, 'all')
+        if lab is not None:
+            Membrane.compute_densities([m], [2], [15.0], True, 1)
+            res.append(m.memb_smooth.attributes_f64['density_type2_1_k15.0'])
+            ids = np.where(labels == 1)[0]
+            m.memb_smooth.compute_density(2, 15.0, 'unfused_1', True, ids, cutoff_sigmas=8.0)
+            res.append(m.memb_smooth.attributes_f64['unfused_1'])
+        res.append(m.memb_smooth.attributes_f64['density_type2_all_k15.0'])
+    f1, u1, fall, uall = res
+    assert close(f1, u1)[0] and close(fall, uall)[0]
+
+
 def test_kde_large_register_blocked_path(oracle):
     """V >= 148*1024 targets takes the R=4 register-blocked kernel; oracle on a target subset."""
     from memsurfer_b200 import TriMesh, synth
