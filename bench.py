@@ -70,7 +70,7 @@ def make_frame_inputs(lipids, frame):
                                                phase_shift=0.05 * frame)
         dfaces, doffs = synth.periodic_delaunay(pts[:, :2], bbox[0], bbox[1])
         tri = synth.trim_periodic(pts, dfaces, doffs, pts.min(axis=0), pts.max(axis=0))
-        leaflets.append(dict(points=pts, labels=labels, bbox=bbox, tri=tri))
+        leaflets.append(dict(points=pts, labels=labels, bbox=bbox, tri=tri, lo=pts.min(axis=0), hi=pts.max(axis=0)))
     return leaflets
 
 
@@ -78,7 +78,7 @@ def new_mesh(lf, device):
     from memsurfer_b200 import TriMesh
     t = lf["tri"]
     mesh = TriMesh(lf["points"], periodic=True, label="memb_smooth", device=device)
-    mesh.set_bbox(lf["points"].min(axis=0), lf["points"].max(axis=0))
+    mesh.set_bbox(lf["lo"], lf["hi"])          # the producer's bbox (spoints min/max, membrane.py:214-217)
     mesh.set_periodic_triangulation(t["faces"], t["periodic_faces"], t["trimmed_faces"],
                                     t["duplicated_vidxs"], t["duplicated_verts"])
     return mesh

@@ -366,7 +366,8 @@ class TriMesh(object):
         dens = _lib.d2h(o32)
         self._fields[name] = dens
         self.attributes_f64[name] = _lib.d2h(o64)
-        LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        if LOGGER.isEnabledFor(logging.INFO):
+            LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         return dens
 
     def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0):
@@ -389,5 +390,6 @@ class TriMesh(object):
         dens = _lib.d2h(o32)
         self._fields[name] = dens
         self.attributes_f64[name] = _lib.d2h(o64)
-        LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        if LOGGER.isEnabledFor(logging.INFO):
+            LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         return dens

@@ -1,0 +1,41 @@
+#!/usr/bin/env python
+"""Key metrics of every kernel in an .ncu-rep (reads `ncu -i ... --page raw --csv`)."""
+import csv
+import subprocess
+import sys
+
+WANT = [
+    "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+    "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
+    "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+    "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct",
+    "l1tex__t_bytes.sum", "sm__cycles_elapsed.max", "smsp__cycles_active.avg",
+]
+STALL = "smsp__average_warp"
+
+
+def main(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    for r in rows[2:]:
+        print("==", r[hdr.index("Kernel Name")][:110])
+        for w in WANT:
+            if w in hdr:
+                print(f"  {w:75s} {r[hdr.index(w)]:>18s} {units[hdr.index(w)]}")
+        st = []
+        for i, h in enumerate(hdr):
+            if "warp_issue_stalled" in h and h.endswith("_per_warp_active.pct"):
+                try:
+                    st.append((float(r[i]), h.replace("smsp__warp_issue_stalled_", "").replace("_per_warp_active.pct", "")))
+                except ValueError:
+                    pass
+        st.sort(reverse=True)
+        print("  stalls (% of warp-active):", ", ".join(f"{n} {v:.1f}" for v, n in st[:6]))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1])
