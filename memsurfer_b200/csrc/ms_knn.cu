@@ -203,6 +203,87 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) k_knn(const float4 *__restrict
     if (lane < k1) nbr[(int64_t)qi * k1 + lane] = (bi == 0x7fffffff) ? -1 : bi;
 }
 
+// One THREAD per query (queries in cell order, so a warp works on neighbouring cells): the K best
+// (d2, index) so far live in registers as a sorted list; a candidate that beats the current worst is
+// inserted by a branch-free compare-exchange chain.  K >= k1 is a compile-time capacity; the search
+// stops when the K-th distance lies inside the explored square, so the first k1 entries are exact.
+// The block's neighbour lists go through shared memory so that rows are written with coalescing.
+#define KNNT_T 128
+template <int K>
+__device__ __forceinline__ void knn_scan(const float4 *__restrict__ sorted, int pb, int pe, double qx, double qy, double qz,
+                                         double (&bd)[K], int (&bi)[K]) {
+    for (int p = pb; p < pe; p++) {
+        const float4 c = __ldg(sorted + p);
+        const double dx = qx - (double)c.x, dy = qy - (double)c.y, dz = qz - (double)c.z;
+        double cd = dx * dx; cd += dy * dy; cd += dz * dz;
+        int ci = __float_as_int(c.w);
+        if (!key_lt(cd, ci, bd[K - 1], bi[K - 1])) continue;
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            const bool lt = key_lt(cd, ci, bd[j], bi[j]);
+            const double td = lt ? bd[j] : cd; const int ti = lt ? bi[j] : ci;
+            bd[j] = lt ? cd : bd[j]; bi[j] = lt ? ci : bi[j];
+            cd = td; ci = ti;
+        }
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict__ sorted, int64_t m, Grid g,
+                                                       const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr) {
+    extern __shared__ int32_t sm_nbr[];                   // KNNT_T * k1 neighbour ids + KNNT_T query ids
+    int32_t *sm_q = sm_nbr + KNNT_T * k1;
+    const int64_t q = (int64_t)blockIdx.x * KNNT_T + threadIdx.x;
+    double bd[K]; int bi[K];
+#pragma unroll
+    for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
+    int qi = -1;
+    if (q < m) {
+        const float4 me = sorted[q];
+        qi = __float_as_int(me.w);
+        const double qx = me.x, qy = me.y, qz = me.z;
+        int cx, cy; cell_of(g, me.x, me.y, cx, cy);
+        const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
+        for (int r = 0; ; r++) {
+            for (int yy = cy - r; yy <= cy + r; yy++) {
+                if (yy < 0 || yy >= g.ny) continue;
+                const bool full_row = (yy == cy - r) || (yy == cy + r);
+                const int nseg = full_row ? 1 : 2;
+                for (int sg = 0; sg < nseg; sg++) {
+                    int x0, x1;
+                    if (full_row) { x0 = cx - r; x1 = cx + r; } else { x0 = x1 = (sg == 0 ? cx - r : cx + r); }
+                    x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
+                    if (x0 > x1) continue;
+                    knn_scan<K>(sorted, __ldg(start + yy * g.nx + x0), __ldg(start + yy * g.nx + x1 + 1), qx, qy, qz, bd, bi);
+                }
+            }
+            if (cx - r <= 0 && cy - r <= 0 && cx + r >= g.nx - 1 && cy + r >= g.ny - 1) break;
+            // distance to the unexplored region; a side on which the window already reaches the grid edge has none
+            const double b0 = cx - r > 0 ? rx - (double)(cx - r) * g.h : DBL_MAX;
+            const double b1 = cx + r < g.nx - 1 ? (double)(cx + r + 1) * g.h - rx : DBL_MAX;
+            const double b2 = cy - r > 0 ? ry - (double)(cy - r) * g.h : DBL_MAX;
+            const double b3 = cy + r < g.ny - 1 ? (double)(cy + r + 1) * g.h - ry : DBL_MAX;
+            const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
+            if (bm > 0.0 && bd[K - 1] < DBL_MAX && sqrt(bd[K - 1]) < bm * (1.0 - 1e-9)) break;
+        }
+    }
+    sm_q[threadIdx.x] = qi;
+#pragma unroll
+    for (int j = 0; j < K; j++) if (j < k1) sm_nbr[threadIdx.x * k1 + j] = (bi[j] == 0x7fffffff) ? -1 : bi[j];
+    __syncthreads();
+    for (int e = threadIdx.x; e < KNNT_T * k1; e += KNNT_T) {
+        const int row = e / k1, col = e - row * k1;
+        const int id = sm_q[row];
+        if (id >= 0) nbr[(int64_t)id * k1 + col] = sm_nbr[e];
+    }
+}
+
+template <int K>
+static void knn_thread_launch(const float4 *sorted, int64_t m, const Grid &g, const int32_t *start, int k1, int32_t *nbr, cudaStream_t s) {
+    const size_t smem = (size_t)KNNT_T * (k1 + 1) * sizeof(int32_t);
+    k_knn_thread<K><<<ms_blocks(m, KNNT_T), KNNT_T, smem, s>>>(sorted, m, g, start, k1, nbr);
+}
+
 extern "C" size_t ms_knn_workspace_bytes(int64_t m, int k1) {
     (void)k1;
     const size_t ncell = (size_t)m + 2048;
@@ -251,7 +332,14 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     MS_K("cell_count", s); k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, g, cell, cnt);
     if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
     MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
-    MS_K("knn", s); k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);
+    MS_K("knn", s);
+    if (m < k1) k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);   // fewer points than k+1
+    else if (k1 <= 8) knn_thread_launch<8>(sorted, m, g, start, k1, nbr, s);
+    else if (k1 <= 12) knn_thread_launch<12>(sorted, m, g, start, k1, nbr, s);
+    else if (k1 <= 16) knn_thread_launch<16>(sorted, m, g, start, k1, nbr, s);
+    else if (k1 <= 19) knn_thread_launch<19>(sorted, m, g, start, k1, nbr, s);
+    else if (k1 <= 24) knn_thread_launch<24>(sorted, m, g, start, k1, nbr, s);
+    else knn_thread_launch<32>(sorted, m, g, start, k1, nbr, s);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
