@@ -89,14 +89,18 @@ int ms_mesh_topology(const float *verts_all, int64_t nv_all, int64_t nv,
                      int32_t *csr_off, int32_t *csr_adj, uint8_t *keep,
                      void *ws, size_t ws_bytes, void *stream);
 
-/* One fused per-vertex gather: area-weighted vertex normals, mixed Voronoi point areas, mean
- * (dihedral) and Gaussian (angle-deficit) curvature.  Any output may be NULL.                  */
+/* Area-weighted vertex normals, mixed Voronoi point areas, mean (dihedral) and Gaussian (angle-deficit)
+ * curvature of the first nv vertices: one pass per face (everything that depends on a single face, one
+ * 128-byte record each), one pass per face edge (mean-curvature edge terms) and one deterministic
+ * gather per vertex.  Any output may be NULL.                                                     */
+size_t ms_mesh_properties_workspace_bytes(int64_t nv, int64_t nf);
 int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
                        const uint32_t *faces_all, int64_t nf,
                        const int32_t *csr_off, const int32_t *csr_adj, const uint8_t *keep,
                        double *vnormals_f64, float *vnormals_f32,
                        double *pareas_f64, float *pareas_f32,
-                       double *mean_curv, double *gaus_curv, void *stream);
+                       double *mean_curv, double *gaus_curv,
+                       void *ws, size_t ws_bytes, void *stream);
 
 /* ---------------------------------------------------------------- KDE densities
  * Replaces memsurfer_cmod.TriMesh.kde types 2 and 3 (TriMesh_kde.cpp:344-392, 443-532) with

@@ -35,7 +35,8 @@ _SIGNATURES = {
     "ms_finish_pnormals": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "ms_mesh_topology_workspace_bytes": (_sz, [_i64, _i64]),
     "ms_mesh_topology": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _f64, _f64, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "ms_mesh_properties": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ms_mesh_properties_workspace_bytes": (_sz, [_i64, _i64]),
+    "ms_mesh_properties": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ms_kde_workspace_bytes": (_sz, [_i64, _i64]),
     "ms_kde": (C.c_int, [_vp, _i64, _vp, _i64, _i32, _i32, C.POINTER(_f32), _f32, _i32, _f64, _vp, _vp, _vp, _sz, _vp]),
     "ms_kde_labels_workspace_bytes": (_sz, [_i64, _i32]),

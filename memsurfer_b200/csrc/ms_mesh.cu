@@ -86,7 +86,7 @@ extern "C" int ms_mesh_topology(const float *verts_all, int64_t nv_all, int64_t 
     return 0;
 }
 
-// ------------------------------------------------------------------ fused properties
+// ------------------------------------------------------------------ properties: face pass, edge pass, vertex gather
 struct D3 { double x, y, z; };
 __device__ __forceinline__ D3 ldv(const float *__restrict__ verts, uint32_t i) {
     const float *p = verts + 3 * (size_t)i;
@@ -109,125 +109,168 @@ __device__ __forceinline__ double angle_between(const D3 &u, const D3 &v) {
     return atan2(sqrt(dot(c, c)), dot(u, v));
 }
 
-// count list entries of vertex list [b,e) (other than face g) whose face is kept and contains u;
-// returns the count and the last such face in nb
-__device__ __forceinline__ int edge_neighbours(const uint32_t *__restrict__ faces, const int32_t *__restrict__ adj,
-                                               const uint8_t *__restrict__ keep, int b, int e, int g, uint32_t u, int &nb) {
-    int cnt = 0;
-    for (int j = b; j < e; j++) {
-        const int h = __ldg(adj + j) >> 2;
-        if (h == g || !__ldg(keep + h)) continue;
-        const uint32_t *t = faces + 3 * (size_t)h;
-        if (__ldg(t) == u || __ldg(t + 1) == u || __ldg(t + 2) == u) { nb = h; cnt++; }
+// Everything that depends on one face only, computed ONCE per face (the reference's face loops,
+// TriMesh.cpp:108-128 and :149-189, and the per-triangle part of vtkCurvatures): 16 doubles = one
+// 128-byte line per face.
+struct __align__(16) FaceRec {
+    double fn[3];      // a x b (unnormalised face normal of need_normals; 0 for a degenerate face)
+    double w[3];       // weight of fn at corner 0,1,2: 1/(|a|^2|c|^2), 1/(|b|^2|a|^2), 1/(|c|^2|b|^2) (0 if degenerate)
+    double ca[3];      // mixed Voronoi corner areas (need_pointareas)
+    double al[3];      // pi - interior angle subtracted from K at corner 0,1,2 (vtkCurvatures Gauss)
+    double area;       // triangle area as vtkTriangle::TriangleArea forms it
+    double nn[3];      // unit normal in the face's own vertex order (vtkTriangle::ComputeNormal)
+};
+
+__global__ void __launch_bounds__(128) k_face_records(const float *__restrict__ verts, const uint32_t *__restrict__ faces,
+                                                      int64_t nf, FaceRec *__restrict__ rec) {
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nf) return;
+    const double PI = 3.14159265358979323846;
+    const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
+    const D3 p[3] = { ldv(verts, t[0]), ldv(verts, t[1]), ldv(verts, t[2]) };
+    FaceRec r;
+    {   // ---- vertex normal contribution (TriMesh.cpp:110-127)
+        const D3 a = sub(p[0], p[1]), bb = sub(p[1], p[2]), c = sub(p[2], p[0]);
+        const double l2a = dot(a, a), l2b = dot(bb, bb), l2c = dot(c, c);
+        r.fn[0] = r.fn[1] = r.fn[2] = 0.0; r.w[0] = r.w[1] = r.w[2] = 0.0;
+        if (l2a != 0.0 && l2b != 0.0 && l2c != 0.0) {
+            const D3 fn = cross(a, bb);
+            r.fn[0] = fn.x; r.fn[1] = fn.y; r.fn[2] = fn.z;
+            r.w[0] = 1.0 / (l2a * l2c); r.w[1] = 1.0 / (l2b * l2a); r.w[2] = 1.0 / (l2c * l2b);
+        }
     }
-    return cnt;
+    {   // ---- mixed Voronoi corner areas (TriMesh.cpp:152-188)
+        const D3 ed[3] = { sub(p[2], p[1]), sub(p[0], p[2]), sub(p[1], p[0]) };
+        const D3 cr = cross(ed[0], ed[1]);
+        const double area = 0.5 * sqrt(dot(cr, cr));
+        const double l2[3] = { dot(ed[0], ed[0]), dot(ed[1], ed[1]), dot(ed[2], ed[2]) };
+        const double ew[3] = { l2[0] * (l2[1] + l2[2] - l2[0]), l2[1] * (l2[2] + l2[0] - l2[1]), l2[2] * (l2[0] + l2[1] - l2[2]) };
+        double *ca = r.ca;
+        if (ew[0] <= 0.0) {
+            ca[1] = -0.25 * l2[2] * area / dot(ed[0], ed[2]);
+            ca[2] = -0.25 * l2[1] * area / dot(ed[0], ed[1]);
+            ca[0] = area - ca[1] - ca[2];
+        } else if (ew[1] <= 0.0) {
+            ca[2] = -0.25 * l2[0] * area / dot(ed[1], ed[0]);
+            ca[0] = -0.25 * l2[2] * area / dot(ed[1], ed[2]);
+            ca[1] = area - ca[2] - ca[0];
+        } else if (ew[2] <= 0.0) {
+            ca[0] = -0.25 * l2[1] * area / dot(ed[2], ed[1]);
+            ca[1] = -0.25 * l2[0] * area / dot(ed[2], ed[0]);
+            ca[2] = area - ca[0] - ca[1];
+        } else {
+            const double ewscale = 0.5 * area / (ew[0] + ew[1] + ew[2]);
+            ca[0] = ewscale * (ew[1] + ew[2]); ca[1] = ewscale * (ew[2] + ew[0]); ca[2] = ewscale * (ew[0] + ew[1]);
+        }
+    }
+    {   // ---- Gaussian curvature terms and the face's own unit normal (vtkCurvatures)
+        const D3 g0 = sub(p[1], p[0]), g1 = sub(p[2], p[1]), g2 = sub(p[0], p[2]);
+        r.al[0] = PI - angle_between(g2, g0); r.al[1] = PI - angle_between(g0, g1); r.al[2] = PI - angle_between(g1, g2);
+        const D3 dn = tri_dir(p[0], p[1], p[2]);
+        r.area = 0.5 * sqrt(dot(dn, dn));
+        const D3 nn = unit_or_same(dn);
+        r.nn[0] = nn.x; r.nn[1] = nn.y; r.nn[2] = nn.z;
+    }
+    rec[g] = r;
 }
 
-__global__ void __launch_bounds__(MESH_T) k_mesh_properties(
-        const float *__restrict__ verts, const uint32_t *__restrict__ faces, int64_t nv,
-        const int32_t *__restrict__ off, const int32_t *__restrict__ adj, const uint8_t *__restrict__ keep,
+// Mean curvature, edge pass (vtkCurvatures::GetMeanCurvature): thread (g, ed) owns edge ed of kept face
+// g.  If exactly one other kept face n shares it and n > g, Hf = 3 * len * dihedral / (A_g + A_n) is
+// stored in He[3g+ed] and bit ed of hflag[g] is set; both end points pick it up in the gather.  The
+// neighbour search walks the incident list of an end point that is an original vertex (every face
+// on the edge is in that list); edges between two duplicated vertices feed dropped rows only.
+__global__ void __launch_bounds__(128) k_edge_mean(const float *__restrict__ verts, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
+                                                   const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
+                                                   const uint8_t *__restrict__ keep, const FaceRec *__restrict__ rec,
+                                                   double *__restrict__ He, uint8_t *__restrict__ hflag) {
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nf) return;
+    uint8_t flag = 0;
+    if (__ldg(keep + g)) {
+        const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
+#pragma unroll 1
+        for (int ed = 0; ed < 3; ed++) {
+            const int il = ed, ir = (ed + 1) % 3, io = (ed + 2) % 3;
+            const uint32_t vl = t[il], vr = t[ir];
+            uint32_t a = vl, u = vr;                       // walk a's list, look for u
+            if ((int64_t)a >= nv) { a = vr; u = vl; }
+            if ((int64_t)a >= nv) continue;
+            const int b = __ldg(off + a), e = __ldg(off + a + 1);
+            int cnt = 0, nb = -1;
+            for (int j = b; j < e; j++) {
+                const int h = __ldg(adj + j) >> 2;
+                if (h == (int)g || !__ldg(keep + h)) continue;
+                const uint32_t *th = faces + 3 * (size_t)h;
+                if (__ldg(th) == u || __ldg(th + 1) == u || __ldg(th + 2) == u) { nb = h; cnt++; }
+            }
+            if (cnt != 1 || nb <= (int)g) continue;
+            const D3 ore = ldv(verts, vl), end = ldv(verts, vr), oth = ldv(verts, t[io]);
+            const D3 d0 = tri_dir(ore, end, oth);
+            const D3 nfu = unit_or_same(d0);
+            const double Af0 = 0.5 * sqrt(dot(d0, d0));
+            const FaceRec *rn = rec + nb;
+            D3 nn; nn.x = rn->nn[0]; nn.y = rn->nn[1]; nn.z = rn->nn[2];
+            const double Af = Af0 + rn->area;
+            D3 ev = sub(end, ore);
+            const double len = sqrt(dot(ev, ev));
+            if (len != 0.0) { ev.x /= len; ev.y /= len; ev.z /= len; }
+            const double cs = dot(nfu, nn);
+            const double sn = dot(cross(nfu, nn), ev);
+            double Hf = (sn != 0.0 || cs != 0.0) ? len * atan2(sn, cs) : 0.0;
+            if (Af != 0.0) Hf = Hf / Af * 3.0;
+            He[3*g + ed] = Hf;
+            flag |= (uint8_t)(1u << ed);
+        }
+    }
+    hflag[g] = flag;
+}
+
+// One thread per ORIGINAL vertex: walk the incident (face, corner) list in ascending order -- the order
+// in which the reference's sequential face loop adds to this vertex -- and sum the per-face records.
+__global__ void __launch_bounds__(MESH_T) k_vertex_gather(
+        int64_t nv, const int32_t *__restrict__ off, const int32_t *__restrict__ adj, const uint8_t *__restrict__ keep,
+        const FaceRec *__restrict__ rec, const double *__restrict__ He, const uint8_t *__restrict__ hflag,
         double *__restrict__ vn64, float *__restrict__ vn32, double *__restrict__ pa64, float *__restrict__ pa32,
         double *__restrict__ Hout, double *__restrict__ Kout) {
     const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= nv) return;
     const double PI = 3.14159265358979323846;
-    const bool want_curv = (Hout != nullptr) || (Kout != nullptr);
-    D3 pn; pn.x = pn.y = pn.z = 0.0;
+    double pnx = 0.0, pny = 0.0, pnz = 0.0;
     double parea = 0.0, Hsum = 0.0, Ksum = 2.0 * PI, dA = 0.0;
     int hcnt = 0;
     const int b = __ldg(off + v), e = __ldg(off + v + 1);
     for (int j = b; j < e; j++) {
         const int packed = __ldg(adj + j);
         const int g = packed >> 2, ci = packed & 3;
-        const uint32_t t[3] = { __ldg(faces + 3*(size_t)g), __ldg(faces + 3*(size_t)g + 1), __ldg(faces + 3*(size_t)g + 2) };
-        const D3 p[3] = { ldv(verts, t[0]), ldv(verts, t[1]), ldv(verts, t[2]) };
-        // ---- vertex normal contribution (TriMesh.cpp:110-127)
-        {
-            const D3 a = sub(p[0], p[1]), bb = sub(p[1], p[2]), c = sub(p[2], p[0]);
-            const double l2a = dot(a, a), l2b = dot(bb, bb), l2c = dot(c, c);
-            if (l2a != 0.0 && l2b != 0.0 && l2c != 0.0) {
-                const D3 fn = cross(a, bb);
-                const double sc = ci == 0 ? 1.0 / (l2a * l2c) : (ci == 1 ? 1.0 / (l2b * l2a) : 1.0 / (l2c * l2b));
-                pn.x += fn.x * sc; pn.y += fn.y * sc; pn.z += fn.z * sc;
-            }
-        }
-        // ---- mixed Voronoi corner area (TriMesh.cpp:152-188)
-        {
-            const D3 ed[3] = { sub(p[2], p[1]), sub(p[0], p[2]), sub(p[1], p[0]) };
-            const D3 cr = cross(ed[0], ed[1]);
-            const double area = 0.5 * sqrt(dot(cr, cr));
-            const double l2[3] = { dot(ed[0], ed[0]), dot(ed[1], ed[1]), dot(ed[2], ed[2]) };
-            const double ew[3] = { l2[0] * (l2[1] + l2[2] - l2[0]), l2[1] * (l2[2] + l2[0] - l2[1]), l2[2] * (l2[0] + l2[1] - l2[2]) };
-            double ca[3];
-            if (ew[0] <= 0.0) {
-                ca[1] = -0.25 * l2[2] * area / dot(ed[0], ed[2]);
-                ca[2] = -0.25 * l2[1] * area / dot(ed[0], ed[1]);
-                ca[0] = area - ca[1] - ca[2];
-            } else if (ew[1] <= 0.0) {
-                ca[2] = -0.25 * l2[0] * area / dot(ed[1], ed[0]);
-                ca[0] = -0.25 * l2[2] * area / dot(ed[1], ed[2]);
-                ca[1] = area - ca[2] - ca[0];
-            } else if (ew[2] <= 0.0) {
-                ca[0] = -0.25 * l2[1] * area / dot(ed[2], ed[1]);
-                ca[1] = -0.25 * l2[0] * area / dot(ed[2], ed[0]);
-                ca[2] = area - ca[0] - ca[1];
-            } else {
-                const double ewscale = 0.5 * area / (ew[0] + ew[1] + ew[2]);
-                ca[0] = ewscale * (ew[1] + ew[2]); ca[1] = ewscale * (ew[2] + ew[0]); ca[2] = ewscale * (ew[0] + ew[1]);
-            }
-            parea += ci == 0 ? ca[0] : (ci == 1 ? ca[1] : ca[2]);
-        }
-        if (!want_curv || !__ldg(keep + g)) continue;
-        // ---- mean curvature: edges of g that touch v, in ascending edge index (vtkCurvatures mean)
-        {
-            const int e0 = ci == 0 ? 0 : ci - 1, e1 = ci == 0 ? 2 : ci;   // {ci,(ci+2)%3} sorted
-#pragma unroll 1
-            for (int k = 0; k < 2; k++) {
-                const int ed = k == 0 ? e0 : e1;
-                const int il = ed, ir = (ed + 1) % 3, io = (ed + 2) % 3;
-                const uint32_t u = (il == ci) ? t[ir] : t[il];
-                int nb = -1;
-                const int cnt = edge_neighbours(faces, adj, keep, b, e, g, u, nb);
-                if (cnt != 1 || nb <= g) continue;
-                const D3 ore = p[il], end = p[ir], oth = p[io];
-                const D3 d0 = tri_dir(ore, end, oth);
-                const D3 nf = unit_or_same(d0);
-                const double Af0 = 0.5 * sqrt(dot(d0, d0));
-                const uint32_t *tn = faces + 3 * (size_t)nb;
-                const D3 a0 = ldv(verts, __ldg(tn)), a1 = ldv(verts, __ldg(tn + 1)), a2 = ldv(verts, __ldg(tn + 2));
-                const D3 d1 = tri_dir(a0, a1, a2);
-                const D3 nn = unit_or_same(d1);
-                const double Af = Af0 + 0.5 * sqrt(dot(d1, d1));
-                D3 ev = sub(end, ore);
-                const double len = sqrt(dot(ev, ev));
-                if (len != 0.0) { ev.x /= len; ev.y /= len; ev.z /= len; }
-                const double cs = dot(nf, nn);
-                const double sn = dot(cross(nf, nn), ev);
-                double Hf = (sn != 0.0 || cs != 0.0) ? len * atan2(sn, cs) : 0.0;
-                if (Af != 0.0) Hf = Hf / Af * 3.0;
-                Hsum += Hf; hcnt++;
-            }
-        }
-        // ---- Gaussian curvature: interior angle at v and face area (vtkCurvatures Gauss)
-        {
-            const D3 g0 = sub(p[1], p[0]), g1 = sub(p[2], p[1]), g2 = sub(p[0], p[2]);
-            const double al = ci == 0 ? PI - angle_between(g2, g0) : (ci == 1 ? PI - angle_between(g0, g1) : PI - angle_between(g1, g2));
-            const D3 dn = tri_dir(p[0], p[1], p[2]);
-            dA += 0.5 * sqrt(dot(dn, dn));
-            Ksum -= al;
-        }
+        const FaceRec *r = rec + g;
+        const double w = r->w[ci];
+        pnx += r->fn[0] * w; pny += r->fn[1] * w; pnz += r->fn[2] * w;
+        parea += r->ca[ci];
+        if (!__ldg(keep + g)) continue;
+        // edges of g that touch v, in ascending edge index: {ci, (ci+2)%3} sorted
+        const int e0 = ci == 0 ? 0 : ci - 1, e1 = ci == 0 ? 2 : ci;
+        const unsigned fl = __ldg(hflag + g);
+        if ((fl >> e0) & 1u) { Hsum += He[3*(size_t)g + e0]; hcnt++; }
+        if ((fl >> e1) & 1u) { Hsum += He[3*(size_t)g + e1]; hcnt++; }
+        dA += r->area;
+        Ksum -= r->al[ci];
     }
     {
-        const double l = sqrt(dot(pn, pn));
-        if (l <= 0.0) { pn.x = 1.0; pn.y = 0.0; pn.z = 0.0; }
-        else { const double r = 1.0 / l; pn.x *= r; pn.y *= r; pn.z *= r; }
+        const double l = sqrt(pnx*pnx + pny*pny + pnz*pnz);
+        if (l <= 0.0) { pnx = 1.0; pny = 0.0; pnz = 0.0; }
+        else { const double q = 1.0 / l; pnx *= q; pny *= q; pnz *= q; }
     }
-    if (vn64) { vn64[3*v] = pn.x; vn64[3*v+1] = pn.y; vn64[3*v+2] = pn.z; }
-    if (vn32) { vn32[3*v] = (float)pn.x; vn32[3*v+1] = (float)pn.y; vn32[3*v+2] = (float)pn.z; }
+    if (vn64) { vn64[3*v] = pnx; vn64[3*v+1] = pny; vn64[3*v+2] = pnz; }
+    if (vn32) { vn32[3*v] = (float)pnx; vn32[3*v+1] = (float)pny; vn32[3*v+2] = (float)pnz; }
     if (pa64) pa64[v] = parea;
     if (pa32) pa32[v] = (float)parea;
     if (Hout) Hout[v] = hcnt > 0 ? 0.5 * Hsum / (double)hcnt : 0.0;
     if (Kout) Kout[v] = dA > 0.0 ? 3.0 * Ksum / dA : 0.0;
+}
+
+extern "C" size_t ms_mesh_properties_workspace_bytes(int64_t nv, int64_t nf) {
+    (void)nv;
+    return ms_align((size_t)(nf + 1) * sizeof(FaceRec)) + ms_align((size_t)(3 * nf + 1) * sizeof(double)) + ms_align((size_t)nf + 1) + 1024;
 }
 
 extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
@@ -235,14 +278,28 @@ extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_
                                   const int32_t *csr_off, const int32_t *csr_adj, const uint8_t *keep,
                                   double *vnormals_f64, float *vnormals_f32,
                                   double *pareas_f64, float *pareas_f32,
-                                  double *mean_curv, double *gaus_curv, void *stream) {
+                                  double *mean_curv, double *gaus_curv,
+                                  void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(nv >= 0 && nv <= nv_all && nf >= 0, "ms_mesh_properties: bad sizes");
     MS_REQUIRE(csr_off && csr_adj && keep, "ms_mesh_properties: topology missing (call ms_mesh_topology first)");
+    MS_REQUIRE(ws_bytes >= ms_mesh_properties_workspace_bytes(nv, nf), "ms_mesh_properties: workspace too small");
     if (nv == 0) return 0;
-    MS_K("mesh_properties", (cudaStream_t)stream); k_mesh_properties<<<ms_blocks(nv, MESH_T), MESH_T, 0, (cudaStream_t)stream>>>(
-        verts_all, faces_all, nv, csr_off, csr_adj, keep,
-        vnormals_f64, vnormals_f32, pareas_f64, pareas_f32, mean_curv, gaus_curv);
-    MS_K(NULL, (cudaStream_t)stream);
+    MsArena A(ws, ws_bytes);
+    FaceRec *rec = A.take<FaceRec>(nf + 1);
+    double *He = A.take<double>(3 * nf + 1);
+    uint8_t *hflag = A.take<uint8_t>(nf + 1);
+    const bool want_curv = mean_curv != NULL || gaus_curv != NULL;
+    if (nf > 0) {
+        MS_K("face_records", s); k_face_records<<<ms_blocks(nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, rec);
+        if (mean_curv) { MS_K("edge_mean", s); k_edge_mean<<<ms_blocks(nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, nv, csr_off, csr_adj, keep, rec, He, hflag); }
+        else MS_CUDA(cudaMemsetAsync(hflag, 0, (size_t)nf, s));
+    }
+    (void)want_curv;
+    MS_K("vertex_gather", s);
+    k_vertex_gather<<<ms_blocks(nv, MESH_T), MESH_T, 0, s>>>(nv, csr_off, csr_adj, keep, rec, He, hflag,
+                                                             vnormals_f64, vnormals_f32, pareas_f64, pareas_f32, mean_curv, gaus_curv);
+    MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
 }

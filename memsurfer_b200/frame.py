@@ -64,6 +64,7 @@ class LeafletFrame(object):
         self.csr_adj = torch.empty(max(3 * nf, 1), dtype=torch.int32, device=dev)
         self.keep = torch.empty(max(nf, 1), dtype=torch.uint8, device=dev)
         self.topo_ws = _lib.workspace(L.ms_mesh_topology_workspace_bytes(nv, nf), dev)
+        self.prop_ws = _lib.workspace(L.ms_mesh_properties_workspace_bytes(nv, nf), dev)
         self.vn64 = torch.empty((nv, 3), dtype=torch.float64, device=dev)
         self.vn32 = torch.empty((nv, 3), dtype=torch.float32, device=dev)
         self.pa64 = torch.empty(nv, dtype=torch.float64, device=dev)
@@ -98,7 +99,8 @@ class LeafletFrame(object):
         _lib.check(L.ms_mesh_properties(self.verts.data_ptr(), self.nv_all, self.nv, self.faces.data_ptr(), self.nf,
                                         self.csr_off.data_ptr(), self.csr_adj.data_ptr(), self.keep.data_ptr(),
                                         self.vn64.data_ptr(), self.vn32.data_ptr(), self.pa64.data_ptr(),
-                                        self.pa32.data_ptr(), self.H.data_ptr(), self.K.data_ptr(), st),
+                                        self.pa32.data_ptr(), self.H.data_ptr(), self.K.data_ptr(),
+                                        self.prop_ws.data_ptr(), self.prop_ws.numel(), st),
                    'ms_mesh_properties')
 
     def run_density(self, name, type, sigma, get_nlipids, ids_dev=None, cutoff_sigmas=0.0):

@@ -204,11 +204,12 @@ class TriMesh(object):
         d['pa32'] = torch.empty(nv, dtype=torch.float32, device=dev)
         d['H'] = torch.empty(nv, dtype=torch.float64, device=dev)
         d['K'] = torch.empty(nv, dtype=torch.float64, device=dev)
+        ws = _lib.workspace(L.ms_mesh_properties_workspace_bytes(nv, nf), dev)
         _lib.check(L.ms_mesh_properties(d['verts'].data_ptr(), nv_all, nv, d['faces'].data_ptr(), nf,
                                         d['csr_off'].data_ptr(), d['csr_adj'].data_ptr(), d['keep'].data_ptr(),
                                         d['vn64'].data_ptr(), d['vn32'].data_ptr(), d['pa64'].data_ptr(),
                                         d['pa32'].data_ptr(), d['H'].data_ptr(), d['K'].data_ptr(),
-                                        _lib.stream_ptr(dev)), 'ms_mesh_properties')
+                                        ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_mesh_properties')
         return d
 
     # ---------------------------------------------------------------------- computation of attributes
