@@ -318,19 +318,18 @@ def main():
             for lf in leaflets:
                 m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=device)
                 pn = m.compute_pnormals(18)
-                h2d += m._pset_points.nbytes; d2h += pn.nbytes + m.pnormals_f64.nbytes
+                h2d += m._pset_points.nbytes; d2h += pn.nbytes
                 m.memb_smooth = new_mesh(lf, device)            # host producer's output, injected
                 m.compute_properties('smooth')
                 mesh = m.memb_smooth
                 h2d += sum(a.nbytes for a in mesh._dev['_host'])
                 d2h += sum(mesh.attributes[k].nbytes for k in ('pnormal', 'parea', 'mean_curv', 'gaus_curv'))
-                d2h += sum(mesh.attributes_f64[k].nbytes for k in ('pnormal', 'parea'))
                 for l in ['all'] + list(range(len(FRACTIONS))):
                     Membrane.compute_densities([m], [2], SIGMAS, True, l)
                     if l != 'all':
                         h2d += 4 * int((lf["labels"] == l).sum()) * len(SIGMAS)
-                d2h += sum(v.nbytes for v in m.attributes.values()) * 3      # f32 + f64 twin
-                recs.append([float(mesh.attributes_f64['parea'].sum()), float(mesh.attributes['mean_curv'].mean())])
+                d2h += sum(v.nbytes for v in m.attributes.values())
+                recs.append([float(mesh.attributes['parea'].sum()), float(mesh.attributes['mean_curv'].mean())])
             bytes_io["h2d"], bytes_io["d2h"] = h2d, d2h
             return recs
 

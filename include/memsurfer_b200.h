@@ -153,10 +153,12 @@ int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream);
 /* ---------------------------------------------------------------- per-frame summaries
  * No reference counterpart: the reference analyses one frame per process (examples/ex_3lipid.py:78)
  * and writes whole fields to .vtp (membrane.py:319-344).  When trajectory frames are sharded over
- * GPUs, ranks exchange only this record per field: out4 (device, 4 doubles) = {sum, sum|x|, min,
- * max} of x (n) f64, reduced in a fixed order (bit-reproducible).                               */
-size_t ms_field_summary_workspace_bytes(void);
-int ms_field_summary(const double *x, int64_t n, double *out4, void *ws, size_t ws_bytes, void *stream);
+ * GPUs, ranks exchange only this record per field: out4 (device, nfields x 4 doubles) = {sum, sum|x|,
+ * min, max} of each of the nfields (<= 64) fp64 fields of n values, fields = HOST array of device
+ * pointers; fixed reduction order (bit-reproducible); two launches for the whole batch.           */
+size_t ms_field_summary_workspace_bytes(int nfields);
+int ms_field_summary(const double *const *fields, int nfields, int64_t n, double *out4,
+                     void *ws, size_t ws_bytes, void *stream);
 
 /* ---------------------------------------------------------------- diagnostics
  * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).

@@ -186,30 +186,39 @@ __device__ __forceinline__ Sum4 sum4_block(Sum4 v, Sum4 *sm) {
     }
     return sm[0];
 }
-__global__ void __launch_bounds__(SUM_T) k_summary_partial(const double *__restrict__ x, int64_t n, Sum4 *part) {
+#define SUM_MAXF 64
+struct SumFields { const double *p[SUM_MAXF]; };
+// grid (blocks, nfields): field y of the batch
+__global__ void __launch_bounds__(SUM_T) k_summary_partial(SumFields f, int64_t n, Sum4 *part) {
     __shared__ Sum4 sm[SUM_T];
+    const double *__restrict__ x = f.p[blockIdx.y];
     Sum4 v; v.s = 0.0; v.a = 0.0; v.mn = INFINITY; v.mx = -INFINITY;
     for (int64_t i = (int64_t)blockIdx.x * SUM_T + threadIdx.x; i < n; i += (int64_t)gridDim.x * SUM_T) {
         const double d = x[i]; v.s += d; v.a += fabs(d); v.mn = fmin(v.mn, d); v.mx = fmax(v.mx, d);
     }
     v = sum4_block(v, sm);
-    if (threadIdx.x == 0) part[blockIdx.x] = v;
+    if (threadIdx.x == 0) part[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = v;
 }
 __global__ void __launch_bounds__(SUM_T) k_summary_final(const Sum4 *__restrict__ part, int nb, double *out4) {
     __shared__ Sum4 sm[SUM_T];
     Sum4 v; v.s = 0.0; v.a = 0.0; v.mn = INFINITY; v.mx = -INFINITY;
-    for (int i = threadIdx.x; i < nb; i += SUM_T) v = sum4_merge(v, part[i]);
+    for (int i = threadIdx.x; i < nb; i += SUM_T) v = sum4_merge(v, part[(size_t)blockIdx.x * nb + i]);
     v = sum4_block(v, sm);
-    if (threadIdx.x == 0) { out4[0] = v.s; out4[1] = v.a; out4[2] = v.mn; out4[3] = v.mx; }
+    if (threadIdx.x == 0) { double *o = out4 + 4 * (size_t)blockIdx.x; o[0] = v.s; o[1] = v.a; o[2] = v.mn; o[3] = v.mx; }
 }
-extern "C" size_t ms_field_summary_workspace_bytes(void) { return ms_align(SUM_BLOCKS * sizeof(Sum4)); }
-extern "C" int ms_field_summary(const double *x, int64_t n, double *out4, void *ws, size_t ws_bytes, void *stream) {
+extern "C" size_t ms_field_summary_workspace_bytes(int nfields) {
+    return ms_align((size_t)SUM_BLOCKS * (size_t)(nfields < 1 ? 1 : nfields) * sizeof(Sum4));
+}
+extern "C" int ms_field_summary(const double *const *fields, int nfields, int64_t n, double *out4,
+                                void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(x && out4 && n > 0, "ms_field_summary: bad arguments");
-    MS_REQUIRE(ws_bytes >= ms_field_summary_workspace_bytes(), "ms_field_summary: workspace too small");
+    MS_REQUIRE(fields && out4 && n > 0 && nfields >= 1 && nfields <= SUM_MAXF, "ms_field_summary: need 1..%d fields of n > 0 values", SUM_MAXF);
+    MS_REQUIRE(ws_bytes >= ms_field_summary_workspace_bytes(nfields), "ms_field_summary: workspace too small");
+    SumFields f;
+    for (int i = 0; i < nfields; i++) { MS_REQUIRE(fields[i] != NULL, "ms_field_summary: field %d is NULL", i); f.p[i] = fields[i]; }
     int nb = ms_blocks(n, SUM_T); if (nb > SUM_BLOCKS) nb = SUM_BLOCKS;
-    MS_K("summary_partial", s); k_summary_partial<<<nb, SUM_T, 0, s>>>(x, n, (Sum4*)ws);
-    MS_K("summary_final", s); k_summary_final<<<1, SUM_T, 0, s>>>((const Sum4*)ws, nb, out4);
+    MS_K("summary_partial", s); k_summary_partial<<<dim3(nb, nfields), SUM_T, 0, s>>>(f, n, (Sum4*)ws);
+    MS_K("summary_final", s); k_summary_final<<<nfields, SUM_T, 0, s>>>((const Sum4*)ws, nb, out4);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;

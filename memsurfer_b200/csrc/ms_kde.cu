@@ -384,21 +384,24 @@ __global__ void __launch_bounds__(RED_T) k_kde_combine(const double *__restrict_
     for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
     if (threadIdx.x == 0) bsum[blockIdx.x] = sm[0];
 }
-__global__ void __launch_bounds__(RED_T) k_kde_total(const double *__restrict__ bsum, int64_t nb, double *total) {
+// get_counts: every block re-reduces the nb block sums in the same fixed order (a few KB from L2;
+// deterministic, and no separate single-block reduction launch), then scales its 256 values
+__global__ void __launch_bounds__(RED_T) k_kde_emit(const double *__restrict__ dens, int64_t nv, const double *__restrict__ bsum, int64_t nb,
+                                                    double npoints, double *__restrict__ o64, float *__restrict__ o32) {
     __shared__ double sm[RED_T];
-    double s = 0.0;
-    for (int64_t i = threadIdx.x; i < nb; i += RED_T) s += bsum[i];
-    sm[threadIdx.x] = s;
-    __syncthreads();
-    for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
-    if (threadIdx.x == 0) *total = sm[0];
-}
-__global__ void __launch_bounds__(256) k_kde_emit(const double *__restrict__ dens, int64_t nv, const double *total, double npoints,
-                                                  double *__restrict__ o64, float *__restrict__ o32) {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double scale = 1.0;
+    if (bsum) {
+        double s = 0.0;
+        for (int64_t i = threadIdx.x; i < nb; i += RED_T) s += bsum[i];
+        sm[threadIdx.x] = s;
+        __syncthreads();
+        for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+        scale = npoints / sm[0];
+    }
+    const int64_t j = (int64_t)blockIdx.x * RED_T + threadIdx.x;
     if (j >= nv) return;
     double d = dens[j];
-    if (total) d *= npoints / *total;
+    if (bsum) d *= scale;
     if (o64) o64[j] = d;
     if (o32) o32[j] = (float)d;
 }
@@ -678,9 +681,7 @@ extern "C" int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_
     if (rc) return rc;
     const int nb = ms_blocks(nv, RED_T);
     MS_K("kde_combine", s); k_kde_combine<<<nb, RED_T, 0, s>>>(c.partial, nv, c.nsplit, (double)c.sfactor * (1.0 / (double)nv), c.dens, c.bsum);
-    double *total = c.bsum + nb;
-    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(c.bsum, nb, total); }
-    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(c.dens, nv, get_counts ? total : NULL, (double)c.p.ns, density_f64, density_f32);
+    MS_K("kde_emit", s); k_kde_emit<<<nb, RED_T, 0, s>>>(c.dens, nv, get_counts ? c.bsum : NULL, nb, (double)c.p.ns, density_f64, density_f32);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
@@ -734,9 +735,7 @@ extern "C" int ms_kde_select(const double *raw, int64_t nv, int nlabels, const u
     double *dens = A.take<double>(nv), *bsum = A.take<double>(nv / RED_T + 2);
     const int nb = ms_blocks(nv, RED_T);
     MS_K("kde_select", s); k_kde_select<<<nb, RED_T, 0, s>>>(raw, nv, nlabels, mask, 1.0 / (double)nv, dens, bsum);
-    double *total = bsum + nb;
-    if (get_counts) { MS_K("kde_total", s); k_kde_total<<<1, RED_T, 0, s>>>(bsum, nb, total); }
-    MS_K("kde_emit", s); k_kde_emit<<<ms_blocks(nv, 256), 256, 0, s>>>(dens, nv, get_counts ? total : NULL, n_selected, density_f64, density_f32);
+    MS_K("kde_emit", s); k_kde_emit<<<nb, RED_T, 0, s>>>(dens, nv, get_counts ? bsum : NULL, nb, n_selected, density_f64, density_f32);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;

@@ -39,31 +39,36 @@ __global__ void __launch_bounds__(256) k_edge_weights(const int32_t *__restrict_
     wkey[e] = key;
 }
 
-__global__ void __launch_bounds__(256) k_orient_init(int64_t m, unsigned *link, unsigned long long *best, int *hook) {
+__global__ void __launch_bounds__(256) k_orient_init(int64_t m, unsigned *link, unsigned long long *best, int *hook, uint8_t *alive) {
     const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= m) return;
-    link[v] = (unsigned)v; best[v] = NOBEST; hook[v] = -1;
+    link[v] = (unsigned)v; best[v] = NOBEST; hook[v] = -1; alive[v] = 1;
 }
 
-// every component records its minimum outgoing edge: key = weight bits << 32 | edge id (a*k1+j)
+// every component records its minimum outgoing edge: key = weight bits << 32 | edge id (a*k1+j).
+// A point whose stored edges are all internal to its component can never contribute again (components
+// only grow): it is marked dead and skipped in later rounds, so the work shrinks geometrically.
 __global__ void __launch_bounds__(256) k_min_edge(const int32_t *__restrict__ nbr, int64_t m, int k1,
                                                   const unsigned *__restrict__ wkey, const unsigned *__restrict__ link,
-                                                  unsigned long long *best) {
+                                                  unsigned long long *best, uint8_t *alive) {
     const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (a >= m) return;
+    if (a >= m || !alive[a]) return;
     const int ca = lk_parent(link[a]);
     unsigned long long mine = NOBEST;
+    bool any = false;
     for (int j = 0; j < k1; j++) {
         const unsigned w = wkey[a * k1 + j];
         if (w == NOEDGE) continue;
         const int b = nbr[a * k1 + j];
         const int cb = lk_parent(link[b]);
         if (cb == ca) continue;
+        any = true;
         const unsigned long long key = ((unsigned long long)w << 32) | (unsigned long long)(a * k1 + j);
         if (key < mine) mine = key;
         atomicMin(best + cb, key);
     }
     if (mine != NOBEST) atomicMin(best + ca, mine);
+    if (!any) alive[a] = 0;
 }
 
 // roots pick their hook: root r joins the component at the other end of its minimum edge; when two
@@ -155,7 +160,7 @@ __global__ void k_source_flip(const unsigned long long *srckey, const double *nr
 }
 
 extern "C" size_t ms_orient_workspace_bytes(int64_t m, int k1) {
-    return ms_align((size_t)m * k1 * 4) + ms_align((size_t)m * 4) * 2 + ms_align((size_t)m * 8) + 4096;
+    return ms_align((size_t)m * k1 * 4) + ms_align((size_t)m * 4) * 2 + ms_align((size_t)m * 8) + ms_align((size_t)m) + 4096;
 }
 
 extern "C" int ms_orient_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
@@ -169,25 +174,30 @@ extern "C" int ms_orient_normals(const float *points_all, int64_t m, const int32
     unsigned *link = A.take<unsigned>(m);
     int *hook = A.take<int>(m);
     unsigned long long *best = A.take<unsigned long long>(m);
+    uint8_t *alive = A.take<uint8_t>(m);
     unsigned long long *srckey = A.take<unsigned long long>(4);       // [0] key, [1] flip0 (int), [2] counters
     int *flip0 = (int*)(srckey + 1);
     int *counters = (int*)(srckey + 2);                               // [0] hooks this round, [1] unoriented
     MS_CUDA(cudaMemsetAsync(srckey, 0, 4 * sizeof(unsigned long long), s));
     const int nb = ms_blocks(m, 256);
     MS_K("edge_weights", s); k_edge_weights<<<ms_blocks(m * k1, 256), 256, 0, s>>>(nbr, m, k1, normals, wkey);
-    MS_K("orient_init", s); k_orient_init<<<nb, 256, 0, s>>>(m, link, best, hook);
+    MS_K("orient_init", s); k_orient_init<<<nb, 256, 0, s>>>(m, link, best, hook, alive);
     MS_K("find_source", s); k_find_source<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, srckey);
     MS_K("source_flip", s); k_source_flip<<<1, 1, 0, s>>>(srckey, normals, flip0);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
-    for (int round = 0; round < 40; round++) {
+    // Boruvka needs at most ceil(log2 m) rounds (every round at least halves the number of components of
+    // a connected graph).  The hook counter is read back only every other round after the third one:
+    // a round without any hook is a cheap no-op, a host synchronisation is not.
+    for (int round = 0; round < 64; round++) {
         MS_CUDA(cudaMemsetAsync(counters, 0, sizeof(int), s));
-        MS_K("min_edge", s); k_min_edge<<<nb, 256, 0, s>>>(nbr, m, k1, wkey, link, best);
+        MS_K("min_edge", s); k_min_edge<<<nb, 256, 0, s>>>(nbr, m, k1, wkey, link, best, alive);
         MS_K("hook", s); k_hook<<<nb, 256, 0, s>>>(nbr, m, k1, normals, link, best, hook, counters);
         MS_K("apply_hooks", s); k_apply_hooks<<<nb, 256, 0, s>>>(m, link, hook, best);
         MS_K("compress", s); k_compress<<<nb, 256, 0, s>>>(m, link);
         MS_K(NULL, s);
         MS_LAUNCH_CHECK();
+        if (round < 3 || (round & 1) == 0) continue;
         int nh = 0;
         MS_CUDA(cudaMemcpyAsync(&nh, counters, sizeof(int), cudaMemcpyDeviceToHost, s));
         MS_CUDA(cudaStreamSynchronize(s));

@@ -75,7 +75,7 @@ class LeafletFrame(object):
         self.kde_ws = _lib.workspace(max(L.ms_kde_workspace_bytes(nv, 0), L.ms_kde_labels_workspace_bytes(nv, nl)), dev)
         self.kde_sel_ws = _lib.workspace(L.ms_kde_select_workspace_bytes(nv), dev)
         self.kde_raw = torch.empty((nl, nv), dtype=torch.float64, device=dev)
-        self.sum_ws = _lib.workspace(L.ms_field_summary_workspace_bytes(), dev)
+        self.sum_ws = _lib.workspace(L.ms_field_summary_workspace_bytes(24), dev)
         self.densities = {}
         self.pnormals32 = self.pnormals64 = None
         self.info = {}
@@ -195,13 +195,18 @@ class LeafletFrame(object):
     def summary(self):
         """(F,4) f64 device tensor: {sum, sum|x|, min, max} of parea, mean_curv, gaus_curv and every
         density field (sorted by name)."""
+        import ctypes as C
         L = _lib.lib()
         st = _lib.stream_ptr(self.device)
         fields = [self.pa64, self.H, self.K] + [self.densities[k][0] for k in sorted(self.densities)]
-        out = torch.empty((len(fields), 4), dtype=torch.float64, device=self.device)
-        for i, f in enumerate(fields):
-            _lib.check(L.ms_field_summary(f.data_ptr(), f.numel(), out[i].data_ptr(), self.sum_ws.data_ptr(),
-                                          self.sum_ws.numel(), st), 'ms_field_summary')
+        nf = len(fields)
+        out = torch.empty((nf, 4), dtype=torch.float64, device=self.device)
+        need = L.ms_field_summary_workspace_bytes(nf)
+        if self.sum_ws.numel() < need:
+            self.sum_ws = _lib.workspace(need, self.device)
+        ptrs = (C.c_void_p * nf)(*[f.data_ptr() for f in fields])
+        _lib.check(L.ms_field_summary(ptrs, nf, self.nv, out.data_ptr(), self.sum_ws.data_ptr(), self.sum_ws.numel(), st),
+                   'ms_field_summary')
         return out
 
     def summary_names(self):

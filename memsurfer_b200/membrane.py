@@ -106,7 +106,8 @@ class Membrane(object):
         self._pset_points = _lib.pinned_copy(self.points, np.float32)
 
         self.pnormals = None
-        self.pnormals_f64 = None
+        self._pnormals_f64 = None
+        self._pnormals_f64_dev = None
         self.spoints = None
         self.ppoints = None
         self.surf_poisson = None
@@ -116,6 +117,14 @@ class Membrane(object):
         self.attributes = {}
         self.properties = {}
         self.info = {}
+
+    @property
+    def pnormals_f64(self):
+        """fp64 twin of `pnormals` (not part of the reference API; fetched from the device on first use)."""
+        if self._pnormals_f64 is None and self._pnormals_f64_dev is not None:
+            self._pnormals_f64 = _lib.d2h(self._pnormals_f64_dev)
+            self._pnormals_f64_dev = None
+        return self._pnormals_f64
 
     # ---------------------------------------------------------------------- host helpers
     def fit_points_to_box_xy(self):
@@ -145,7 +154,7 @@ class Membrane(object):
             LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
                            "Some normals may be incorrectly oriented!")
         self.pnormals = _lib.d2h(o32)
-        self.pnormals_f64 = _lib.d2h(o64)
+        self._pnormals_f64_dev, self._pnormals_f64 = o64, None      # fp64 twin stays in HBM until asked for
         if self.pnormals.shape != (self.npoints, 3):
             raise ValueError(f'PointSet computed incorrect normals (got {self.pnormals.size} values')
         return self.pnormals
@@ -201,7 +210,14 @@ class Membrane(object):
     def _label_table(self):
         """Distinct label values and the per-point index into them (computed once)."""
         if getattr(self, '_label_values', None) is None:
-            self._label_values, self._label_inverse = np.unique(self.labels, return_inverse=True)
+            lab = self.labels
+            if lab.dtype.kind in 'iu' and lab.size > 0 and lab.min() >= 0 and lab.max() < 65536:
+                # small non-negative integers: counting is much cheaper than the sort inside np.unique
+                present = np.bincount(lab) > 0
+                self._label_values = np.flatnonzero(present).astype(lab.dtype)
+                self._label_inverse = (np.cumsum(present) - 1)[lab]
+            else:
+                self._label_values, self._label_inverse = np.unique(lab, return_inverse=True)
         return self._label_values, self._label_inverse
 
     def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=None):

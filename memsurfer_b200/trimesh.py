@@ -20,6 +20,31 @@ from . import _lib, synth
 LOGGER = logging.getLogger(__name__)
 
 
+class LazyF64(dict):
+    """name -> fp64 twin of a float32 result.  The values stay in HBM until somebody asks for them:
+    `park(name, tensor)` registers the device tensor, the first lookup copies it to the host."""
+
+    def __init__(self):
+        super().__init__()
+        self._parked = {}
+
+    def park(self, name, tensor):
+        self._parked[name] = tensor
+        super().pop(name, None)
+
+    def __missing__(self, name):
+        t = self._parked.pop(name)            # KeyError if unknown, like a dict
+        v = _lib.d2h(t)
+        self[name] = v
+        return v
+
+    def __contains__(self, name):
+        return super().__contains__(name) or name in self._parked
+
+    def keys(self):
+        return list(super().keys()) + list(self._parked.keys())
+
+
 class TriMesh(object):
     """Triangular mesh (2D or 3D vertices) with GPU-computed per-vertex properties."""
 
@@ -54,7 +79,7 @@ class TriMesh(object):
         self._delaunay = None            # (dfaces, doffs) of the periodic Delaunay (host producer)
 
         self.attributes = {}
-        self.attributes_f64 = {}
+        self.attributes_f64 = LazyF64()   # fp64 twins, fetched from the device on first access
         self._fields = {}                # KDE fields cached by name (TriMesh_kde.cpp:455-460)
         self._label_index = None         # optional per-vertex integer labels (label-fused KDE)
         self._nlabels = 0
@@ -220,7 +245,7 @@ class TriMesh(object):
             return self.attributes[key]
         d = self.properties_device()
         self.attributes[key] = _lib.d2h(d['vn32'])
-        self.attributes_f64[key] = _lib.d2h(d['vn64'])
+        self.attributes_f64.park(key, d['vn64'])
         return self.attributes[key]
 
     def compute_pointareas(self):
@@ -230,7 +255,7 @@ class TriMesh(object):
             return self.attributes[key]
         d = self.properties_device()
         self.attributes[key] = _lib.d2h(d['pa32'])
-        self.attributes_f64[key] = _lib.d2h(d['pa64'])
+        self.attributes_f64.park(key, d['pa64'])
         return self.attributes[key]
 
     def compute_curvatures(self):
@@ -366,7 +391,7 @@ class TriMesh(object):
         o64, o32 = self.density_select_device(raw, select, get_nlipids)
         dens = _lib.d2h(o32)
         self._fields[name] = dens
-        self.attributes_f64[name] = _lib.d2h(o64)
+        self.attributes_f64.park(name, o64)
         if LOGGER.isEnabledFor(logging.INFO):
             LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         return dens
@@ -390,7 +415,7 @@ class TriMesh(object):
         o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
         dens = _lib.d2h(o32)
         self._fields[name] = dens
-        self.attributes_f64[name] = _lib.d2h(o64)
+        self.attributes_f64.park(name, o64)
         if LOGGER.isEnabledFor(logging.INFO):
             LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         return dens
