@@ -41,7 +41,7 @@ FRACTIONS = [0.4, 0.3, 0.3]
 METRIC = "membrane_frames_per_sec"
 # fp64 FLOP per evaluated 2-D periodic pair / algorithmic bytes per vertex
 FLOP_PER_PAIR_2D = 32.0
-FP64_INSTR_PER_PAIR = {"kde_pairs": 15, "kde_cells": 11}
+FP64_INSTR_PER_PAIR = {"kde_pairs": 15, "kde_cells": 11, "kde_groups": 11}
 GEOM_BYTES_PER_VERTEX = 84.0
 
 
@@ -364,7 +364,7 @@ def main():
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     pairs_allpairs_equiv = sum(fr.pairs_per_run(SIGMAS) for fr in frames)
     pairs_step = sum(fr.evaluated_pairs(SIGMAS, cutoff_sigmas=args.kde_cutoff) for fr in frames)
-    kname = "kde_cells" if prof.get("kde_cells", {"ms": 0.0})["ms"] > prof.get("kde_pairs", {"ms": 0.0})["ms"] else "kde_pairs"
+    kname = max(("kde_groups", "kde_cells", "kde_pairs"), key=lambda k: prof.get(k, {"ms": 0.0})["ms"])
     kp = prof.get(kname, {"launches": 0, "ms": 0.0})
     roof = None
     if kp["launches"]:

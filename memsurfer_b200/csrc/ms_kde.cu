@@ -27,6 +27,7 @@
 //     independent DFMA chains.
 #include "ms_common.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 #define KDE_STAGE_BYTES 16384    // all-pairs: bytes per shared-memory stage (1024 double2 / 512 double4)
 #define CELL_STAGE_BYTES 8192    // cell list: bytes per stage
@@ -367,8 +368,314 @@ __global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::
     }
 }
 
+// ------------------------------------------------------------------ target groups (cut-off variant, current)
+// Sources live in FINE cells (pitch ~rcut/8) sorted by (label, cell).  Targets are sorted by
+// (strip of B fine rows, fine column, index) and cut into GROUPS of 64 consecutive targets of one
+// strip: every lane slot is used (the fixed cell/tile versions wasted 12-25 % of the lanes).  The
+// window of a group is the Minkowski sum box(group) (+) disc(rcut) at the fine-cell pitch: per fine row
+// one contiguous range of the sorted source array whose half-width follows the circle.
+// Every WARP is an autonomous worker: it draws (group, label, half-of-the-rows) items from an atomic
+// counter, keeps its 64 targets in registers (2 per lane), plans its own batches (lane = row piece:
+// two offset loads + a warp scan), stages them with cp.async.bulk into its private double buffer
+// (one mbarrier per stage, no CTA-wide barrier anywhere) and adds its sums with one fp64 atomicAdd per
+// target: with exactly two addends per output (the two halves) onto zero the result is independent of
+// their order, i.e. bit-reproducible.  The 256-entry exp2 table is replicated 16x (entry e of copy k
+// at double index e*16+k, lane l reads copy l&15): every lane of a half-warp owns its bank pair, so
+// the table LDS.64 costs 2 wavefronts instead of ~6.5 (ncu: 4.1-way conflicts in k_kde_cells).
+#ifndef GR_NW
+#define GR_NW 12                 // warps per CTA
+#endif
+#ifndef GR_MINB
+#define GR_MINB 2                // CTAs per SM
+#endif
+#ifndef GR_UNROLL
+#define GR_UNROLL 2
+#endif
+#define GR_THREADS (GR_NW * 32)
+#define GR_CAP 128               // sources per stage (per warp)
+#define GR_TGT 64                // targets per group
+#define GR_TAB_BYTES (KDE_TAB * 16 * 8)
+
+struct KdeTiling {
+    KdeGrid gs;               // fine source grid; gs.m is unused
+    int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
+    double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
+};
+struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; };      // targets [t0,t1), fine columns [ca,cb]
+
+// piece q of the window of a box of fine columns [ca,cb] in strip TY: row q>>1 (bottom-up), part q&1
+// (1 = the part of the row that wrapped around the period).  code = 3*(sx+1)+(sy+1): the image shift
+// (sx*wx, sy*wy) to add to the targets.
+__device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, int ca, int cb, int q, const int32_t *__restrict__ sstart,
+                                                int &off, int &cnt, int &code) {
+    off = 0; cnt = 0; code = 4;
+    const KdeGrid &g = T.gs;
+    const int rows = T.B + 2 * T.mf;
+    const int ri = q >> 1, part = q & 1;
+    if (ri >= rows) return;
+    const int gap = ri < T.mf ? T.mf - 1 - ri : (ri >= T.mf + T.B ? ri - T.mf - T.B : 0);   // full fine rows between row and strip
+    const double gy = (double)gap * T.cys;
+    const double h2 = T.rc2 - gy * gy;
+    if (h2 <= 0.0) return;
+    const int mx = (int)ceil(sqrt(h2) / T.cxs);
+    int row = TY * T.B - T.mf + ri, sy = 0;
+    if (row < 0) { if (!g.periodic) return; row += g.ncy; sy = 1; }
+    else if (row >= g.ncy) { if (!g.periodic) return; row -= g.ncy; sy = -1; }
+    int xa = ca - mx, xb = cb + mx, sx = 0;
+    if (!g.periodic) {
+        if (part) return;
+        xa = max(xa, 0); xb = min(xb, g.ncx - 1);
+    } else if (xa < 0) {
+        if (part == 0) { xa += g.ncx; xb = g.ncx - 1; sx = 1; } else { xa = 0; }
+    } else if (xb >= g.ncx) {
+        if (part == 0) { xb = g.ncx - 1; } else { xa = 0; xb -= g.ncx; sx = -1; }
+    } else if (part) return;
+    if (xa > xb) return;
+    off = __ldg(sstart + row * g.ncx + xa);
+    cnt = __ldg(sstart + row * g.ncx + xb + 1) - off;
+    code = 3 * (sx + 1) + (sy + 1);
+}
+
+// 2^-(r/256) = sc * p with the lane-private table copy (tbase = shared address of the table + 8*(lane&15)).
+// !ECLAMP: the table holds T'[i] = T[i] with (i << 12) pre-added to its high word, so that the exponent
+// shift is ONE integer multiply-add: hi(T') - (n << 12) = hi(T) - ((n >> 8) << 20)  (n < 2^18 guaranteed
+// by the host: the window keeps r below 256*1000).  Per pair: LOP3 + IMAD + LDS.64 + IMAD.
+template <bool ECLAMP>
+__device__ __forceinline__ double kde_scale_t(int n, uint32_t tbase) {
+    int lo, hi;
+    asm("{ .reg .b32 i, a; and.b32 i, %2, 255; mad.lo.u32 a, i, 128, %3; ld.shared.v2.b32 {%0, %1}, [a]; }"
+        : "=r"(lo), "=r"(hi) : "r"(n), "r"(tbase));
+    if (ECLAMP) hi -= min(n >> 8, 1021) << 20;
+    else        hi -= n << 12;
+    return __hiloint2double(hi, lo);
+}
+template <bool ECLAMP>
+__device__ __forceinline__ void kde_term_t(double r, uint32_t tbase, double &acc) {
+    const double t = r + KDE_MAGIC;
+    const int n = __double2loint(t);
+    const double f = r - (t - KDE_MAGIC);
+    double p = fma(KDE_C3, f, KDE_C2);
+    p = fma(p, f, KDE_C1);
+    p = fma(p, f, 1.0);
+    acc = fma(kde_scale_t<ECLAMP>(n, tbase), p, acc);
+}
+
+template <int DIM, bool CLAMP, int R>
+__device__ __forceinline__ void kde_accumulate_t(const typename SrcT<DIM>::type *__restrict__ S, int cnt, uint32_t tabl,
+                                                 const double (&tx)[R], const double (&ty)[R], const double (&tz)[R], double (&acc)[R]) {
+    constexpr int kUnroll = GR_UNROLL;
+#pragma unroll kUnroll
+    for (int i = 0; i < cnt; i++) {
+        const typename SrcT<DIM>::type sp = S[i];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const double dx = sp.x - tx[r], dy = sp.y - ty[r];
+            double r2 = fma(dy, dy, dx * dx);
+            if (DIM == 3) { const double dz = ((const double*)&sp)[2] - tz[r]; r2 = fma(dz, dz, r2); }
+            if (CLAMP) r2 = r2 < KDE_RMAX ? r2 : KDE_RMAX;
+            kde_term_t<CLAMP>(r2, tabl, acc[r]);
+        }
+    }
+}
+
+// ---- groups of 64 consecutive targets per strip
+__global__ void __launch_bounds__(128) k_kde_group_count(const int32_t *__restrict__ tstart, int ncx, int nty, int32_t *ng) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < nty) ng[s] = (tstart[(s + 1) * ncx] - tstart[s * ncx] + GR_TGT - 1) / GR_TGT;
+}
+__global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restrict__ tstart, const int32_t *__restrict__ tcell,
+                                                        const int32_t *__restrict__ tperm, int ncx, int nty,
+                                                        const int32_t *__restrict__ gstart, KdeGroup *groups) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= gstart[nty]) return;
+    int lo = 0, hi = nty;                       // largest s with gstart[s] <= g
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (gstart[mid] <= g) lo = mid; else hi = mid; }
+    const int s = lo, b = tstart[s * ncx], e = tstart[(s + 1) * ncx];
+    KdeGroup G;
+    G.t0 = b + (g - gstart[s]) * GR_TGT; G.t1 = min(G.t0 + GR_TGT, e); G.strip = s;
+    G.ca = tcell[tperm[G.t0]] % ncx; G.cb = tcell[tperm[G.t1 - 1]] % ncx;
+    G.pad0 = G.pad1 = G.pad2 = 0;
+    groups[g] = G;
+}
+
+// ---- per-warp batch planner: the warp caches 32 consecutive pieces (lane = piece) and hands out runs of
+// them that fit one stage and share one image shift; a piece larger than a stage is sliced
+struct KdePlanState { int pbase, pos, intra, c_off, c_cnt, c_code; };
+struct KdeBatch { int total, code, take_off, take_cnt, dst; };
+
+__device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling &T, int TY, int ca, int cb, int q_hi,
+                                              const int32_t *__restrict__ sstart, int lane, KdeBatch &b) {
+    for (;;) {
+        if (st.pos >= 32) {
+            st.pbase += 32; st.pos = 0; st.intra = 0;
+            if (st.pbase >= q_hi) return false;
+            kde_group_piece(T, TY, ca, cb, st.pbase + lane, sstart, st.c_off, st.c_cnt, st.c_code);
+            if (st.pbase + lane >= q_hi) st.c_cnt = 0;
+        }
+        const int eff = lane < st.pos ? 0 : (lane == st.pos ? st.c_cnt - st.intra : st.c_cnt);
+        const unsigned ne = __ballot_sync(0xffffffffu, eff > 0);
+        if (ne == 0u) { st.pos = 32; continue; }
+        const int first = __ffs(ne) - 1;
+        const int code = __shfl_sync(0xffffffffu, st.c_code, first);
+        int pre = eff;                                   // inclusive prefix sum of the remaining piece sizes
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += v; }
+        const unsigned bad = __ballot_sync(0xffffffffu, eff > 0 && (st.c_code != code || pre > GR_CAP));
+        const int nfit = bad ? __ffs(bad) - 1 : 32;
+        b.code = code; b.take_cnt = 0; b.dst = pre - eff;
+        b.take_off = st.c_off + (lane == st.pos ? st.intra : 0);
+        if (nfit <= first) {                             // the first non-empty piece alone overflows a stage: take a slice
+            if (lane == first) b.take_cnt = GR_CAP;
+            b.total = GR_CAP;
+            if (first == st.pos) st.intra += GR_CAP; else { st.pos = first; st.intra = GR_CAP; }
+        } else {
+            if (lane < nfit) b.take_cnt = eff;
+            b.total = __shfl_sync(0xffffffffu, pre, nfit - 1);
+            st.pos = nfit; st.intra = 0;
+        }
+        return true;
+    }
+}
+
+// lane 0 issues the copies of every lane's piece (a cp.async.bulk is a one-thread instruction: spread over
+// the lanes the compiler serialises it anyway and leaves the warp split for the rest of the loop)
+template <class S>
+__device__ __forceinline__ void kde_issue_batch(const KdeBatch &b, S *stage, const S *__restrict__ src, uint64_t *bar, int lane) {
+    unsigned m = __ballot_sync(0xffffffffu, b.take_cnt > 0);
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)b.total * (uint32_t)sizeof(S));
+    while (m) {
+        const int i = __ffs(m) - 1; m &= m - 1;
+        const int off = __shfl_sync(0xffffffffu, b.take_off, i), cnt = __shfl_sync(0xffffffffu, b.take_cnt, i);
+        const int dst = __shfl_sync(0xffffffffu, b.dst, i);
+        if (lane == 0) bulk_g2s(stage + dst, src + off, (uint32_t)cnt * (uint32_t)sizeof(S), bar);
+    }
+    __syncwarp();
+}
+
+template <int DIM, bool CLAMP>
+__global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typename SrcT<DIM>::type *__restrict__ tgt, const int32_t *__restrict__ tstart,
+                                                                   const int32_t *__restrict__ tperm, const KdeGroup *__restrict__ groups,
+                                                                   const int32_t *__restrict__ gtotal,
+                                                                   const typename SrcT<DIM>::type *__restrict__ src, const int32_t *__restrict__ sstart_all,
+                                                                   int nlabels, int64_t out_stride, KdeTiling T, unsigned *counter,
+                                                                   double *__restrict__ out_all) {
+    typedef typename SrcT<DIM>::type S;
+    extern __shared__ __align__(128) unsigned char gr_smem[];
+    double *tab = (double*)gr_smem;                                             // [KDE_TAB][16]
+    S *buf_all = (S*)(gr_smem + GR_TAB_BYTES);                                  // [GR_NW][2][GR_CAP]
+    uint64_t *bar_all = (uint64_t*)(gr_smem + GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S));   // [GR_NW][2]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < KDE_TAB * 16; i += GR_THREADS) {
+        const double v = c_exp2_tab[i >> 4];
+        tab[i] = CLAMP ? v : __hiloint2double(__double2hiint(v) + ((i >> 4) << 12), __double2loint(v));
+    }
+    S *buf = buf_all + (size_t)warp * 2 * GR_CAP;
+    uint64_t *bar = bar_all + warp * 2;
+    if (lane == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    const uint32_t tabl = smem_u32(tab) + 8u * (uint32_t)(lane & 15);
+    const int ncell = T.gs.ncx * T.gs.ncy;
+    const int nrows = T.B + 2 * T.mf;
+    const int q_mid = 2 * (nrows / 2), q_end = 2 * nrows;
+    const int nitems = __ldg(gtotal) * nlabels * 2;
+    uint32_t phase = 0u;                       // bit s = parity to wait for on stage s
+
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = (int)atomicAdd(counter, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= nitems) break;
+        const int half = item & 1, lab = (item >> 1) % nlabels, g = (item >> 1) / nlabels;
+        const int4 gi = __ldg((const int4*)(groups + g));            // t0, t1, strip, ca
+        const int g_cb = __ldg(&groups[g].cb);
+        const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
+        const int q_lo = half ? q_mid : 0, q_hi = half ? q_end : q_mid;
+        for (int pa = gi.w; pa <= g_cb; pa += T.wmax) {               // one pass unless the group is wider than the period allows
+            const int pb = min(g_cb, pa + T.wmax - 1);
+            int a0 = gi.x, a1 = gi.y;
+            if (pa != gi.w || pb != g_cb) {
+                a0 = max(a0, __ldg(tstart + gi.z * T.gs.ncx + pa));
+                a1 = min(a1, __ldg(tstart + gi.z * T.gs.ncx + pb + 1));
+            }
+            if (a0 >= a1) continue;
+            double tx[2], ty[2], tz[2], acc[2];
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                const int j = a0 + lane + r * 32;
+                S q; q.x = 0.0; q.y = 0.0; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
+                if (j < a1) q = tgt[j];
+                tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0; acc[r] = 0.0;
+            }
+            const bool two = a0 + 32 < a1;
+            KdePlanState st; st.pbase = q_lo - 32; st.pos = 32; st.intra = 0; st.c_off = st.c_cnt = 0; st.c_code = 4;
+            KdeBatch cur, nxt;
+            int s = 0;
+            bool have = kde_plan_next(st, T, gi.z, pa, pb, q_hi, sstart, lane, cur);
+            if (have) {
+                kde_issue_batch<S>(cur, buf, src, &bar[0], lane);
+            }
+            while (have) {
+                const bool more = kde_plan_next(st, T, gi.z, pa, pb, q_hi, sstart, lane, nxt);
+                if (more) {                    // stage s^1 was drained by this warp in the previous round
+                    kde_issue_batch<S>(nxt, buf + (s ^ 1) * GR_CAP, src, &bar[s ^ 1], lane);
+                }
+                mbar_wait(&bar[s], (phase >> s) & 1u); phase ^= 1u << s;
+                __syncwarp();                  // the lanes leave the try_wait loop one by one: reconverge before the pair loop
+                const double shx = (double)(cur.code / 3 - 1) * T.gs.wx, shy = (double)(cur.code % 3 - 1) * T.gs.wy;
+                const S *__restrict__ Bs = buf + s * GR_CAP;
+                if (two) {
+                    const double sx[2] = { tx[0] + shx, tx[1] + shx }, sy[2] = { ty[0] + shy, ty[1] + shy };
+                    kde_accumulate_t<DIM, CLAMP, 2>(Bs, cur.total, tabl, sx, sy, tz, acc);
+                } else {
+                    const double sx[1] = { tx[0] + shx }, sy[1] = { ty[0] + shy }, tz1[1] = { tz[0] };
+                    double a1v[1] = { acc[0] };
+                    kde_accumulate_t<DIM, CLAMP, 1>(Bs, cur.total, tabl, sx, sy, tz1, a1v);
+                    acc[0] = a1v[0];
+                }
+                __syncwarp();
+                s ^= 1; have = more; cur = nxt;
+            }
+            double *__restrict__ out = out_all + (size_t)lab * out_stride;
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                const int j = a0 + lane + r * 32;
+                if (j < a1) atomicAdd(out + __ldg(tperm + j), acc[r]);
+            }
+        }
+    }
+}
+
+// pairs the group kernel evaluates: sum over groups of (#targets) x (#sources of every label in the window)
+__global__ void __launch_bounds__(128) k_kde_groups_count(const KdeGroup *__restrict__ groups, const int32_t *__restrict__ gtotal,
+                                                          const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart_all,
+                                                          int nlabels, KdeTiling T, unsigned long long *total) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ncell = T.gs.ncx * T.gs.ncy, npieces = 2 * (T.B + 2 * T.mf);
+    unsigned long long mine = 0ull;
+    if (g < gtotal[0]) {
+        const KdeGroup G = groups[g];
+        for (int pa = G.ca; pa <= G.cb; pa += T.wmax) {
+            const int pb = min(G.cb, pa + T.wmax - 1);
+            int a0 = G.t0, a1 = G.t1;
+            if (pa != G.ca || pb != G.cb) { a0 = max(a0, tstart[G.strip * T.gs.ncx + pa]); a1 = min(a1, tstart[G.strip * T.gs.ncx + pb + 1]); }
+            if (a0 >= a1) continue;
+            unsigned long long nsrc = 0ull;
+            for (int l = 0; l < nlabels; l++)
+                for (int q = 0; q < npieces; q++) {
+                    int off, cnt, code;
+                    kde_group_piece(T, G.strip, pa, pb, q, sstart_all + (size_t)l * ncell, off, cnt, code);
+                    nsrc += (unsigned long long)cnt;
+                }
+            mine += nsrc * (unsigned long long)(a1 - a0);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(total, mine);
+}
+
 // ------------------------------------------------------------------ normalisation (TriMesh_kde.cpp:504-524)
 #define RED_T 256
+
 __global__ void __launch_bounds__(RED_T) k_kde_combine(const double *__restrict__ partial, int64_t nv, int nsplit,
                                                        double factor, double *__restrict__ dens, double *__restrict__ bsum) {
     __shared__ double sm[RED_T];
@@ -459,8 +766,10 @@ static KdePlan kde_plan(int64_t nv, int64_t ns) {
     p.nsplit = (int)want;
     return p;
 }
-static int64_t kde_max_cells(int64_t nv) { return nv / 16 + 4096; }
+static int64_t kde_max_cells(int64_t nv) { return nv / 3 + 4096; }     // fine source cells of the tile plan: <= 16 per ~56-target tile
 #define KDE_MAX_LABELS 64
+#define KDE_MAX_STRIPS 65536
+static int64_t kde_max_groups(int64_t nv) { return nv / GR_TGT + KDE_MAX_STRIPS + 8; }
 
 static size_t kde_ws_bytes(int64_t nv, int64_t ns, int nlabels) {
     const KdePlan p = kde_plan(nv, ns);
@@ -468,7 +777,8 @@ static size_t kde_ws_bytes(int64_t nv, int64_t ns, int nlabels) {
     return 2 * ms_align((size_t)nv * 32) + 2 * ms_align((size_t)ns * 32)         // staged + cell-sorted targets, sources
          + ms_align((size_t)p.nsplit * nv * 8) + ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8)
          + 2 * ms_align((size_t)(nv + 1) * 4) + 2 * ms_align((size_t)(ns + 1) * 4) // bin ids, permutations
-         + 4 * ms_align(nc * 4) + ms_scan_ws_bytes((int64_t)nc) + 8192;
+         + 4 * ms_align(nc * 4) + ms_scan_ws_bytes((int64_t)nc) + 8192
+         + 2 * ms_align((KDE_MAX_STRIPS + 8) * 4) + ms_align((size_t)kde_max_groups(nv) * sizeof(KdeGroup));
 }
 extern "C" size_t ms_kde_workspace_bytes(int64_t nv, int64_t nids) { return kde_ws_bytes(nv, nids > 0 ? nids : nv, 1); }
 extern "C" size_t ms_kde_labels_workspace_bytes(int64_t nv, int nlabels) { return kde_ws_bytes(nv, nv, nlabels < 1 ? 1 : nlabels); }
@@ -539,11 +849,14 @@ __global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restri
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(total, mine);
 }
 
+static bool kde_env_flag(const char *name) { const char *v = getenv(name); return v && v[0] && v[0] != '0'; }
+
 struct KdeCtx {
-    KdePlan p; bool cells; KdeGrid g; int type, periodic, nsplit, nlabels; bool clamp;
+    KdePlan p; bool cells, tiles; KdeGrid g; KdeTiling tl; int type, periodic, nsplit, nlabels; bool clamp;
     double wx, wy; float sfactor;
     void *tgt, *tgt_sorted, *src, *src_sorted; const void *ssorted; const int32_t *sst;
-    double *partial, *dens, *bsum; int32_t *tperm, *tstart, *sstart; unsigned long long *counter;
+    double *partial, *dens, *bsum; int32_t *tperm, *tstart, *sstart, *tcell, *ng, *gstart; KdeGroup *groups; int64_t max_groups;
+    unsigned long long *counter; void *scan_ws;
 };
 
 // validation, staging of the scaled coordinates, choice between all pairs and the cell list, binning.
@@ -581,8 +894,10 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
     c.bsum = A.take<double>(nv / RED_T + 2);
     int32_t *tcell = A.take<int32_t>(nv + 1), *tperm = A.take<int32_t>(nv), *scell = A.take<int32_t>(ns + 1), *sperm = A.take<int32_t>(ns);
     int32_t *cnt = A.take<int32_t>(nc), *cursor = A.take<int32_t>(nc), *tstart = A.take<int32_t>(nc), *sstart = A.take<int32_t>(nc);
-    void *scan_ws = A.take<char>(ms_scan_ws_bytes((int64_t)nc));
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes((int64_t)nc)); c.scan_ws = scan_ws;
     c.counter = (unsigned long long*)A.take<unsigned long long>(4);
+    c.ng = A.take<int32_t>(KDE_MAX_STRIPS + 8); c.gstart = A.take<int32_t>(KDE_MAX_STRIPS + 8);
+    c.max_groups = kde_max_groups(nv); c.groups = A.take<KdeGroup>((size_t)c.max_groups); c.tcell = tcell;
 
     MS_K("kde_stage", s);
     if (type == 2) k_kde_stage<2><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, NULL, nv, scale, (double2*)tgt);
@@ -598,7 +913,45 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
     // ---- cell-list plan: needs the grid extent (box6); periodic grids must tile the period
     bool cells = false; KdeGrid g; double rwin = 0.0;
     g.ncx = g.ncy = 1; g.m = 0; g.periodic = periodic ? 1 : 0; g.b0x = g.b0y = 0.0; g.inv_cx = g.inv_cy = 0.0; g.wx = wx; g.wy = wy;
-    if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
+    c.tiles = false;
+    if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0 && !kde_env_flag("MS_KDE_NO_TILES")) {
+        // ---- group plan: strips of B fine rows, ~square groups of 64 targets, fine cells of ~rcut/8
+        const double rcut = cutoff_sigmas * sg * scale;
+        const double tside = sqrt((double)GR_TGT * wx * wy / (double)nv);
+        const double ntyd = floor(wy / tside);
+        if (ntyd >= 1.0 && ntyd <= (double)KDE_MAX_STRIPS) {
+            KdeTiling T;
+            T.nty = (int)ntyd;
+            const double tsy = wy / T.nty;
+            int B = (int)lround(tsy / (rcut / 8.0));
+            B = B < 1 ? 1 : (B > 4 ? 4 : B);
+            double ncxd = 0.0;
+            for (;; B--) {                                 // fine cells ~square; their count must fit the workspace
+                ncxd = floor(wx / (tsy / B)); if (ncxd < 1.0) ncxd = 1.0;
+                if (B == 1 || ncxd * ntyd * B <= (double)kde_max_cells(nv)) break;
+            }
+            KdeGrid gs = g;
+            gs.ncx = (int)ncxd; gs.ncy = T.nty * B; gs.m = 0;
+            T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut;
+            T.mf = (int)ceil(rcut / T.cys);
+            const int mxmax = (int)ceil(rcut / T.cxs);
+            gs.b0x = (double)box6[0] * scale; gs.b0y = (double)box6[1] * scale;
+            gs.inv_cx = 1.0 / T.cxs; gs.inv_cy = 1.0 / T.cys;
+            T.gs = gs;
+            T.wmax = periodic ? gs.ncx - 2 * mxmax - 1 : (1 << 30);      // widest box whose window does not meet itself
+            const bool fits = ncxd * ntyd * B <= (double)kde_max_cells(nv) && T.mf <= 4096
+                           && (!periodic || (T.wmax >= 1 && B + 2 * T.mf <= gs.ncy));
+            if (fits) {
+                c.tiles = cells = true; c.tl = T;
+                g = gs; g.ncy = T.nty; g.inv_cy = 1.0 / tsy;            // the target grid: fine columns x strips
+                const double ex = (double)(2 * mxmax + 2) * T.cxs + 2.0 * tside, ey = (B + T.mf + 1) * T.cys;
+                rwin = ex * ex + ey * ey;
+                // the exponent shift n>>8 is not clamped in the kernel unless CLAMP: keep it far below 1021
+                if (rwin >= 256.0 * 1000.0) rwin = 2.0 * KDE_RMAX;
+            }
+        }
+    }
+    if (!cells && cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
         const double rcut = cutoff_sigmas * sg * scale;                      // scaled cut-off radius
         double cs = rcut / 4.0;
         const double cmin = sqrt(56.0 * wx * wy / (double)nv);               // ~56 targets per cell
@@ -648,16 +1001,57 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
         if (rc) return rc;
         c.ssorted = tgt_sorted; c.sst = tstart;
     }
-    if (ids || labels) {
-        if (type == 2) rc = kde_bin<2>(src, ns, g, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
-        else           rc = kde_bin<3>(src, ns, g, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+    if (ids || labels || c.tiles) {
+        const KdeGrid &gsrc = c.tiles ? c.tl.gs : g;      // tiles: the sources always live on the fine grid
+        if (type == 2) rc = kde_bin<2>(src, ns, gsrc, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
+        else           rc = kde_bin<3>(src, ns, gsrc, labels, nlabels, scell, cnt, cursor, sstart, sperm, src_sorted, scan_ws, s);
         if (rc) return rc;
         c.ssorted = src_sorted; c.sst = sstart;
     }
     return 0;
 }
 
+// groups of 64 consecutive targets per strip: counts -> offsets -> descriptors
+static int kde_build_groups(const KdeCtx &c, cudaStream_t s) {
+    const KdeTiling &T = c.tl;
+    MS_K("kde_group_count", s); k_kde_group_count<<<ms_blocks(T.nty, 128), 128, 0, s>>>(c.tstart, T.gs.ncx, T.nty, c.ng);
+    if (ms_exclusive_scan_i32(c.ng, c.gstart, T.nty, c.scan_ws, s)) return 2;
+    MS_K("kde_group_fill", s); k_kde_group_fill<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.tstart, c.tcell, c.tperm, T.gs.ncx, T.nty, c.gstart, c.groups);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int DIM, bool CLAMP>
+static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s) {
+    typedef typename SrcT<DIM>::type S;
+    const size_t smem = GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S) + (size_t)GR_NW * 2 * sizeof(uint64_t);
+    static int per_sm = 0;                     // resident CTAs per SM of this instantiation (set once; same on every B200)
+    if (per_sm == 0) {
+        MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int n = 0;
+        MS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_kde_groups<DIM, CLAMP>, GR_THREADS, smem));
+        MS_REQUIRE(n >= 1, "ms_kde: k_kde_groups does not fit an SM (%zu bytes of shared memory)", smem);
+        per_sm = n;
+    }
+    int sms = MS_SM_COUNT, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const KdeTiling &T = c.tl;
+    if (kde_build_groups(c, s)) return 2;
+    unsigned *item_counter = (unsigned*)(c.counter + 2);
+    MS_CUDA(cudaMemsetAsync(item_counter, 0, sizeof(unsigned), s));
+    MS_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)nv * (size_t)c.nlabels, s));
+    MS_K("kde_groups", s);
+    k_kde_groups<DIM, CLAMP><<<sms * per_sm, GR_THREADS, smem, s>>>((const S*)c.tgt_sorted, c.tstart, c.tperm, c.groups, c.gstart + T.nty,
+                                                                     (const S*)c.ssorted, c.sst, c.nlabels, nv, T, item_counter, out);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
 static int kde_launch_cells(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s) {
+    if (c.tiles) {
+        if (c.type == 2) return c.clamp ? kde_run_groups<2, true>(c, nv, out, s) : kde_run_groups<2, false>(c, nv, out, s);
+        return kde_run_groups<3, true>(c, nv, out, s);
+    }
     const int ncell = c.g.ncx * c.g.ncy;
     MS_K("kde_cells", s);
     if (c.type == 2) {
@@ -752,7 +1146,11 @@ extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int3
     if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); *pairs = (double)nv * (double)c.p.ns; return 0; }
     MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
     const int ncell = c.g.ncx * c.g.ncy;
-    MS_K("kde_cells_count", s); k_kde_cells_count<<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.nlabels, c.g, c.counter);
+    if (c.tiles) {
+        if (kde_build_groups(c, s)) return 2;
+        MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
+    }
+    else { MS_K("kde_cells_count", s); k_kde_cells_count<<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.nlabels, c.g, c.counter); }
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     unsigned long long h = 0ull;
