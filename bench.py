@@ -313,21 +313,25 @@ def main():
         bytes_io = {"h2d": 0, "d2h": 0}
 
         def step_e2e():
+            # one frame as a user script runs it: build both Membranes from host arrays, queue the three
+            # stages per leaflet, then read EVERY result back as numpy (downloads included in the timing)
             h2d = d2h = 0
-            recs = []
+            ms = []
             for lf in leaflets:
                 m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=device)
                 pn = m.compute_pnormals(18)
-                h2d += m._pset_points.nbytes; d2h += pn.nbytes
+                h2d += m._pset_nbytes; d2h += pn.nbytes
                 m.memb_smooth = new_mesh(lf, device)            # host producer's output, injected
                 m.compute_properties('smooth')
-                mesh = m.memb_smooth
-                h2d += sum(a.nbytes for a in mesh._dev['_host'])
-                d2h += sum(mesh.attributes[k].nbytes for k in ('pnormal', 'parea', 'mean_curv', 'gaus_curv'))
+                h2d += sum(a.nbytes for a in m.memb_smooth._dev['_host'])
                 for l in ['all'] + list(range(len(FRACTIONS))):
                     Membrane.compute_densities([m], [2], SIGMAS, True, l)
-                    if l != 'all':
-                        h2d += 4 * int((lf["labels"] == l).sum()) * len(SIGMAS)
+                h2d += 4 * lf["labels"].shape[0]                # the per-vertex label index
+                ms.append(m)
+            recs = []
+            for m in ms:
+                mesh = m.memb_smooth
+                d2h += sum(mesh.attributes[k].nbytes for k in ('pnormal', 'parea', 'mean_curv', 'gaus_curv'))
                 d2h += sum(v.nbytes for v in m.attributes.values())
                 recs.append([float(mesh.attributes['parea'].sum()), float(mesh.attributes['mean_curv'].mean())])
             bytes_io["h2d"], bytes_io["d2h"] = h2d, d2h

@@ -125,6 +125,93 @@ def d2h(t):
     return out.numpy()
 
 
+_copy_streams = {}
+
+
+def copy_stream(device):
+    """Side stream for result downloads (one per device): copies overlap the kernels of the main stream."""
+    key = torch.device(device).index or 0
+    st = _copy_streams.get(key)
+    if st is None:
+        st = _copy_streams[key] = torch.cuda.Stream(device=device)
+    return st
+
+
+class Pending(object):
+    """A device->host copy in flight: page-locked destination + the event that marks its completion."""
+    __slots__ = ("host", "event")
+
+    def __init__(self, host, event):
+        self.host, self.event = host, event
+
+    def result(self):
+        self.event.synchronize()
+        return self.host.numpy()
+
+
+def d2h_async(t):
+    """Start the download of tensor `t` on the copy stream (after everything queued so far on the current
+    stream); returns a Pending whose result() is the numpy array."""
+    dev = t.device
+    cs = copy_stream(dev)
+    cs.wait_stream(torch.cuda.current_stream(dev))
+    host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    with torch.cuda.stream(cs):
+        host.copy_(t, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(cs)
+    t.record_stream(cs)
+    return Pending(host, ev)
+
+
+class LazyResults(dict):
+    """dict of numpy results whose values may still be downloading: `park(name, tensor)` starts the
+    device->host copy and returns at once; any read access (`d[name]`, get, values, items, pop) waits
+    for that copy and hands out the numpy array.  Lets the host queue a whole frame without stalling
+    on every field, while callers still see plain numpy arrays."""
+
+    def park(self, name, tensor):
+        p = d2h_async(tensor)
+        dict.__setitem__(self, name, p)
+        return p
+
+    def adopt(self, name, pending):
+        dict.__setitem__(self, name, pending)
+
+    def _res(self, k, v):
+        if isinstance(v, Pending):
+            v = v.result()
+            dict.__setitem__(self, k, v)
+        return v
+
+    def __getitem__(self, k):
+        return self._res(k, dict.__getitem__(self, k))
+
+    def get(self, k, default=None):
+        return self[k] if k in self else default
+
+    def pop(self, k, *a):
+        if k in self:
+            v = self[k]
+            dict.__delitem__(self, k)
+            return v
+        return dict.pop(self, k, *a)
+
+    def values(self):
+        return [self[k] for k in list(self.keys())]
+
+    def items(self):
+        return [(k, self[k]) for k in list(self.keys())]
+
+    def resolve(self):
+        for k in list(self.keys()):
+            self[k]
+        return self
+
+    def copy(self):
+        return dict(self.items())
+
+
 def box6(a):
     arr = (C.c_float * 6)()
     for i in range(6):

@@ -213,40 +213,56 @@ __global__ void __launch_bounds__(256) k_kde_cell_scatter(int64_t n, const int32
     if (c >= 0) perm[start[c] + atomicAdd(cursor + c, 1)] = (int32_t)i;
 }
 // ascending element order inside every cell => the summation order (and the result) is reproducible.
-// One warp per cell: every lane ranks its elements against the whole cell (counting sort by
-// comparison, all in registers); cells with more than 256 elements fall back to a serial sort.
+// One LANE per cell for the common small cells (serial insertion sort of <= SORT_SMALL indices); the
+// rare bigger cells of a warp's 32 are then sorted one at a time by the whole warp: every lane ranks its
+// elements against the whole cell (counting sort by comparison, in registers); cells with more than 256
+// elements fall back to a serial sort.
 #define SORT_K 8
+#define SORT_SMALL 16
 __global__ void __launch_bounds__(128) k_kde_cell_sort(int ncell, const int32_t *__restrict__ start, int32_t *perm) {
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (c >= ncell) return;
-    const int b = start[c], e = start[c + 1], n = e - b;
-    if (n <= 1) return;
-    if (n > 32 * SORT_K) {            // crowded cell (strongly clustered input): serial insertion sort, correct but slow
-        if (lane == 0)
-            for (int i = b + 1; i < e; i++) {
-                const int32_t key = perm[i]; int j = i - 1;
-                while (j >= b && perm[j] > key) { perm[j + 1] = perm[j]; j--; }
-                perm[j + 1] = key;
-            }
-        return;
-    }
-    int32_t v[SORT_K]; int rank[SORT_K];
-#pragma unroll
-    for (int k = 0; k < SORT_K; k++) { const int i = lane + 32 * k; v[k] = i < n ? perm[b + i] : 0x7fffffff; rank[k] = 0; }
-    const int rounds = (n + 31) >> 5;
-#pragma unroll
-    for (int k2 = 0; k2 < SORT_K; k2++) {
-        if (k2 < rounds) {
-            for (int l = 0; l < 32; l++) {
-                const int32_t o = __shfl_sync(0xffffffffu, v[k2], l);
-#pragma unroll
-                for (int k = 0; k < SORT_K; k++) rank[k] += o < v[k];
-            }
+    const int c0 = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+    int b0 = 0, n0 = 0;
+    if (c0 < ncell) { b0 = start[c0]; n0 = start[c0 + 1] - b0; }
+    if (n0 > 1 && n0 <= SORT_SMALL) {
+        for (int i = b0 + 1; i < b0 + n0; i++) {
+            const int32_t key = perm[i]; int j = i - 1;
+            while (j >= b0 && perm[j] > key) { perm[j + 1] = perm[j]; j--; }
+            perm[j + 1] = key;
         }
     }
-    __syncwarp();
+    unsigned big = __ballot_sync(0xffffffffu, n0 > SORT_SMALL);
+    while (big) {
+        const int src = __ffs(big) - 1; big &= big - 1;
+        const int b = __shfl_sync(0xffffffffu, b0, src), n = __shfl_sync(0xffffffffu, n0, src), e = b + n;
+        if (n > 32 * SORT_K) {            // crowded cell (strongly clustered input): serial insertion sort, correct but slow
+            if (lane == 0)
+                for (int i = b + 1; i < e; i++) {
+                    const int32_t key = perm[i]; int j = i - 1;
+                    while (j >= b && perm[j] > key) { perm[j + 1] = perm[j]; j--; }
+                    perm[j + 1] = key;
+                }
+            __syncwarp();
+            continue;
+        }
+        int32_t v[SORT_K]; int rank[SORT_K];
 #pragma unroll
-    for (int k = 0; k < SORT_K; k++) if (lane + 32 * k < n) perm[b + rank[k]] = v[k];      // indices are distinct
+        for (int k = 0; k < SORT_K; k++) { const int i = lane + 32 * k; v[k] = i < n ? perm[b + i] : 0x7fffffff; rank[k] = 0; }
+        const int rounds = (n + 31) >> 5;
+#pragma unroll
+        for (int k2 = 0; k2 < SORT_K; k2++) {
+            if (k2 < rounds) {
+                for (int l = 0; l < 32; l++) {
+                    const int32_t o = __shfl_sync(0xffffffffu, v[k2], l);
+#pragma unroll
+                    for (int k = 0; k < SORT_K; k++) rank[k] += o < v[k];
+                }
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < SORT_K; k++) if (lane + 32 * k < n) perm[b + rank[k]] = v[k];      // indices are distinct
+        __syncwarp();
+    }
 }
 
 // sorted[i] = point perm[i], folded into the canonical period [b0, b0+w) when the grid is periodic so
@@ -401,12 +417,12 @@ struct KdeTiling {
     int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
     double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
 };
-struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; };      // targets [t0,t1), fine columns [ca,cb]
+struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; double xlo, xhi; };   // targets [t0,t1), fine columns [ca,cb], x extent
 
-// piece q of the window of a box of fine columns [ca,cb] in strip TY: row q>>1 (bottom-up), part q&1
+// piece q of the window of the box [xlo,xhi] x strip TY: row q>>1 (bottom-up), part q&1
 // (1 = the part of the row that wrapped around the period).  code = 3*(sx+1)+(sy+1): the image shift
 // (sx*wx, sy*wy) to add to the targets.
-__device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, int ca, int cb, int q, const int32_t *__restrict__ sstart,
+__device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, double xlo, double xhi, int q, const int32_t *__restrict__ sstart,
                                                 int &off, int &cnt, int &code) {
     off = 0; cnt = 0; code = 4;
     const KdeGrid &g = T.gs;
@@ -417,11 +433,11 @@ __device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, int 
     const double gy = (double)gap * T.cys;
     const double h2 = T.rc2 - gy * gy;
     if (h2 <= 0.0) return;
-    const int mx = (int)ceil(sqrt(h2) / T.cxs);
+    const double hx = sqrt(h2);
     int row = TY * T.B - T.mf + ri, sy = 0;
     if (row < 0) { if (!g.periodic) return; row += g.ncy; sy = 1; }
     else if (row >= g.ncy) { if (!g.periodic) return; row -= g.ncy; sy = -1; }
-    int xa = ca - mx, xb = cb + mx, sx = 0;
+    int xa = (int)floor((xlo - hx - g.b0x) * g.inv_cx), xb = (int)floor((xhi + hx - g.b0x) * g.inv_cx), sx = 0;
     if (!g.periodic) {
         if (part) return;
         xa = max(xa, 0); xb = min(xb, g.ncx - 1);
@@ -485,7 +501,8 @@ __global__ void __launch_bounds__(128) k_kde_group_count(const int32_t *__restri
 }
 __global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restrict__ tstart, const int32_t *__restrict__ tcell,
                                                         const int32_t *__restrict__ tperm, int ncx, int nty,
-                                                        const int32_t *__restrict__ gstart, KdeGroup *groups) {
+                                                        const int32_t *__restrict__ gstart, const double *__restrict__ tx, int xstride,
+                                                        KdeGroup *groups) {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= gstart[nty]) return;
     int lo = 0, hi = nty;                       // largest s with gstart[s] <= g
@@ -495,6 +512,9 @@ __global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restric
     G.t0 = b + (g - gstart[s]) * GR_TGT; G.t1 = min(G.t0 + GR_TGT, e); G.strip = s;
     G.ca = tcell[tperm[G.t0]] % ncx; G.cb = tcell[tperm[G.t1 - 1]] % ncx;
     G.pad0 = G.pad1 = G.pad2 = 0;
+    double xlo = tx[(size_t)G.t0 * xstride], xhi = xlo;
+    for (int j = G.t0 + 1; j < G.t1; j++) { const double x = tx[(size_t)j * xstride]; xlo = fmin(xlo, x); xhi = fmax(xhi, x); }
+    G.xlo = xlo; G.xhi = xhi;
     groups[g] = G;
 }
 
@@ -503,13 +523,13 @@ __global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restric
 struct KdePlanState { int pbase, pos, intra, c_off, c_cnt, c_code; };
 struct KdeBatch { int total, code, take_off, take_cnt, dst; };
 
-__device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling &T, int TY, int ca, int cb, int q_hi,
+__device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling &T, int TY, double xlo, double xhi, int q_hi,
                                               const int32_t *__restrict__ sstart, int lane, KdeBatch &b) {
     for (;;) {
         if (st.pos >= 32) {
             st.pbase += 32; st.pos = 0; st.intra = 0;
             if (st.pbase >= q_hi) return false;
-            kde_group_piece(T, TY, ca, cb, st.pbase + lane, sstart, st.c_off, st.c_cnt, st.c_code);
+            kde_group_piece(T, TY, xlo, xhi, st.pbase + lane, sstart, st.c_off, st.c_cnt, st.c_code);
             if (st.pbase + lane >= q_hi) st.c_cnt = 0;
         }
         const int eff = lane < st.pos ? 0 : (lane == st.pos ? st.c_cnt - st.intra : st.c_cnt);
@@ -588,14 +608,17 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
         const int half = item & 1, lab = (item >> 1) % nlabels, g = (item >> 1) / nlabels;
         const int4 gi = __ldg((const int4*)(groups + g));            // t0, t1, strip, ca
         const int g_cb = __ldg(&groups[g].cb);
+        const double g_xlo = __ldg(&groups[g].xlo), g_xhi = __ldg(&groups[g].xhi);
         const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
         const int q_lo = half ? q_mid : 0, q_hi = half ? q_end : q_mid;
         for (int pa = gi.w; pa <= g_cb; pa += T.wmax) {               // one pass unless the group is wider than the period allows
             const int pb = min(g_cb, pa + T.wmax - 1);
             int a0 = gi.x, a1 = gi.y;
+            double xlo = g_xlo, xhi = g_xhi;
             if (pa != gi.w || pb != g_cb) {
                 a0 = max(a0, __ldg(tstart + gi.z * T.gs.ncx + pa));
                 a1 = min(a1, __ldg(tstart + gi.z * T.gs.ncx + pb + 1));
+                xlo = T.gs.b0x + (double)pa * T.cxs; xhi = T.gs.b0x + (double)(pb + 1) * T.cxs;
             }
             if (a0 >= a1) continue;
             double tx[2], ty[2], tz[2], acc[2];
@@ -610,12 +633,12 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
             KdePlanState st; st.pbase = q_lo - 32; st.pos = 32; st.intra = 0; st.c_off = st.c_cnt = 0; st.c_code = 4;
             KdeBatch cur, nxt;
             int s = 0;
-            bool have = kde_plan_next(st, T, gi.z, pa, pb, q_hi, sstart, lane, cur);
+            bool have = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, cur);
             if (have) {
                 kde_issue_batch<S>(cur, buf, src, &bar[0], lane);
             }
             while (have) {
-                const bool more = kde_plan_next(st, T, gi.z, pa, pb, q_hi, sstart, lane, nxt);
+                const bool more = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, nxt);
                 if (more) {                    // stage s^1 was drained by this warp in the previous round
                     kde_issue_batch<S>(nxt, buf + (s ^ 1) * GR_CAP, src, &bar[s ^ 1], lane);
                 }
@@ -657,13 +680,17 @@ __global__ void __launch_bounds__(128) k_kde_groups_count(const KdeGroup *__rest
         for (int pa = G.ca; pa <= G.cb; pa += T.wmax) {
             const int pb = min(G.cb, pa + T.wmax - 1);
             int a0 = G.t0, a1 = G.t1;
-            if (pa != G.ca || pb != G.cb) { a0 = max(a0, tstart[G.strip * T.gs.ncx + pa]); a1 = min(a1, tstart[G.strip * T.gs.ncx + pb + 1]); }
+            double xlo = G.xlo, xhi = G.xhi;
+            if (pa != G.ca || pb != G.cb) {
+                a0 = max(a0, tstart[G.strip * T.gs.ncx + pa]); a1 = min(a1, tstart[G.strip * T.gs.ncx + pb + 1]);
+                xlo = T.gs.b0x + (double)pa * T.cxs; xhi = T.gs.b0x + (double)(pb + 1) * T.cxs;
+            }
             if (a0 >= a1) continue;
             unsigned long long nsrc = 0ull;
             for (int l = 0; l < nlabels; l++)
                 for (int q = 0; q < npieces; q++) {
                     int off, cnt, code;
-                    kde_group_piece(T, G.strip, pa, pb, q, sstart_all + (size_t)l * ncell, off, cnt, code);
+                    kde_group_piece(T, G.strip, xlo, xhi, q, sstart_all + (size_t)l * ncell, off, cnt, code);
                     nsrc += (unsigned long long)cnt;
                 }
             mine += nsrc * (unsigned long long)(a1 - a0);
@@ -820,7 +847,7 @@ static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, const int32_t 
     MS_K("kde_cell_count", s); k_kde_cell_count<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, labels, nlabels, cell, cnt);
     if (ms_exclusive_scan_i32(cnt, start, nbins, scan_ws, s)) return 2;
     MS_K("kde_cell_scatter", s); k_kde_cell_scatter<<<ms_blocks(n, 256), 256, 0, s>>>(n, cell, start, cursor, perm);
-    MS_K("kde_cell_sort", s); k_kde_cell_sort<<<ms_blocks((int64_t)nbins * 32, 128), 128, 0, s>>>(nbins, start, perm);
+    MS_K("kde_cell_sort", s); k_kde_cell_sort<<<ms_blocks((int64_t)nbins, 128), 128, 0, s>>>(nbins, start, perm);
     MS_K("kde_cell_gather", s); k_kde_cell_gather<DIM><<<ms_blocks(n, 256), 256, 0, s>>>(pts, n, g, start + nbins, perm, sorted);
     MS_LAUNCH_CHECK();
     return 0;
@@ -923,8 +950,10 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             KdeTiling T;
             T.nty = (int)ntyd;
             const double tsy = wy / T.nty;
-            int B = (int)lround(tsy / (rcut / 8.0));
-            B = B < 1 ? 1 : (B > 4 ? 4 : B);
+            const char *fe = getenv("MS_KDE_FINE");
+            const double fine = fe && atof(fe) > 0.0 ? atof(fe) : 16.0;
+            int B = (int)lround(tsy / (rcut / fine));
+            B = B < 1 ? 1 : (B > 6 ? 6 : B);
             double ncxd = 0.0;
             for (;; B--) {                                 // fine cells ~square; their count must fit the workspace
                 ncxd = floor(wx / (tsy / B)); if (ncxd < 1.0) ncxd = 1.0;
@@ -1016,7 +1045,8 @@ static int kde_build_groups(const KdeCtx &c, cudaStream_t s) {
     const KdeTiling &T = c.tl;
     MS_K("kde_group_count", s); k_kde_group_count<<<ms_blocks(T.nty, 128), 128, 0, s>>>(c.tstart, T.gs.ncx, T.nty, c.ng);
     if (ms_exclusive_scan_i32(c.ng, c.gstart, T.nty, c.scan_ws, s)) return 2;
-    MS_K("kde_group_fill", s); k_kde_group_fill<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.tstart, c.tcell, c.tperm, T.gs.ncx, T.nty, c.gstart, c.groups);
+    MS_K("kde_group_fill", s); k_kde_group_fill<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.tstart, c.tcell, c.tperm, T.gs.ncx, T.nty, c.gstart,
+                                                                                         (const double*)c.tgt_sorted, c.type == 2 ? 2 : 4, c.groups);
     MS_LAUNCH_CHECK();
     return 0;
 }

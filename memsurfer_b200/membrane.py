@@ -102,8 +102,14 @@ class Membrane(object):
         self.points = _lib.pinned_copy(self.points, np.float32)
         self.bbox = self.bbox.astype(np.float32)
         # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
-        # later fit_points_to_box_xy(): normals are computed on these coordinates
-        self._pset_points = _lib.pinned_copy(self.points, np.float32)
+        # later fit_points_to_box_xy(): normals are computed on these coordinates.  The PointSet copy
+        # lives in HBM: the upload starts now and self.points is not touched before it has landed.
+        self._pset_dev, self._pset_event = None, None
+        if torch.cuda.is_available():
+            self._pset_dev = _lib.h2d(self.points, self.device)
+            self._pset_event = torch.cuda.Event()
+            self._pset_event.record(torch.cuda.current_stream(self.device))
+        self._pset_nbytes = self.points.nbytes
 
         self.pnormals = None
         self._pnormals_f64 = None
@@ -114,7 +120,7 @@ class Membrane(object):
         self.memb_planar = None
         self.memb_smooth = None
         self.memb_exact = None
-        self.attributes = {}
+        self.attributes = _lib.LazyResults()      # numpy on access; downloads may still be in flight
         self.properties = {}
         self.info = {}
 
@@ -130,6 +136,8 @@ class Membrane(object):
     def fit_points_to_box_xy(self):
         """Wrap x,y into the box (membrane.py:100-121); returns the number of adjusted coordinates."""
         nadjusted = 0
+        if self._pset_event is not None:
+            self._pset_event.synchronize()         # the PointSet upload reads self.points
         boxw = self.bbox[1, :] - self.bbox[0, :]
         for d in range(2):
             lo = self.points[:, d] < self.bbox[0, d]
@@ -145,7 +153,7 @@ class Membrane(object):
         if self.pnormals is not None:
             return self.pnormals
         _lib.require_cuda()
-        pts = _lib.h2d(self._pset_points, self.device)
+        pts = self._pset_dev
         o32, o64, info = point_normals_device(pts, self.bbox, self.periodic,
                                               getattr(self, 'blayer', 0.2), knbrs, ndir_hint)
         self.info['pnormals'] = info
@@ -199,11 +207,11 @@ class Membrane(object):
 
     # ---------------------------------------------------------------------- properties / densities (GPU)
     def compute_properties(self, mtype='smooth'):
+        """Vertex normals, point areas and curvatures of the chosen mesh (membrane.py:237-247).  The results
+        land in mesh.attributes; the launch and the downloads are only queued here."""
         assert mtype == 'smooth' or mtype == 'exact'
         mesh = self.memb_exact if mtype == 'exact' else self.memb_smooth
-        mesh.compute_normals()
-        mesh.compute_pointareas()
-        mesh.compute_curvatures()
+        mesh._properties_lazy()
 
     MAX_FUSED_LABELS = 64
 
@@ -213,11 +221,17 @@ class Membrane(object):
             lab = self.labels
             if lab.dtype.kind in 'iu' and lab.size > 0 and lab.min() >= 0 and lab.max() < 65536:
                 # small non-negative integers: counting is much cheaper than the sort inside np.unique
-                present = np.bincount(lab) > 0
+                counts = np.bincount(lab)
+                present = counts > 0
                 self._label_values = np.flatnonzero(present).astype(lab.dtype)
-                self._label_inverse = (np.cumsum(present) - 1)[lab]
+                if present.all():                  # 0..L-1 all in use: the labels are their own index
+                    self._label_inverse = lab
+                else:
+                    self._label_inverse = (np.cumsum(present) - 1)[lab]
+                self._label_counts = counts[present]
             else:
-                self._label_values, self._label_inverse = np.unique(lab, return_inverse=True)
+                self._label_values, self._label_inverse, self._label_counts = \
+                    np.unique(lab, return_inverse=True, return_counts=True)
         return self._label_values, self._label_inverse
 
     def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=None):
@@ -238,15 +252,15 @@ class Membrane(object):
             fused = values.shape[0] <= self.MAX_FUSED_LABELS
         if fused:
             if mesh._label_index is None:
-                mesh.set_vertex_labels(inverse, values.shape[0])
+                mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
             select = np.arange(values.shape[0]) if len(labels) == 0 else np.where(np.isin(values, labels))[0]
-            self.attributes[name] = mesh.compute_density_labels(type, sigma, name, get_nlipdis, select, cutoff_sigmas)
+            self.attributes.adopt(name, mesh.compute_density_labels(type, sigma, name, get_nlipdis, select, cutoff_sigmas, lazy=True))
             return
         if len(labels) == 0:
-            self.attributes[name] = mesh.compute_density(type, sigma, name, get_nlipdis, np.empty([0]), cutoff_sigmas)
+            self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, np.empty([0]), cutoff_sigmas, lazy=True))
             return
         lidxs = np.where(np.isin(self.labels, labels))[0]
-        self.attributes[name] = mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas)
+        self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas, lazy=True))
 
     @staticmethod
     def compute_thickness(a, b, mtype='smooth'):

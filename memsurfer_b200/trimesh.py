@@ -78,9 +78,9 @@ class TriMesh(object):
         self._parameterized_verts = None
         self._delaunay = None            # (dfaces, doffs) of the periodic Delaunay (host producer)
 
-        self.attributes = {}
+        self.attributes = _lib.LazyResults()     # numpy on access; downloads may still be in flight
         self.attributes_f64 = LazyF64()   # fp64 twins, fetched from the device on first access
-        self._fields = {}                # KDE fields cached by name (TriMesh_kde.cpp:455-460)
+        self._fields = _lib.LazyResults() # KDE fields cached by name (TriMesh_kde.cpp:455-460)
         self._label_index = None         # optional per-vertex integer labels (label-fused KDE)
         self._nlabels = 0
         self._dev = {}                   # device-resident buffers
@@ -115,12 +115,11 @@ class TriMesh(object):
 
     def set_periodic_triangulation(self, faces, periodic_faces, trimmed_faces, duplicated_vidxs, duplicated_verts):
         """Inject the arrays `_fetch_faces` (trimesh.py:421-436) would fetch from the C++ object."""
-        self.faces = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
+        self.faces = _lib.pinned_copy(np.asarray(faces).reshape(-1, 3), np.uint32)
         self._periodic_faces = np.ascontiguousarray(periodic_faces, dtype=np.uint32).reshape(-1, 3)
-        self._trimmed_faces = np.ascontiguousarray(trimmed_faces, dtype=np.uint32).reshape(-1, 3)
+        self._trimmed_faces = _lib.pinned_copy(np.asarray(trimmed_faces).reshape(-1, 3), np.uint32)
         self._duplicated_vidxs = np.ascontiguousarray(duplicated_vidxs, dtype=np.uint32)
-        self._duplicated_verts = np.ascontiguousarray(duplicated_verts, dtype=np.float32) \
-            .reshape(-1, self.vertices.shape[1])
+        self._duplicated_verts = _lib.pinned_copy(np.asarray(duplicated_verts).reshape(-1, self.vertices.shape[1]), np.float32)
         self._invalidate()
 
     def _retrim(self):
@@ -175,18 +174,38 @@ class TriMesh(object):
         return verts, faces
 
     def to_device(self, pinned=None):
-        """Stage verts ++ dup verts and faces ++ trimmed faces in HBM (TriMesh.hpp:360-364 layout)."""
+        """Stage verts ++ dup verts and faces ++ trimmed faces in HBM (TriMesh.hpp:360-364 layout).  The pieces
+        are uploaded straight into slices of the device arrays (no concatenated host copy)."""
         _lib.require_cuda()
         if 'verts' in self._dev:
             return self._dev
         if self.faces is None:
             raise ValueError(f'{self.tag()} has no faces (call compute_delaunay or pass faces=)')
-        verts, faces = self._concat_host()
+        include_periodic = self.periodic and (self._duplicated_vidxs is not None)
+        V, dim = self.vertices.shape
         d = self._dev
-        d['verts'] = _lib.h2d(verts, self.device)
-        d['faces'] = _lib.h2d(faces.view(np.int32), self.device)
-        d['_host'] = (verts, faces)          # keep the page-locked staging alive until the copy is done
-        d['nv'] = self.vertices.shape[0]
+        if dim != 3:
+            verts, faces = self._concat_host()
+            d['verts'] = _lib.h2d(verts, self.device)
+            d['faces'] = _lib.h2d(faces.view(np.int32), self.device)
+            d['_host'] = (verts, faces)          # keep the page-locked staging alive until the copy is done
+        else:
+            Vd = self._duplicated_verts.shape[0] if include_periodic else 0
+            F0 = self.faces.shape[0]
+            Ft = self._trimmed_faces.shape[0] if include_periodic else 0
+            dv = torch.empty((V + Vd, 3), dtype=torch.float32, device=self.device)
+            df = torch.empty((F0 + Ft, 3), dtype=torch.int32, device=self.device)
+            host = [self.vertices, self.faces]
+            dv[:V].copy_(torch.from_numpy(self.vertices), non_blocking=True)
+            df[:F0].copy_(torch.from_numpy(self.faces.view(np.int32)), non_blocking=True)
+            if Vd:
+                dv[V:].copy_(torch.from_numpy(self._duplicated_verts), non_blocking=True)
+                host.append(self._duplicated_verts)
+            if Ft:
+                df[F0:].copy_(torch.from_numpy(self._trimmed_faces.view(np.int32)), non_blocking=True)
+                host.append(self._trimmed_faces)
+            d['verts'], d['faces'], d['_host'] = dv, df, tuple(host)
+        d['nv'] = V
         return d
 
     def _half_box(self):
@@ -238,37 +257,30 @@ class TriMesh(object):
         return d
 
     # ---------------------------------------------------------------------- computation of attributes
+    def _properties_lazy(self):
+        """Queue the fused properties launch and the four downloads; nothing is waited for here."""
+        if 'pnormal' in self.attributes:
+            return
+        d = self.properties_device()
+        for key, t32, t64 in (('pnormal', d['vn32'], d['vn64']), ('parea', d['pa32'], d['pa64']),
+                              ('mean_curv', d['H'], d['H']), ('gaus_curv', d['K'], d['K'])):
+            self.attributes.park(key, t32)
+            self.attributes_f64.park(key, t64)
+
     def compute_normals(self):
         """(V,3) float32 vertex normals (trimesh.py:244-261 -> TriMesh.cpp:99-133)."""
-        key = 'pnormal'
-        if key in self.attributes:
-            return self.attributes[key]
-        d = self.properties_device()
-        self.attributes[key] = _lib.d2h(d['vn32'])
-        self.attributes_f64.park(key, d['vn64'])
-        return self.attributes[key]
+        self._properties_lazy()
+        return self.attributes['pnormal']
 
     def compute_pointareas(self):
         """(V,) float32 mixed Voronoi vertex areas (trimesh.py:264-281 -> TriMesh.cpp:140-190)."""
-        key = 'parea'
-        if key in self.attributes:
-            return self.attributes[key]
-        d = self.properties_device()
-        self.attributes[key] = _lib.d2h(d['pa32'])
-        self.attributes_f64.park(key, d['pa64'])
-        return self.attributes[key]
+        self._properties_lazy()
+        return self.attributes['parea']
 
     def compute_curvatures(self):
         """((V,) f64 mean, (V,) f64 Gaussian) as vtkCurvatures gives them (trimesh.py:284-316)."""
-        keys = ['mean_curv', 'gaus_curv']
-        if keys[0] in self.attributes and keys[1] in self.attributes:
-            return self.attributes[keys[0]], self.attributes[keys[1]]
-        d = self.properties_device()
-        self.attributes[keys[0]] = _lib.d2h(d['H'])
-        self.attributes[keys[1]] = _lib.d2h(d['K'])
-        self.attributes_f64[keys[0]] = self.attributes[keys[0]]
-        self.attributes_f64[keys[1]] = self.attributes[keys[1]]
-        return self.attributes[keys[0]], self.attributes[keys[1]]
+        self._properties_lazy()
+        return self.attributes['mean_curv'], self.attributes['gaus_curv']
 
     def compute_distance_to_surface(self, other):
         raise NotImplementedError('distance_to_other_mesh (TriMesh_cgal.cpp:390-425) is outside the GPU hot path '
@@ -327,7 +339,7 @@ class TriMesh(object):
                             ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_kde')
         return o64, o32
 
-    def set_vertex_labels(self, label_index, nlabels):
+    def set_vertex_labels(self, label_index, nlabels, counts=None):
         """Integer label in [0, nlabels) per vertex (negative: never a KDE source).  Enables the label-fused
         KDE: one pass evaluates every vertex pair once and keeps the sums apart by the source's label."""
         label_index = np.asarray(label_index)
@@ -335,7 +347,8 @@ class TriMesh(object):
             raise ValueError(f'{self.tag()} expects one label per vertex')
         self._label_index = _lib.pinned_copy(label_index, np.int32)
         self._nlabels = int(nlabels)
-        self._label_counts = np.bincount(label_index[label_index >= 0], minlength=self._nlabels)
+        self._label_counts = np.asarray(counts) if counts is not None else \
+            np.bincount(label_index[label_index >= 0], minlength=self._nlabels)
         self._dev.pop('labels', None)
         self._dev.pop('kde_raw', None)
 
@@ -378,25 +391,26 @@ class TriMesh(object):
                                    _lib.stream_ptr(dev)), 'ms_kde_select')
         return o64, o32
 
-    def compute_density_labels(self, type, sigma, name, get_nlipids, select, cutoff_sigmas=0.0):
+    def compute_density_labels(self, type, sigma, name, get_nlipids, select, cutoff_sigmas=0.0, lazy=False):
         """Label-fused twin of compute_density: `select` = label indices (set_vertex_labels) whose vertices
         are the sources.  Same result as compute_density with the ids of those vertices."""
         if type < 1 or type > 3:
             raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
         if type == 1:
             raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
-        if name in self._fields:
-            return self._fields[name]
-        raw = self.density_labels_device(type, sigma, cutoff_sigmas)
-        o64, o32 = self.density_select_device(raw, select, get_nlipids)
-        dens = _lib.d2h(o32)
-        self._fields[name] = dens
-        self.attributes_f64.park(name, o64)
-        if LOGGER.isEnabledFor(logging.INFO):
-            LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
-        return dens
+        if name not in self._fields:
+            raw = self.density_labels_device(type, sigma, cutoff_sigmas)
+            o64, o32 = self.density_select_device(raw, select, get_nlipids)
+            self._fields.park(name, o32)
+            self.attributes_f64.park(name, o64)
+            if LOGGER.isEnabledFor(logging.INFO):
+                dens = self._fields[name]
+                LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        if lazy:                  # hand out the download in flight (or the finished array)
+            return dict.__getitem__(self._fields, name)
+        return self._fields[name]
 
-    def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0):
+    def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0, lazy=False):
         """(V,) float32 density (trimesh.py:324-361 -> TriMesh::kde TriMesh_kde.cpp:443-532).
 
         type 2: 2-D Gaussian on (x,y); type 3: 3-D Gaussian.  type 1 (geodesic, Floyd-Warshall
@@ -406,16 +420,17 @@ class TriMesh(object):
             raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
         if type == 1:
             raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
-        if name in self._fields:                      # TriMesh_kde.cpp:455-460: name-keyed cache
-            return self._fields[name]
-        pidxs = np.asarray(pidxs)
-        pd = None
-        if pidxs.shape[0] > 0:
-            pd = _lib.h2d(_lib.pinned_copy(pidxs, np.int32), self.device)
-        o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
-        dens = _lib.d2h(o32)
-        self._fields[name] = dens
-        self.attributes_f64.park(name, o64)
-        if LOGGER.isEnabledFor(logging.INFO):
-            LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
-        return dens
+        if name not in self._fields:                  # TriMesh_kde.cpp:455-460: name-keyed cache
+            pidxs = np.asarray(pidxs)
+            pd = None
+            if pidxs.shape[0] > 0:
+                pd = _lib.h2d(_lib.pinned_copy(pidxs, np.int32), self.device)
+            o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
+            self._fields.park(name, o32)
+            self.attributes_f64.park(name, o64)
+            if LOGGER.isEnabledFor(logging.INFO):
+                dens = self._fields[name]
+                LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
+        if lazy:
+            return dict.__getitem__(self._fields, name)
+        return self._fields[name]

@@ -17,6 +17,7 @@ dev = torch.device("cuda:0")
 
 
 def step():
+    ms = []
     for lf in leaflets:
         m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=dev)
         m.compute_pnormals(18)
@@ -24,6 +25,9 @@ def step():
         m.compute_properties('smooth')
         for l in ['all', 0, 1, 2]:
             Membrane.compute_densities([m], [2], bench.SIGMAS, True, l)
+        ms.append(m)
+    for m in ms:
+        m.memb_smooth.attributes.resolve(); m.attributes.resolve()
     torch.cuda.synchronize()
 
 
