@@ -146,6 +146,19 @@ int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, i
                            int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                            double *pairs, void *ws, size_t ws_bytes, void *stream);
 
+/* ---------------------------------------------------------------- closest point / thickness
+ * Replaces TriMesh::project_on_surface (memsurfer/src/TriMesh_cgal.cpp:295-363: CGAL AABB tree over the
+ * mesh's own faces, closest_point_and_primitive per query, barycentric coordinates by TriMesh::Point2Bary
+ * TriMesh.cpp:28-42) and TriMesh::distance_to_other_mesh (TriMesh_cgal.cpp:390-425; Euclidean, no
+ * periodic wrap).  verts (nv,3) f32, faces (nf,3) u32 (the mesh's own faces only), box4 (host) = xy
+ * extent of the vertices {xmin, ymin, xmax, ymax}; queries (nq,3) f32.  Outputs (each may be NULL):
+ * face_id (nq) i32 = closest face (ties: smallest id), bary (nq,3) f64 = barycentric coordinates of the
+ * closest point, dist_f64 / dist_f32 (nq) = distance.  Syncs the stream once (list size check).        */
+size_t ms_closest_point_workspace_bytes(int64_t nv, int64_t nf);
+int ms_closest_point(const float *verts, int64_t nv, const uint32_t *faces, int64_t nf, const float *box4,
+                     const float *queries, int64_t nq, int32_t *face_id, double *bary,
+                     double *dist_f64, float *dist_f32, void *ws, size_t ws_bytes, void *stream);
+
 /* fp64 FMA peak probe used for the KDE roofline: runs `iters` dependent-chain DFMA rounds on
  * every SM and returns the number of FLOP issued in *flop (host); time it with events.         */
 int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream);

@@ -264,8 +264,15 @@ class Membrane(object):
 
     @staticmethod
     def compute_thickness(a, b, mtype='smooth'):
-        raise NotImplementedError('leaflet thickness (mesh-to-mesh distance, TriMesh_cgal.cpp:390-425) is outside '
-                                  'the GPU hot path (SURVEY.md section 8(f), rank 1)')
+        """Leaflet thickness: distance of every vertex of one membrane's surface to the other's
+        (membrane.py:277-286 -> TriMesh::distance_to_other_mesh); stored in .properties['thickness']."""
+        assert mtype in ['smooth', 'exact']
+        if mtype == 'exact':
+            a.properties['thickness'] = a.memb_exact.compute_distance_to_surface(b.memb_exact)
+            b.properties['thickness'] = b.memb_exact.compute_distance_to_surface(a.memb_exact)
+        else:
+            a.properties['thickness'] = a.memb_smooth.compute_distance_to_surface(b.memb_smooth)
+            b.properties['thickness'] = b.memb_smooth.compute_distance_to_surface(a.memb_smooth)
 
     @staticmethod
     def compute_densities(membranes, types, sigmas, get_nlipdis, l):

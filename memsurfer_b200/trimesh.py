@@ -282,9 +282,79 @@ class TriMesh(object):
         self._properties_lazy()
         return self.attributes['mean_curv'], self.attributes['gaus_curv']
 
+    # ---------------------------------------------------------------------- closest point / thickness
+    def closest_point_device(self, queries_dev):
+        """Closest point of THIS mesh's own faces to every query (device tensors in, device tensors out):
+        (face id i32 (n,), barycentric f64 (n,3), distance f64 (n,), distance f32 (n,))."""
+        _lib.require_cuda()
+        L = _lib.lib()
+        d = self.to_device()
+        dev = self.device
+        V, F0 = self.vertices.shape[0], self.faces.shape[0]
+        if self.vertices.shape[1] != 3:
+            raise ValueError(f'{self.tag()} project_on_surface() requires a mesh in 3D!')
+        nq = int(queries_dev.shape[0])
+        fid = torch.empty(nq, dtype=torch.int32, device=dev)
+        bary = torch.empty((nq, 3), dtype=torch.float64, device=dev)
+        d64 = torch.empty(nq, dtype=torch.float64, device=dev)
+        d32 = torch.empty(nq, dtype=torch.float32, device=dev)
+        lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
+        box4 = (_lib.C.c_float * 4)(float(lo[0]), float(lo[1]), float(hi[0]), float(hi[1]))
+        ws = self._workspace('proj_ws', L.ms_closest_point_workspace_bytes(V, F0))
+        _lib.check(L.ms_closest_point(d['verts'].data_ptr(), V, d['faces'].data_ptr(), F0, box4,
+                                      queries_dev.data_ptr(), nq, fid.data_ptr(), bary.data_ptr(), d64.data_ptr(),
+                                      d32.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_closest_point')
+        return fid, bary, d64, d32
+
+    def project_on_surface(self, points):
+        """(face ids (n,) int, barycentric coordinates (n,3) f64) of the closest surface point of every
+        point (TriMesh::project_on_surface, TriMesh_cgal.cpp:295-363, without the float packing)."""
+        points = np.asarray(points)
+        if points.ndim != 2 or points.shape[1] != 3:
+            raise ValueError(f'{self.tag()} project_on_surface() needs 3D points: got {points.shape}')
+        q = _lib.h2d(_lib.pinned_copy(points, np.float32), self.device)
+        fid, bary, _, _ = self.closest_point_device(q)
+        return _lib.d2h(fid).astype(int), _lib.d2h(bary)
+
+    def set_parameterization(self, pverts):
+        """Inject the producer's planar parameterisation (the reference computes it with CGAL, trimesh.py:129-156)."""
+        pverts = np.asarray(pverts, np.float32).reshape(-1, 2)
+        if pverts.shape[0] != self.vertices.shape[0]:
+            raise ValueError(f'{self.tag()} expects one parameterized vertex per vertex')
+        self._parameterized_verts = pverts
+
+    def parameterize(self):
+        """Planar parameterisation of the vertices.  The CGAL producer (trimesh.py:129-156) is a host step that
+        is not available here: unless one was injected, the xy projection (TriMesh::parameterize_xy) is used."""
+        if self._parameterized_verts is None:
+            self._parameterized_verts = np.ascontiguousarray(self.vertices[:, :2], np.float32)
+        return self._parameterized_verts
+
+    def project_on_surface_and_plane(self, points):
+        """Project points on the triangulation and on its parameterisation (trimesh.py:158-190): returns
+        (spoints (n,3) f32, ppoints (n,2) f32).  The per-point Python loop of the reference is three
+        vectorised accumulations in the same order and dtypes."""
+        self.parameterize()
+        fids, fbarys = self.project_on_surface(points)
+        npoints = fids.shape[0]
+        spoints = np.zeros((npoints, 3), dtype=np.float32)
+        ppoints = np.zeros((npoints, 2), dtype=np.float32)
+        f = self.faces[fids].astype(np.int64)
+        for j in range(3):
+            spoints += fbarys[:, j, None] * self.vertices[f[:, j]]
+            ppoints += fbarys[:, j, None] * self._parameterized_verts[f[:, j]]
+        return spoints, ppoints
+
     def compute_distance_to_surface(self, other):
-        raise NotImplementedError('distance_to_other_mesh (TriMesh_cgal.cpp:390-425) is outside the GPU hot path '
-                                  '(SURVEY.md section 8(f), rank 1)')
+        """(V,) float32 distance of every vertex of this mesh to the other mesh's surface (trimesh.py:319-321 ->
+        TriMesh::distance_to_other_mesh, TriMesh_cgal.cpp:390-425)."""
+        d = self.to_device()
+        q = d['verts'][:self.vertices.shape[0]]
+        if other.device != self.device:
+            q = q.to(other.device)
+        _, _, d64, d32 = other.closest_point_device(q)
+        self.attributes_f64.park('distance_to_surface', d64)
+        return _lib.d2h(d32)
 
     # ---------------------------------------------------------------------- KDE
     def _kde_box(self, cutoff_sigmas):

@@ -583,3 +583,77 @@ void orc_kde_raw_targets(const float *verts, int64_t nv, const int32_t *ids, int
         density[t] = acc;
     }
 }
+
+/* ------------------------------------------------------------------ closest point on a mesh
+ * TriMesh::project_on_surface (memsurfer/src/TriMesh_cgal.cpp:295-363) asks CGAL's AABB tree for the
+ * closest point of the mesh's own faces to every query and converts it to barycentric coordinates with
+ * TriMesh::Point2Bary (memsurfer/src/TriMesh.cpp:28-42); TriMesh::distance_to_other_mesh
+ * (TriMesh_cgal.cpp:390-425) turns that into a distance.  CGAL is not in the tree: the closest point is
+ * restated as a sequential scan of all faces with the standard region test (Ericson 5.1.5), fp64, the
+ * first (smallest id) face winning ties.                                                              */
+static void orc_closest_on_triangle(const double *p, const double *a, const double *b, const double *c, double *o) {
+    double ab[3], ac[3], ap[3], bp[3], cp[3];
+    for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; ap[k] = p[k] - a[k]; }
+    const double d1 = dot3(ab, ap), d2 = dot3(ac, ap);
+    if (d1 <= 0.0 && d2 <= 0.0) { for (int k = 0; k < 3; k++) o[k] = a[k]; return; }
+    for (int k = 0; k < 3; k++) bp[k] = p[k] - b[k];
+    const double d3 = dot3(ab, bp), d4 = dot3(ac, bp);
+    if (d3 >= 0.0 && d4 <= d3) { for (int k = 0; k < 3; k++) o[k] = b[k]; return; }
+    const double vc = d1 * d4 - d3 * d2;
+    if (vc <= 0.0 && d1 >= 0.0 && d3 <= 0.0) {
+        const double v = d1 / (d1 - d3);
+        for (int k = 0; k < 3; k++) o[k] = a[k] + v * ab[k];
+        return;
+    }
+    for (int k = 0; k < 3; k++) cp[k] = p[k] - c[k];
+    const double d5 = dot3(ab, cp), d6 = dot3(ac, cp);
+    if (d6 >= 0.0 && d5 <= d6) { for (int k = 0; k < 3; k++) o[k] = c[k]; return; }
+    const double vb = d5 * d2 - d1 * d6;
+    if (vb <= 0.0 && d2 >= 0.0 && d6 <= 0.0) {
+        const double w = d2 / (d2 - d6);
+        for (int k = 0; k < 3; k++) o[k] = a[k] + w * ac[k];
+        return;
+    }
+    const double va = d3 * d6 - d5 * d4;
+    if (va <= 0.0 && (d4 - d3) >= 0.0 && (d5 - d6) >= 0.0) {
+        const double w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+        for (int k = 0; k < 3; k++) o[k] = b[k] + w * (c[k] - b[k]);
+        return;
+    }
+    const double denom = 1.0 / (va + vb + vc);
+    const double v = vb * denom, w = vc * denom;
+    for (int k = 0; k < 3; k++) o[k] = a[k] + ab[k] * v + ac[k] * w;
+}
+
+void orc_closest_point(const float *verts, int64_t nv, const uint32_t *faces, int64_t nf, const float *queries, int64_t nq,
+                       int32_t *face_id, double *bary, double *dist) {
+    (void)nv;
+    for (int64_t i = 0; i < nq; i++) {
+        const double p[3] = { queries[3*i], queries[3*i+1], queries[3*i+2] };
+        double best = 1e300, bc[3] = { 0, 0, 0 }; int64_t bf = -1;
+        for (int64_t f = 0; f < nf; f++) {
+            double a[3], b[3], c[3], q[3];
+            for (int k = 0; k < 3; k++) { a[k] = verts[3*(int64_t)faces[3*f] + k]; b[k] = verts[3*(int64_t)faces[3*f+1] + k]; c[k] = verts[3*(int64_t)faces[3*f+2] + k]; }
+            orc_closest_on_triangle(p, a, b, c, q);
+            const double dq[3] = { p[0] - q[0], p[1] - q[1], p[2] - q[2] };
+            const double dd = dot3(dq, dq);
+            if (dd < best) { best = dd; bf = f; bc[0] = q[0]; bc[1] = q[1]; bc[2] = q[2]; }
+        }
+        double u = 0.0, v = 0.0, w = 0.0;
+        if (bf >= 0) {          /* TriMesh::Point2Bary, TriMesh.cpp:28-42 */
+            double a[3], v0[3], v1[3], v2[3];
+            for (int k = 0; k < 3; k++) {
+                a[k] = verts[3*(int64_t)faces[3*bf] + k];
+                v0[k] = (double)verts[3*(int64_t)faces[3*bf+1] + k] - a[k]; v1[k] = (double)verts[3*(int64_t)faces[3*bf+2] + k] - a[k]; v2[k] = bc[k] - a[k];
+            }
+            const double d00 = dot3(v0, v0), d01 = dot3(v0, v1), d11 = dot3(v1, v1), d20 = dot3(v2, v0), d21 = dot3(v2, v1);
+            const double denom = d00 * d11 - d01 * d01;
+            v = (d11 * d20 - d01 * d21) / denom;
+            w = (d00 * d21 - d01 * d20) / denom;
+            u = 1.0 - v - w;
+        }
+        if (face_id) face_id[i] = (int32_t)bf;
+        if (bary) { bary[3*i] = u; bary[3*i+1] = v; bary[3*i+2] = w; }
+        if (dist) dist[i] = bf >= 0 ? sqrt(best) : 0.0;
+    }
+}

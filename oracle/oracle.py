@@ -50,6 +50,7 @@ def lib():
         L.orc_pca_normals.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p]
         L.orc_mst_orient.restype = C.c_int64
         L.orc_mst_orient.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p, _u8p]
+        L.orc_closest_point.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, _f32p, C.c_int64, _i32p, _f64p, _f64p]
         _LIB = L
     return _LIB
 
@@ -210,3 +211,13 @@ def ref_kde(verts, ids, type, sigma, get_counts, bbox=None):
     out = np.empty((v.shape[0],), np.float32)
     assert ref().msref_kde(v, v.shape[0], type, int(get_counts), sigma, int(periodic), box, 6, ids, ids.shape[0], out) == 0
     return out
+
+
+def closest_point(verts, faces, queries):
+    """(face id i32, barycentric (nq,3) f64, distance f64) of the closest mesh point to every query."""
+    verts = np.ascontiguousarray(verts, np.float32); faces = np.ascontiguousarray(faces, np.uint32)
+    queries = np.ascontiguousarray(queries, np.float32)
+    nq = queries.shape[0]
+    fid = np.zeros(nq, np.int32); bary = np.zeros((nq, 3), np.float64); dist = np.zeros(nq, np.float64)
+    lib().orc_closest_point(verts, verts.shape[0], faces, faces.shape[0], queries, nq, fid, bary, dist)
+    return fid, bary, dist
