@@ -146,6 +146,16 @@ int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, i
                            int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                            double *pairs, void *ws, size_t ws_bytes, void *stream);
 
+/* ---------------------------------------------------------------- overlapping points
+ * Replaces the detection part of utils.test_overlapping_points (memsurfer/utils.py:91-159: scipy pdist
+ * over all pairs < dthreshold).  points (m,3) f32 (2-D callers pad z = 0); pairs (max_pairs,2) i32
+ * receives index pairs i<j in no particular order; *npairs (host) = number of pairs closer than
+ * dthreshold (may exceed max_pairs); *min_above (host, may be NULL) = smallest distance > dthreshold
+ * among the scanned neighbours (+inf if none).  Syncs the stream.                                        */
+size_t ms_overlap_workspace_bytes(int64_t m);
+int ms_overlapping_pairs(const float *points, int64_t m, double dthreshold, int32_t *pairs, int64_t max_pairs,
+                         int64_t *npairs, double *min_above, void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- closest point / thickness
  * Replaces TriMesh::project_on_surface (memsurfer/src/TriMesh_cgal.cpp:295-363: CGAL AABB tree over the
  * mesh's own faces, closest_point_and_primitive per query, barycentric coordinates by TriMesh::Point2Bary

@@ -345,6 +345,103 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     return 0;
 }
 
+// ------------------------------------------------------------------ overlapping points
+// Replaces utils.test_overlapping_points memsurfer/utils.py:91-159 (scipy pdist over ALL pairs, O(N^2) memory:
+// unusable beyond ~5e4 points) for the detection part: pairs closer than dthreshold can only sit in the
+// same or an adjacent cell of the kNN cell list (cell side >= dthreshold), so one thread per point scans its
+// 3x3 cells.  pairs (max_pairs,2) receives (i<j) index pairs in no particular order; *npairs their total
+// count (may exceed max_pairs); *min_above = smallest distance > dthreshold seen among the scanned
+// candidates (the reference's move radius, utils.py:129; +inf if none).
+__global__ void __launch_bounds__(128) k_overlap(const float4 *__restrict__ sorted, int64_t m, Grid g, const int32_t *__restrict__ start,
+                                                 double thr, int32_t *pairs, unsigned long long max_pairs,
+                                                 unsigned long long *npairs, unsigned long long *min_above_bits) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double mine = 1e300;
+    if (p < m) {
+        const float4 q = __ldg(sorted + p);
+        const int qi = __float_as_int(q.w);
+        int cx, cy; cell_of(g, q.x, q.y, cx, cy);
+        for (int yy = max(cy - 1, 0); yy <= min(cy + 1, g.ny - 1); yy++)
+            for (int xx = max(cx - 1, 0); xx <= min(cx + 1, g.nx - 1); xx++) {
+                const int c = yy * g.nx + xx;
+                const int e1 = __ldg(start + c + 1);
+                for (int e = __ldg(start + c); e < e1; e++) {
+                    const float4 o = __ldg(sorted + e);
+                    const int oi = __float_as_int(o.w);
+                    if (oi <= qi) continue;
+                    const double dx = (double)q.x - (double)o.x, dy = (double)q.y - (double)o.y, dz = (double)q.z - (double)o.z;
+                    double d2 = dx * dx; d2 += dy * dy; d2 += dz * dz;
+                    const double d = sqrt(d2);
+                    if (d < thr) {
+                        const unsigned long long at = atomicAdd(npairs, 1ull);
+                        if (at < max_pairs) { pairs[2 * at] = qi; pairs[2 * at + 1] = oi; }
+                    } else if (d > thr && d < mine) mine = d;
+                }
+            }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mine = fmin(mine, __shfl_xor_sync(0xffffffffu, mine, o));
+    if ((threadIdx.x & 31) == 0 && mine < 1e300) atomicMin(min_above_bits, (unsigned long long)__double_as_longlong(mine));   // positive doubles order as integers
+}
+
+extern "C" size_t ms_overlap_workspace_bytes(int64_t n) { return ms_knn_workspace_bytes(n, 19); }
+
+extern "C" int ms_overlapping_pairs(const float *points, int64_t m, double dthreshold, int32_t *pairs, int64_t max_pairs,
+                                    int64_t *npairs_out, double *min_above_out, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(points && npairs_out && m > 0 && dthreshold >= 0.0 && max_pairs >= 0 && (pairs || max_pairs == 0), "ms_overlapping_pairs: bad arguments");
+    MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_overlapping_pairs: too many points");
+    MS_REQUIRE(ws_bytes >= ms_overlap_workspace_bytes(m), "ms_overlapping_pairs: workspace too small");
+    const int64_t ncell_max = m + 2048;
+    MsArena A(ws, ws_bytes);
+    int32_t *cell = A.take<int32_t>(m);
+    int32_t *cnt = A.take<int32_t>(ncell_max), *start = A.take<int32_t>(ncell_max), *cursor = A.take<int32_t>(ncell_max);
+    float4 *sorted = A.take<float4>(m);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(ncell_max));
+    unsigned *bb = (unsigned*)A.take<unsigned>(64);
+    unsigned long long *res = (unsigned long long*)(bb + 8);            // [0] = pair count, [1] = min distance bits
+    const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
+    const unsigned long long rinit[2] = { 0ull, 0x7ff0000000000000ull };
+    MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    MS_CUDA(cudaMemcpyAsync(res, rinit, sizeof(rinit), cudaMemcpyHostToDevice, s));
+    MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points, m, bb);
+    unsigned hb[4];
+    MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    float lo[2], hi[2];
+    for (int d = 0; d < 2; d++) {
+        unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
+        u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
+    }
+    double wx = (double)hi[0] - lo[0], wy = (double)hi[1] - lo[1];
+    MS_REQUIRE(wx == wx && wy == wy && wx < 1e30 && wy < 1e30, "ms_overlapping_pairs: non-finite coordinates");
+    if (!(wx > 0.0)) wx = 1e-6; if (!(wy > 0.0)) wy = 1e-6;
+    double h = sqrt(wx * wy * 2.0 / (double)m);
+    if (h < dthreshold) h = dthreshold;
+    Grid g;
+    for (;;) {
+        const double nxd = floor(wx / h) + 1.0, nyd = floor(wy / h) + 1.0;
+        if (nxd * nyd <= (double)(ncell_max - 1)) { g.nx = (int)nxd; g.ny = (int)nyd; break; }
+        h *= 1.5;
+    }
+    g.lox = lo[0]; g.loy = lo[1]; g.h = h; g.inv_h = 1.0 / h;
+    const int64_t ncell = (int64_t)g.nx * g.ny;
+    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
+    MS_K("cell_count", s); k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points, m, g, cell, cnt);
+    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
+    MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points, m, cell, start, cursor, sorted);
+    MS_K("overlap", s); k_overlap<<<ms_blocks(m, 128), 128, 0, s>>>(sorted, m, g, start, dthreshold, pairs, (unsigned long long)max_pairs, res, res + 1);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    unsigned long long h2[2];
+    MS_CUDA(cudaMemcpyAsync(h2, res, sizeof(h2), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *npairs_out = (int64_t)h2[0];
+    if (min_above_out) memcpy(min_above_out, &h2[1], 8);
+    return 0;
+}
+
 // ------------------------------------------------------------------ stage 3: PCA normals
 // One thread per point: centroid and covariance in neighbour order, cyclic Jacobi (CGAL's internal
 // 3x3 solver when CGAL_EIGEN3_ENABLED is off, setup.py:217), smallest-eigenvalue eigenvector.

@@ -110,6 +110,10 @@ class Membrane(object):
             self._pset_event = torch.cuda.Event()
             self._pset_event.record(torch.cuda.current_stream(self.device))
         self._pset_nbytes = self.points.nbytes
+        # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist)
+        if self._pset_dev is not None and kwargs.get('check_overlaps', True):
+            from .utils import test_overlapping_points
+            test_overlapping_points(self.points, fix=False, points_dev=self._pset_dev)
 
         self.pnormals = None
         self._pnormals_f64 = None
@@ -188,6 +192,10 @@ class Membrane(object):
         self.spoints = self.points.copy()
         self.ppoints = self.points[:, :2].copy()
         self._planar_bbox = (self.bbox[0, :2].copy(), self.bbox[1, :2].copy())
+        # membrane.py:199-200 -- separate coincident projections before triangulating
+        from .utils import test_overlapping_points
+        test_overlapping_points(self.spoints, fix=True, device=self.device)
+        test_overlapping_points(self.ppoints, fix=True, device=self.device)
         self._build_meshes()
 
     def _build_meshes(self):

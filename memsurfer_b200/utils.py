@@ -1,0 +1,84 @@
+"""memsurfer_b200.utils -- the O(N^2) guard of the reference flow, grid-based on the GPU.
+
+`test_overlapping_points` mirrors memsurfer/utils.py:91-159 (same arguments, return value, warning text
+and in-place `fix`): the reference builds scipy's condensed all-pairs distance vector (N(N-1)/2 doubles:
+a 1M-lipid leaflet would need 1 TB), here the pairs closer than the threshold come from the kNN cell list
+in HBM (include/memsurfer_b200.h: ms_overlapping_pairs).  No CPU fallback.
+"""
+import ctypes as C
+import logging
+
+import numpy as np
+import torch
+
+from . import _lib
+
+LOGGER = logging.getLogger(__name__)
+MAX_REPORTED_PAIRS = 1 << 20
+
+
+def overlapping_pairs_device(points_dev, dthreshold):
+    """(pairs (k,2) int32 sorted like the reference's condensed order, min distance above the threshold)."""
+    _lib.require_cuda()
+    L = _lib.lib()
+    dev = points_dev.device
+    n = int(points_dev.shape[0])
+    pairs = torch.empty((MAX_REPORTED_PAIRS, 2), dtype=torch.int32, device=dev)
+    ws = _lib.workspace(L.ms_overlap_workspace_bytes(n), dev)
+    npairs, dmin = C.c_int64(0), C.c_double(0.0)
+    _lib.check(L.ms_overlapping_pairs(points_dev.data_ptr(), n, float(dthreshold), pairs.data_ptr(), MAX_REPORTED_PAIRS,
+                                      C.byref(npairs), C.byref(dmin), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)),
+               'ms_overlapping_pairs')
+    k = int(npairs.value)
+    if k > MAX_REPORTED_PAIRS:
+        raise ValueError(f'{k} overlapping point pairs (more than {MAX_REPORTED_PAIRS}): the input is degenerate')
+    if k == 0:
+        return np.zeros((0, 2), np.int32), float(dmin.value)
+    p = pairs[:k].cpu().numpy()
+    p = p[np.lexsort((p[:, 1], p[:, 0]))]          # condensed pdist order: by row, then column
+    return p, float(dmin.value)
+
+
+def test_overlapping_points(points, dthreshold=0.00001, fix=False, device='cuda:0', points_dev=None):
+    """True if no two points are closer than dthreshold; else warn and return False, or (fix=True) move one point of
+    every coincident pair in place exactly as memsurfer/utils.py:118-159 does.  `points_dev`: the same points
+    already in HBM as an (n,3) float32 tensor (saves the upload)."""
+    points = np.asarray(points) if not isinstance(points, np.ndarray) else points
+    LOGGER.debug(f'Testing for overlapping points ({points.shape}, threshold={dthreshold}, fix={fix})')
+    if points_dev is None:
+        p3 = np.zeros((points.shape[0], 3), np.float32)
+        p3[:, :points.shape[1]] = points
+        points_dev = torch.from_numpy(p3).to(device)
+    is_zero, dmin = overlapping_pairs_device(points_dev, dthreshold)
+    nzero = is_zero.shape[0]
+    if nzero == 0:
+        return True
+    is_zero = [(int(x), int(y)) for x, y in is_zero]
+    LOGGER.warning(f'Found {nzero} overlapping points: {is_zero}')
+    if not fix:
+        return False
+
+    # now, try to fix them: we want to move the fewest points possible (utils.py:124-159)
+    dupls, dupls_cnts = np.unique([x for sublist in is_zero for x in sublist], return_counts=True)
+    dupls = {dupls[i]: dupls_cnts[i] for i in range(len(dupls))}
+    if not np.isfinite(dmin):
+        raise ValueError('cannot separate overlapping points: no distinct neighbour found')
+    max_move = 0.5 * dmin
+    for x, y in is_zero:
+        dist0 = np.linalg.norm(points[x] - points[y])
+        if not np.isclose(dist0, 0.):      # we have moved either of these points before
+            continue
+        if dupls[x] == -1 or dupls[y] == -1:
+            continue
+        a, b = (x, y) if dupls[x] > dupls[y] else (y, x)      # move the one that impacts more points
+        pa = f'{points[a]}'
+        rad = np.random.rand() * max_move
+        theta = np.random.rand() * np.pi
+        points[a, 0] += rad * np.cos(theta)
+        points[a, 1] += rad * np.sin(theta)
+        dist1 = np.linalg.norm(points[x] - points[y])
+        LOGGER.debug(f'Moved point {a}: {pa} --> {points[a]} : dist = {dist0} --> {dist1}')
+        dupls[a] = -1          # mark this as moved
+
+
+test_overlapping_points.__test__ = False      # not a pytest test

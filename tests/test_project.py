@@ -103,3 +103,33 @@ def test_thickness_full_size_properties():
     ub = np.linalg.norm(a.vertices[sub].astype(np.float64) - b.vertices[j].astype(np.float64), axis=1)
     assert (d[sub] <= ub + 1e-4).all()
     torch.cuda.synchronize()
+
+
+@pytest.mark.gpu
+def test_overlapping_points_vs_pdist():
+    """the grid-based guard finds exactly the pairs scipy's pdist finds (memsurfer/utils.py:112-113)."""
+    import scipy.spatial.distance
+    import torch
+    from memsurfer_b200 import synth, Membrane
+    from memsurfer_b200.utils import test_overlapping_points, overlapping_pairs_device
+    pts, labels, bbox = synth.make_leaflet(2500, seed=8)
+    assert test_overlapping_points(pts) is True
+    bad = pts.copy()
+    bad[17] = bad[900]; bad[1200] = bad[900]                      # a triple
+    bad[33] = bad[34] + np.array([3e-6, 0, 0], np.float32)       # closer than 1e-5
+    bad[50] = bad[51] + np.array([0, 5e-3, 0], np.float32)       # close but not overlapping
+    pd = scipy.spatial.distance.pdist(bad)
+    n = bad.shape[0]
+    iu = np.triu_indices(n, 1)
+    want = np.stack([iu[0][pd < 1e-5], iu[1][pd < 1e-5]], axis=1)
+    got, dmin = overlapping_pairs_device(torch.from_numpy(bad).cuda(), 1e-5)
+    assert np.array_equal(got, want.astype(np.int32))
+    assert np.isclose(dmin, pd[pd > 1e-5].min(), rtol=0, atol=0)
+    assert test_overlapping_points(bad) is False
+    fixed = bad.copy()
+    test_overlapping_points(fixed, fix=True)
+    assert test_overlapping_points(fixed) is True                 # every coincident pair was separated
+    assert (fixed != bad).any(axis=1).sum() <= 3
+    # 2-D input (ppoints) and the Membrane constructor hook
+    assert test_overlapping_points(pts[:, :2].copy()) is True
+    Membrane(bad, labels=labels, periodic=True, bbox=bbox)        # warns, does not raise (membrane.py:84)
