@@ -137,6 +137,19 @@ int ms_kde_select(const double *raw, int64_t nv, int nlabels, const uint8_t *sel
                   int get_counts, double *density_f64, float *density_f32,
                   void *ws, size_t ws_bytes, void *stream);
 
+/* Several sigmas in one call: raw (nsigma, nlabels, nv) = the ms_kde_labels result of every sigma (host array
+ * `sigmas`).  With a cut-off whose window plan fits every sigma the vertices are binned ONCE (on the grid of the
+ * smallest sigma) and only re-staged per sigma; otherwise a loop over ms_kde_labels.  This is the loop
+ * `for s in sigmas` of Membrane.compute_densities (membrane.py:289-297) hoisted below the ABI.            */
+size_t ms_kde_labels_multi_workspace_bytes(int64_t nv, int nlabels);
+int ms_kde_labels_multi(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                        int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                        double *raw, void *ws, size_t ws_bytes, void *stream);
+/* Diagnostic twin: pairs[i] (host doubles) = pairs the launch of sigma i evaluates.  Syncs the stream. */
+int ms_kde_labels_multi_pairs(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                              int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                              double *pairs, void *ws, size_t ws_bytes, void *stream);
+
 /* Diagnostic (roofline accounting): the number of pairs ms_kde (labels == NULL) or ms_kde_labels
  * evaluates for the same arguments -- nv*n_sources for the all-pairs kernel, the sum over cells of
  * targets x window sources for the cell list.  *pairs is a host double; ws sized by the matching

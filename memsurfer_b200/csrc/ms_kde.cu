@@ -416,6 +416,7 @@ struct KdeTiling {
     KdeGrid gs;               // fine source grid; gs.m is unused
     int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
     double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
+    double gscale;            // factor on the stored group x extents (1 unless the binning is shared between sigmas)
 };
 struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; double xlo, xhi; };   // targets [t0,t1), fine columns [ca,cb], x extent
 
@@ -608,7 +609,7 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
         const int half = item & 1, lab = (item >> 1) % nlabels, g = (item >> 1) / nlabels;
         const int4 gi = __ldg((const int4*)(groups + g));            // t0, t1, strip, ca
         const int g_cb = __ldg(&groups[g].cb);
-        const double g_xlo = __ldg(&groups[g].xlo), g_xhi = __ldg(&groups[g].xhi);
+        const double g_xlo = __ldg(&groups[g].xlo) * T.gscale, g_xhi = __ldg(&groups[g].xhi) * T.gscale;
         const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
         const int q_lo = half ? q_mid : 0, q_hi = half ? q_end : q_mid;
         for (int pa = gi.w; pa <= g_cb; pa += T.wmax) {               // one pass unless the group is wider than the period allows
@@ -680,7 +681,7 @@ __global__ void __launch_bounds__(128) k_kde_groups_count(const KdeGroup *__rest
         for (int pa = G.ca; pa <= G.cb; pa += T.wmax) {
             const int pb = min(G.cb, pa + T.wmax - 1);
             int a0 = G.t0, a1 = G.t1;
-            double xlo = G.xlo, xhi = G.xhi;
+            double xlo = G.xlo * T.gscale, xhi = G.xhi * T.gscale;
             if (pa != G.ca || pb != G.cb) {
                 a0 = max(a0, tstart[G.strip * T.gs.ncx + pa]); a1 = min(a1, tstart[G.strip * T.gs.ncx + pb + 1]);
                 xlo = T.gs.b0x + (double)pa * T.cxs; xhi = T.gs.b0x + (double)(pb + 1) * T.cxs;
@@ -883,7 +884,7 @@ struct KdeCtx {
     double wx, wy; float sfactor;
     void *tgt, *tgt_sorted, *src, *src_sorted; const void *ssorted; const int32_t *sst;
     double *partial, *dens, *bsum; int32_t *tperm, *tstart, *sstart, *tcell, *ng, *gstart; KdeGroup *groups; int64_t max_groups;
-    unsigned long long *counter; void *scan_ws;
+    unsigned long long *counter; void *scan_ws; int32_t *sperm; double scale;
 };
 
 // validation, staging of the scaled coordinates, choice between all pairs and the cell list, binning.
@@ -936,6 +937,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
     } else src = tgt;
     MS_LAUNCH_CHECK();
     c.tgt = tgt; c.src = src; c.tgt_sorted = tgt_sorted; c.src_sorted = src_sorted; c.tperm = tperm; c.tstart = tstart; c.sstart = sstart;
+    c.sperm = sperm; c.scale = scale;
 
     // ---- cell-list plan: needs the grid extent (box6); periodic grids must tile the period
     bool cells = false; KdeGrid g; double rwin = 0.0;
@@ -961,7 +963,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             }
             KdeGrid gs = g;
             gs.ncx = (int)ncxd; gs.ncy = T.nty * B; gs.m = 0;
-            T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut;
+            T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut; T.gscale = 1.0;
             T.mf = (int)ceil(rcut / T.cys);
             const int mxmax = (int)ceil(rcut / T.cxs);
             gs.b0x = (double)box6[0] * scale; gs.b0y = (double)box6[1] * scale;
@@ -1052,7 +1054,7 @@ static int kde_build_groups(const KdeCtx &c, cudaStream_t s) {
 }
 
 template <int DIM, bool CLAMP>
-static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s) {
+static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s, bool build = true) {
     typedef typename SrcT<DIM>::type S;
     const size_t smem = GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S) + (size_t)GR_NW * 2 * sizeof(uint64_t);
     static int per_sm = 0;                     // resident CTAs per SM of this instantiation (set once; same on every B200)
@@ -1066,7 +1068,7 @@ static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t
     int sms = MS_SM_COUNT, dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const KdeTiling &T = c.tl;
-    if (kde_build_groups(c, s)) return 2;
+    if (build && kde_build_groups(c, s)) return 2;
     unsigned *item_counter = (unsigned*)(c.counter + 2);
     MS_CUDA(cudaMemsetAsync(item_counter, 0, sizeof(unsigned), s));
     MS_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)nv * (size_t)c.nlabels, s));
@@ -1077,10 +1079,10 @@ static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t
     return 0;
 }
 
-static int kde_launch_cells(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s) {
+static int kde_launch_cells(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s, bool build = true) {
     if (c.tiles) {
-        if (c.type == 2) return c.clamp ? kde_run_groups<2, true>(c, nv, out, s) : kde_run_groups<2, false>(c, nv, out, s);
-        return kde_run_groups<3, true>(c, nv, out, s);
+        if (c.type == 2) return c.clamp ? kde_run_groups<2, true>(c, nv, out, s, build) : kde_run_groups<2, false>(c, nv, out, s, build);
+        return kde_run_groups<3, true>(c, nv, out, s, build);
     }
     const int ncell = c.g.ncx * c.g.ncy;
     MS_K("kde_cells", s);
@@ -1145,6 +1147,143 @@ extern "C" int ms_kde_labels(const float *verts, int64_t nv, const int32_t *labe
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
+}
+
+// ------------------------------------------------------------------ several sigmas on one binning
+// sorted[i] = fold(scale * vertex perm[i]): the staged + cell-sorted coordinates of another sigma on the SAME
+// permutation (bins are scale-invariant: only the grid is rescaled)
+template <int DIM>
+__global__ void __launch_bounds__(256) k_kde_restage(const float *__restrict__ verts, const int32_t *__restrict__ perm, int64_t n,
+                                                     const int32_t *__restrict__ nbinned, double scale_ref, KdeGrid gref,
+                                                     double scale, double wx, double wy, typename SrcT<DIM>::type *sorted) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || (nbinned && i >= (int64_t)__ldg(nbinned))) return;
+    const int64_t v = (int64_t)__ldg(perm + i);
+    const double x = ms_ld_f(verts + 3*v), y = ms_ld_f(verts + 3*v + 1);
+    typename SrcT<DIM>::type p;
+    p.x = x * scale; p.y = y * scale;
+    if (DIM == 3) { ((double*)&p)[2] = ms_ld_f(verts + 3*v + 2) * scale; ((double*)&p)[3] = 0.0; }
+    if (gref.periodic) {      // the period count is decided on the REFERENCE staging, exactly as the binning decided it
+        const double xr = __dmul_rn(x, scale_ref), yr = __dmul_rn(y, scale_ref);      // rounded products, as k_kde_stage stored them (no FMA contraction)
+        const int cx = (int)floor((xr - gref.b0x) * gref.inv_cx), cy = (int)floor((yr - gref.b0y) * gref.inv_cy);
+        const int kx = (cx >= 0 ? cx : cx - gref.ncx + 1) / gref.ncx, ky = (cy >= 0 ? cy : cy - gref.ncy + 1) / gref.ncy;
+        p.x -= (double)kx * wx; p.y -= (double)ky * wy;
+    }
+    sorted[i] = p;
+}
+
+extern "C" size_t ms_kde_labels_multi_workspace_bytes(int64_t nv, int nlabels) { return ms_kde_labels_workspace_bytes(nv, nlabels); }
+
+// raw (nsigma, nlabels, nv): per-label pair sums for every sigma.  With a cut-off whose group plan fits every
+// sigma the vertices are binned ONCE (on the grid of the smallest sigma) and only re-staged per sigma;
+// otherwise this is a loop over ms_kde_labels.
+extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, const int32_t *labels, int nlabels,
+                                      int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
+                                      double *pairs, void *ws, size_t ws_bytes, void *stream);
+static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                                 int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                                 double *raw, double *pairs, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(labels != NULL && (raw != NULL || pairs != NULL) && sigmas != NULL && nsigma >= 1, "ms_kde_labels_multi: labels, sigmas and an output are required");
+    const size_t per = (size_t)nlabels * (size_t)nv;
+    int ref = 0;
+    for (int i = 1; i < nsigma; i++) if (sigmas[i] < sigmas[ref]) ref = i;
+    bool shared = nsigma > 1 && cutoff_sigmas > 0.0;
+    KdeCtx c;
+    KdeTiling Ts[64]; bool clamps[64]; double scales[64]; float sfac[64];
+    if (shared && nsigma <= 64) {
+        int rc = kde_front(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigmas[ref], cutoff_sigmas, ws, ws_bytes, s, c);
+        if (rc) return rc;
+        shared = c.tiles;
+        for (int i = 0; shared && i < nsigma; i++) {
+            MS_REQUIRE(sigmas[i] > 0.0f, "ms_kde_labels_multi: bad sigma %g", (double)sigmas[i]);
+            const double sg = (double)sigmas[i];
+            const float efactor = (float)(-1.0 / (2.0 * sg * sg));
+            sfac[i] = type == 3 ? (float)(1.0 / pow(sqrt(2.0 * M_PI) * sg, 3.0)) : (float)(1.0 / (2.0 * M_PI * sg * sg));
+            scales[i] = sqrt(-(double)efactor * 1.4426950408889634074 * (double)KDE_TAB);
+            const double rho = scales[i] / c.scale, rcut = cutoff_sigmas * sg * scales[i];
+            KdeTiling T = c.tl;
+            T.gs.b0x = (double)box6[0] * scales[i]; T.gs.b0y = (double)box6[1] * scales[i];
+            T.gs.wx = (double)(float)(box6[3] - box6[0]) * scales[i]; T.gs.wy = (double)(float)(box6[4] - box6[1]) * scales[i];
+            T.cxs = T.gs.wx / T.gs.ncx; T.cys = T.gs.wy / T.gs.ncy;
+            T.gs.inv_cx = 1.0 / T.cxs; T.gs.inv_cy = 1.0 / T.cys;
+            T.rc2 = rcut * rcut;
+            T.mf = (int)ceil(rcut / T.cys);
+            const int mxmax = (int)ceil(rcut / T.cxs);
+            T.wmax = periodic ? T.gs.ncx - 2 * mxmax - 1 : (1 << 30);
+            if (T.mf > 4096 || (periodic && (T.wmax < 1 || T.B + 2 * T.mf > T.gs.ncy))) { shared = false; break; }
+            const double tside = T.cys * T.B;
+            const double ex = (double)(2 * mxmax + 2) * T.cxs + 2.0 * tside, ey = (T.B + T.mf + 1) * T.cys;
+            const double rwin = ex * ex + ey * ey;
+            clamps[i] = type == 3 || !periodic || !(rwin < 256.0 * 1000.0);
+            Ts[i] = T;
+            (void)rho;
+        }
+    } else shared = false;
+    if (!shared) {
+        for (int i = 0; i < nsigma; i++) {
+            const int rc = pairs ? ms_kde_evaluated_pairs(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, pairs + i, ws, ws_bytes, stream)
+                                 : ms_kde_labels(verts, nv, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, raw + (size_t)i * per, ws, ws_bytes, stream);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    if (kde_build_groups(c, s)) return 2;
+    const int nbins_s = c.tl.gs.ncx * c.tl.gs.ncy * nlabels;
+    const KdeGrid gs_ref = c.tl.gs, gt_ref = c.g;
+    if (pairs) {             // diagnostic: the pairs every sigma's launch evaluates on this shared binning
+        for (int i = 0; i < nsigma; i++) {
+            c.tl = Ts[i]; c.tl.gscale = scales[i] / c.scale;
+            MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
+            MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
+            MS_K(NULL, s);
+            MS_LAUNCH_CHECK();
+            unsigned long long h = 0ull;
+            MS_CUDA(cudaMemcpyAsync(&h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
+            MS_CUDA(cudaStreamSynchronize(s));
+            pairs[i] = (double)h;
+        }
+        return 0;
+    }
+    for (int k = 0; k < nsigma; k++) {
+        const int i = k == 0 ? ref : (k <= ref ? k - 1 : k);           // the reference sigma first: its coordinates are staged
+        if (i != ref || k != 0) {
+            const KdeGrid gref = gs_ref, gref_t = gt_ref;      // every array folds on the grid it was binned on
+            const double wxi = Ts[i].gs.wx, wyi = Ts[i].gs.wy;
+            MS_K("kde_restage", s);
+            if (type == 2) {
+                k_kde_restage<2><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, c.tperm, nv, NULL, c.scale, gref_t, scales[i], wxi, wyi, (double2*)c.tgt_sorted);
+                k_kde_restage<2><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, c.sperm, nv, c.sstart + nbins_s, c.scale, gref, scales[i], wxi, wyi, (double2*)c.src_sorted);
+            } else {
+                k_kde_restage<3><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, c.tperm, nv, NULL, c.scale, gref_t, scales[i], wxi, wyi, (double4*)c.tgt_sorted);
+                k_kde_restage<3><<<ms_blocks(nv, 256), 256, 0, s>>>(verts, c.sperm, nv, c.sstart + nbins_s, c.scale, gref, scales[i], wxi, wyi, (double4*)c.src_sorted);
+            }
+            MS_LAUNCH_CHECK();
+        }
+        c.tl = Ts[i]; c.clamp = clamps[i];
+        // group x extents were measured on the reference staging: they scale with the coordinates
+        c.tl.gscale = scales[i] / c.scale;
+        double *out = raw + (size_t)i * per;
+        const int rc = kde_launch_cells(c, nv, out, s, false);
+        if (rc) return rc;
+        MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(out, nv * nlabels, (double)sfac[i]);
+    }
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ms_kde_labels_multi(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                                   int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                                   double *raw, void *ws, size_t ws_bytes, void *stream) {
+    MS_REQUIRE(raw != NULL, "ms_kde_labels_multi: raw is required");
+    return kde_labels_multi_impl(verts, nv, labels, nlabels, type, periodic, box6, sigmas, nsigma, cutoff_sigmas, raw, NULL, ws, ws_bytes, stream);
+}
+extern "C" int ms_kde_labels_multi_pairs(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                                         int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                                         double *pairs, void *ws, size_t ws_bytes, void *stream) {
+    MS_REQUIRE(pairs != NULL, "ms_kde_labels_multi_pairs: pairs is required");
+    return kde_labels_multi_impl(verts, nv, labels, nlabels, type, periodic, box6, sigmas, nsigma, cutoff_sigmas, NULL, pairs, ws, ws_bytes, stream);
 }
 
 extern "C" size_t ms_kde_select_workspace_bytes(int64_t nv) { return ms_align((size_t)nv * 8) + ms_align(((size_t)nv / RED_T + 2) * 8) + 1024; }

@@ -123,6 +123,23 @@ class LeafletFrame(object):
         L = _lib.lib()
         st = _lib.stream_ptr(self.device)
         fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
+        raws = {}
+        if fused and len(sigmas) > 1:      # all sigmas of a type on one binning of the vertices
+            nl = int(self.label_values.shape[0])
+            need = len(sigmas) * nl * self.nv
+            if getattr(self, 'kde_raw_multi', None) is None or self.kde_raw_multi.numel() < need:
+                self.kde_raw_multi = torch.empty(need, dtype=torch.float64, device=self.device)
+            import ctypes as C
+            sg = (C.c_float * len(sigmas))(*[float(x) for x in sigmas])
+            for t in types:
+                _lib.check(L.ms_kde_labels_multi(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(), nl, int(t),
+                                                 int(self.periodic), self._box(cutoff_sigmas), sg, len(sigmas), float(cutoff_sigmas),
+                                                 self.kde_raw_multi.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
+                           'ms_kde_labels_multi')
+                if len(types) > 1:
+                    raise NotImplementedError('run_densities: one density type per call when sigmas share a binning')
+                for i, s in enumerate(sigmas):
+                    raws[(t, float(s))] = self.kde_raw_multi[i * nl * self.nv:(i + 1) * nl * self.nv]
         for t in types:
             for s in sigmas:
                 if not fused:
@@ -131,10 +148,13 @@ class LeafletFrame(object):
                         self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, l, s), t, s, get_nlipids, ids, cutoff_sigmas)
                     continue
                 nl = int(self.label_values.shape[0])
-                _lib.check(L.ms_kde_labels(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(), nl, int(t),
-                                           int(self.periodic), self._box(cutoff_sigmas), float(s), float(cutoff_sigmas),
-                                           self.kde_raw.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
-                           'ms_kde_labels')
+                raw = raws.get((t, float(s)))
+                if raw is None:
+                    raw = self.kde_raw
+                    _lib.check(L.ms_kde_labels(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(), nl, int(t),
+                                               int(self.periodic), self._box(cutoff_sigmas), float(s), float(cutoff_sigmas),
+                                               self.kde_raw.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
+                               'ms_kde_labels')
                 for li, l in enumerate(['all'] + [v.item() for v in self.label_values]):
                     name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)
                     out = self.densities.get(name)
@@ -143,7 +163,7 @@ class LeafletFrame(object):
                                                       torch.empty(self.nv, dtype=torch.float32, device=self.device))
                     sel = np.ones(nl, np.uint8) if li == 0 else np.eye(nl, dtype=np.uint8)[li - 1]
                     nsel = float(self.nv if li == 0 else self.label_counts[li - 1])
-                    _lib.check(L.ms_kde_select(self.kde_raw.data_ptr(), self.nv, nl, sel.tobytes(), nsel, int(bool(get_nlipids)),
+                    _lib.check(L.ms_kde_select(raw.data_ptr(), self.nv, nl, sel.tobytes(), nsel, int(bool(get_nlipids)),
                                                out[0].data_ptr(), out[1].data_ptr(), self.kde_sel_ws.data_ptr(),
                                                self.kde_sel_ws.numel(), st), 'ms_kde_select')
 
@@ -171,6 +191,16 @@ class LeafletFrame(object):
         total = 0.0
         out = C.c_double(0)
         fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
+        if fused and len(sigmas) > 1:          # the sigmas share one binning (ms_kde_labels_multi)
+            sg = (C.c_float * len(sigmas))(*[float(x) for x in sigmas])
+            per = (C.c_double * len(sigmas))()
+            for t in types:
+                _lib.check(L.ms_kde_labels_multi_pairs(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(),
+                                                       int(self.label_values.shape[0]), int(t), int(self.periodic), self._box(cutoff_sigmas),
+                                                       sg, len(sigmas), float(cutoff_sigmas), per, self.kde_ws.data_ptr(),
+                                                       self.kde_ws.numel(), _lib.stream_ptr(self.device)), 'ms_kde_labels_multi_pairs')
+                total += sum(per)
+            return total
         for t in types:
             for s in sigmas:
                 if fused:

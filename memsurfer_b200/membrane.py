@@ -270,6 +270,19 @@ class Membrane(object):
         lidxs = np.where(np.isin(self.labels, labels))[0]
         self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas, lazy=True))
 
+    def _prefetch_densities(self, types, sigmas):
+        if self.labels is None or self.memb_smooth is None or len(sigmas) < 2:
+            return
+        values, inverse = self._label_table()
+        if values.shape[0] > self.MAX_FUSED_LABELS:
+            return
+        mesh = self.memb_smooth
+        if mesh._label_index is None:
+            mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
+        for t in types:
+            if t in (2, 3):
+                mesh.density_labels_prefetch(t, sigmas, self.KDE_CUTOFF_SIGMAS)
+
     @staticmethod
     def compute_thickness(a, b, mtype='smooth'):
         """Leaflet thickness: distance of every vertex of one membrane's surface to the other's
@@ -285,6 +298,8 @@ class Membrane(object):
     @staticmethod
     def compute_densities(membranes, types, sigmas, get_nlipdis, l):
         labels = [] if l == 'all' else [l]
+        for m in membranes:            # label-fused path: all sigmas of a type on one binning of the vertices
+            m._prefetch_densities(types, sigmas)
         for t in types:
             for s in sigmas:
                 name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)

@@ -445,6 +445,31 @@ class TriMesh(object):
         cache[key] = raw
         return raw
 
+    def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0):
+        """Raw per-label sums of SEVERAL sigmas in one ms_kde_labels_multi call (the vertices are binned once);
+        fills the cache density_labels_device reads.  No-op for sigmas that are already cached."""
+        _lib.require_cuda()
+        L = _lib.lib()
+        dev = self.device
+        d = self._dev
+        cache = d.setdefault('kde_raw', {})
+        todo = [float(s) for s in sigmas if (int(type), float(s), float(cutoff_sigmas)) not in cache]
+        if len(todo) < 2 or self._label_index is None:
+            return
+        kverts = self._kde_verts_device()
+        nv = kverts.shape[0]
+        if 'labels' not in d:
+            d['labels'] = _lib.h2d(self._label_index, dev)
+        raw = torch.empty((len(todo), self._nlabels, nv), dtype=torch.float64, device=dev)
+        ws = self._workspace('kde_ws', L.ms_kde_labels_multi_workspace_bytes(nv, self._nlabels))
+        sg = (_lib.C.c_float * len(todo))(*todo)
+        _lib.check(L.ms_kde_labels_multi(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
+                                         int(bool(self.periodic)), self._kde_box(cutoff_sigmas), sg, len(todo),
+                                         float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
+                                         _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
+        for i, s_ in enumerate(todo):
+            cache[(int(type), s_, float(cutoff_sigmas))] = raw[i]
+
     def density_select_device(self, raw, select, get_nlipids):
         """Normalised density of the union of the selected labels from the raw per-label sums."""
         L = _lib.lib()
