@@ -133,6 +133,35 @@ def d2h(t):
 
 
 _copy_streams = {}
+_work_streams = {}
+
+
+def next_stream(device, nstreams=2):
+    """Round-robin over a small pool of work streams per device.  Every Membrane (and the meshes it drives) runs
+    on one of them, so that the stream synchronisations of one leaflet (read-backs of counts, result downloads)
+    do not wait for the kernels another leaflet still has in flight."""
+    key = torch.device(device).index or 0
+    pool = _work_streams.setdefault(key, {"streams": [], "next": 0})
+    if len(pool["streams"]) < nstreams:
+        pool["streams"].append(torch.cuda.Stream(device=device))
+    st = pool["streams"][pool["next"] % len(pool["streams"])]
+    pool["next"] += 1
+    return st
+
+
+def home_stream(fn):
+    """Method decorator: run on the object's home stream (`self._stream`) when it has one."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrap(self, *a, **k):
+        st = getattr(self, "_stream", None)
+        if st is None or torch.cuda.current_stream(st.device) == st:
+            return fn(self, *a, **k)
+        with torch.cuda.stream(st):
+            return fn(self, *a, **k)
+    return wrap
+
 
 
 def copy_stream(device):

@@ -104,16 +104,11 @@ class Membrane(object):
         # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
         # later fit_points_to_box_xy(): normals are computed on these coordinates.  The PointSet copy
         # lives in HBM: the upload starts now and self.points is not touched before it has landed.
-        self._pset_dev, self._pset_event = None, None
-        if torch.cuda.is_available():
-            self._pset_dev = _lib.h2d(self.points, self.device)
-            self._pset_event = torch.cuda.Event()
-            self._pset_event.record(torch.cuda.current_stream(self.device))
+        self._pset_dev, self._pset_event, self._stream = None, None, None
         self._pset_nbytes = self.points.nbytes
-        # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist)
-        if self._pset_dev is not None and kwargs.get('check_overlaps', True):
-            from .utils import test_overlapping_points
-            test_overlapping_points(self.points, fix=False, points_dev=self._pset_dev)
+        if torch.cuda.is_available():
+            self._stream = _lib.next_stream(self.device)
+            self._upload_and_check(kwargs.get('check_overlaps', True))
 
         self.pnormals = None
         self._pnormals_f64 = None
@@ -128,11 +123,28 @@ class Membrane(object):
         self.properties = {}
         self.info = {}
 
+    @_lib.home_stream
+    def _upload_and_check(self, check_overlaps):
+        self._pset_dev = _lib.h2d(self.points, self.device)
+        self._pset_event = torch.cuda.Event()
+        self._pset_event.record(torch.cuda.current_stream(self.device))
+        # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist)
+        if check_overlaps:
+            from .utils import test_overlapping_points
+            test_overlapping_points(self.points, fix=False, points_dev=self._pset_dev)
+
+    def _adopt(self, mesh):
+        """The meshes this membrane drives run on its stream."""
+        if mesh is not None and mesh._stream is None:
+            mesh._stream = self._stream
+        return mesh
+
     @property
     def pnormals_f64(self):
         """fp64 twin of `pnormals` (not part of the reference API; fetched from the device on first use)."""
         if self._pnormals_f64 is None and self._pnormals_f64_dev is not None:
-            self._pnormals_f64 = _lib.d2h(self._pnormals_f64_dev)
+            with torch.cuda.stream(self._stream):
+                self._pnormals_f64 = _lib.d2h(self._pnormals_f64_dev)
             self._pnormals_f64_dev = None
         return self._pnormals_f64
 
@@ -152,6 +164,7 @@ class Membrane(object):
         return nadjusted
 
     # ---------------------------------------------------------------------- point normals (GPU)
+    @_lib.home_stream
     def compute_pnormals(self, knbrs=18, ndir_hint=+1):
         """(npoints,3) float32 normals by (k+1)-NN PCA + MST orientation (membrane.py:124-157)."""
         if self.pnormals is not None:
@@ -179,6 +192,7 @@ class Membrane(object):
         self.compute_pnormals()
         self.surf_poisson = None
 
+    @_lib.home_stream
     def set_membrane_surface(self, spoints, ppoints, planar_bbox):
         """Inject a producer's output: points projected on the smooth surface and on the plane."""
         self.spoints = np.asarray(spoints, np.float32)
@@ -186,6 +200,7 @@ class Membrane(object):
         self._planar_bbox = (np.asarray(planar_bbox[0], np.float32), np.asarray(planar_bbox[1], np.float32))
         self._build_meshes()
 
+    @_lib.home_stream
     def compute_membrane_surface(self):
         """Stand-in for membrane.py:186-234 without Poisson/CGAL: spoints = points, ppoints = their
         (x,y); planar bbox = the periodic box.  Everything after that follows the reference."""
@@ -203,6 +218,8 @@ class Membrane(object):
         self.memb_planar = TriMesh(self.ppoints, periodic=self.periodic, label='memb_planar', device=dev)
         self.memb_smooth = TriMesh(self.spoints, periodic=self.periodic, label='memb_smooth', device=dev)
         self.memb_exact = TriMesh(self.points, periodic=self.periodic, label='memb_exact', device=dev)
+        for mesh in (self.memb_planar, self.memb_smooth, self.memb_exact):
+            self._adopt(mesh)
         if self.periodic:
             self.memb_planar.set_bbox(*self._planar_bbox)
             self.memb_smooth.set_bbox(self.spoints.min(axis=0), self.spoints.max(axis=0))
@@ -214,11 +231,12 @@ class Membrane(object):
             self.memb_planar.set_bbox(self.ppoints.min(axis=0), self.ppoints.max(axis=0))
 
     # ---------------------------------------------------------------------- properties / densities (GPU)
+    @_lib.home_stream
     def compute_properties(self, mtype='smooth'):
         """Vertex normals, point areas and curvatures of the chosen mesh (membrane.py:237-247).  The results
         land in mesh.attributes; the launch and the downloads are only queued here."""
         assert mtype == 'smooth' or mtype == 'exact'
-        mesh = self.memb_exact if mtype == 'exact' else self.memb_smooth
+        mesh = self._adopt(self.memb_exact if mtype == 'exact' else self.memb_smooth)
         mesh._properties_lazy()
 
     MAX_FUSED_LABELS = 64
@@ -242,6 +260,7 @@ class Membrane(object):
                     np.unique(lab, return_inverse=True, return_counts=True)
         return self._label_values, self._label_inverse
 
+    @_lib.home_stream
     def compute_density(self, type, sigma, name, get_nlipdis, labels=[], cutoff_sigmas=None):
         """Density of the points carrying one of `labels` (all points if empty) on memb_smooth
         (membrane.py:252-274).  With point labels available the label-fused kernel is used: the first
@@ -251,7 +270,7 @@ class Membrane(object):
             cutoff_sigmas = self.KDE_CUTOFF_SIGMAS
         if type < 1 or type > 3:
             raise ValueError(f'Invalid density type, {type}. Should be 1 (geodesic), 2 (2D) or 3 (3D)')
-        mesh = self.memb_smooth
+        mesh = self._adopt(self.memb_smooth)
         if len(labels) > 0 and self.labels is None:
             raise ValueError('Cannot compute density of selected labels, because point labels are not available')
         fused = self.labels is not None and type != 1
@@ -270,13 +289,14 @@ class Membrane(object):
         lidxs = np.where(np.isin(self.labels, labels))[0]
         self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas, lazy=True))
 
+    @_lib.home_stream
     def _prefetch_densities(self, types, sigmas):
         if self.labels is None or self.memb_smooth is None or len(sigmas) < 2:
             return
         values, inverse = self._label_table()
         if values.shape[0] > self.MAX_FUSED_LABELS:
             return
-        mesh = self.memb_smooth
+        mesh = self._adopt(self.memb_smooth)
         if mesh._label_index is None:
             mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
         for t in types:
@@ -288,6 +308,8 @@ class Membrane(object):
         """Leaflet thickness: distance of every vertex of one membrane's surface to the other's
         (membrane.py:277-286 -> TriMesh::distance_to_other_mesh); stored in .properties['thickness']."""
         assert mtype in ['smooth', 'exact']
+        for m in (a, b):
+            m._adopt(m.memb_exact); m._adopt(m.memb_smooth)
         if mtype == 'exact':
             a.properties['thickness'] = a.memb_exact.compute_distance_to_surface(b.memb_exact)
             b.properties['thickness'] = b.memb_exact.compute_distance_to_surface(a.memb_exact)

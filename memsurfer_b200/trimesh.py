@@ -29,12 +29,13 @@ class LazyF64(dict):
         self._parked = {}
 
     def park(self, name, tensor):
-        self._parked[name] = tensor
+        self._parked[name] = (tensor, torch.cuda.current_stream(tensor.device))
         super().pop(name, None)
 
     def __missing__(self, name):
-        t = self._parked.pop(name)            # KeyError if unknown, like a dict
-        v = _lib.d2h(t)
+        t, st = self._parked.pop(name)        # KeyError if unknown, like a dict
+        with torch.cuda.stream(st):           # the stream that produced it
+            v = _lib.d2h(t)
         self[name] = v
         return v
 
@@ -84,6 +85,7 @@ class TriMesh(object):
         self._label_index = None         # optional per-vertex integer labels (label-fused KDE)
         self._nlabels = 0
         self._dev = {}                   # device-resident buffers
+        self._stream = None              # home stream (set by the Membrane that drives this mesh)
 
     def tag(self):
         return f'[{self.label}, periodic={self.periodic}]'
@@ -173,6 +175,7 @@ class TriMesh(object):
             faces[F0:] = self._trimmed_faces
         return verts, faces
 
+    @_lib.home_stream
     def to_device(self, pinned=None):
         """Stage verts ++ dup verts and faces ++ trimmed faces in HBM (TriMesh.hpp:360-364 layout).  The pieces
         are uploaded straight into slices of the device arrays (no concatenated host copy)."""
@@ -217,6 +220,7 @@ class TriMesh(object):
         yw = np.float32(0.5) * (self.bbox[1, 1] - self.bbox[0, 1])
         return float(xw), float(yw)
 
+    @_lib.home_stream
     def _topology_device(self):
         d = self.to_device()
         if 'csr_off' in d:
@@ -234,6 +238,7 @@ class TriMesh(object):
                                       ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_mesh_topology')
         return d
 
+    @_lib.home_stream
     def properties_device(self):
         """One fused launch: vertex normals, point areas, mean and Gaussian curvature (device tensors)."""
         d = self._topology_device()
@@ -257,6 +262,7 @@ class TriMesh(object):
         return d
 
     # ---------------------------------------------------------------------- computation of attributes
+    @_lib.home_stream
     def _properties_lazy(self):
         """Queue the fused properties launch and the four downloads; nothing is waited for here."""
         if 'pnormal' in self.attributes:
@@ -283,6 +289,7 @@ class TriMesh(object):
         return self.attributes['mean_curv'], self.attributes['gaus_curv']
 
     # ---------------------------------------------------------------------- closest point / thickness
+    @_lib.home_stream
     def closest_point_device(self, queries_dev):
         """Closest point of THIS mesh's own faces to every query (device tensors in, device tensors out):
         (face id i32 (n,), barycentric f64 (n,3), distance f64 (n,), distance f32 (n,))."""
@@ -306,6 +313,7 @@ class TriMesh(object):
                                       d32.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_closest_point')
         return fid, bary, d64, d32
 
+    @_lib.home_stream
     def project_on_surface(self, points):
         """(face ids (n,) int, barycentric coordinates (n,3) f64) of the closest surface point of every
         point (TriMesh::project_on_surface, TriMesh_cgal.cpp:295-363, without the float packing)."""
@@ -352,9 +360,12 @@ class TriMesh(object):
         q = d['verts'][:self.vertices.shape[0]]
         if other.device != self.device:
             q = q.to(other.device)
+        if self._stream is not None and other._stream is not self._stream:     # the queries were staged on this mesh's stream
+            (other._stream or torch.cuda.current_stream(other.device)).wait_stream(self._stream)
         _, _, d64, d32 = other.closest_point_device(q)
-        self.attributes_f64.park('distance_to_surface', d64)
-        return _lib.d2h(d32)
+        with torch.cuda.stream(other._stream or torch.cuda.current_stream(other.device)):    # where the result was produced
+            self.attributes_f64.park('distance_to_surface', d64)
+            return _lib.d2h(d32)
 
     # ---------------------------------------------------------------------- KDE
     def _kde_box(self, cutoff_sigmas):
@@ -392,6 +403,7 @@ class TriMesh(object):
             ws = self._dev[key] = _lib.workspace(nbytes, self.device)
         return ws
 
+    @_lib.home_stream
     def density_device(self, type, sigma, get_nlipids, pidxs_dev=None, cutoff_sigmas=0.0):
         """Run ms_kde on device-resident inputs; returns (f64 tensor, f32 tensor)."""
         _lib.require_cuda()
@@ -422,6 +434,7 @@ class TriMesh(object):
         self._dev.pop('labels', None)
         self._dev.pop('kde_raw', None)
 
+    @_lib.home_stream
     def density_labels_device(self, type, sigma, cutoff_sigmas=0.0):
         """(nlabels, V) f64 device tensor of raw per-label pair sums (cached per (type, sigma, cut-off))."""
         _lib.require_cuda()
@@ -445,6 +458,7 @@ class TriMesh(object):
         cache[key] = raw
         return raw
 
+    @_lib.home_stream
     def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0):
         """Raw per-label sums of SEVERAL sigmas in one ms_kde_labels_multi call (the vertices are binned once);
         fills the cache density_labels_device reads.  No-op for sigmas that are already cached."""
@@ -470,6 +484,7 @@ class TriMesh(object):
         for i, s_ in enumerate(todo):
             cache[(int(type), s_, float(cutoff_sigmas))] = raw[i]
 
+    @_lib.home_stream
     def density_select_device(self, raw, select, get_nlipids):
         """Normalised density of the union of the selected labels from the raw per-label sums."""
         L = _lib.lib()
@@ -486,6 +501,7 @@ class TriMesh(object):
                                    _lib.stream_ptr(dev)), 'ms_kde_select')
         return o64, o32
 
+    @_lib.home_stream
     def compute_density_labels(self, type, sigma, name, get_nlipids, select, cutoff_sigmas=0.0, lazy=False):
         """Label-fused twin of compute_density: `select` = label indices (set_vertex_labels) whose vertices
         are the sources.  Same result as compute_density with the ids of those vertices."""
@@ -505,6 +521,7 @@ class TriMesh(object):
             return dict.__getitem__(self._fields, name)
         return self._fields[name]
 
+    @_lib.home_stream
     def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0, lazy=False):
         """(V,) float32 density (trimesh.py:324-361 -> TriMesh::kde TriMesh_kde.cpp:443-532).
 
