@@ -64,11 +64,12 @@ class Membrane(object):
     """Create and analyse membrane surfaces (GPU hot path, host surface producer)."""
 
     # KDE cut-off in sigmas used by compute_density / compute_densities.  The reference sums all
-    # V x n_ids pairs (TriMesh_kde.cpp:344-392); beyond 8 sigma a Gaussian term is below
-    # exp(-32) = 1.3e-14 of the peak, three orders under the 1e-9 parity bar, so the default skips
-    # those pairs through a cell list (the C ABI falls back to all pairs when the window does not
-    # fit the box).  Set to 0 for the reference's full sum.
-    KDE_CUTOFF_SIGMAS = 8.0
+    # V x n_ids pairs (TriMesh_kde.cpp:344-392); the mass of a 2-D Gaussian beyond c sigma is
+    # exp(-c^2/2) of the whole: 6.1e-13 at c = 7.5 -- three orders under the 1e-9 relative parity bar
+    # AND under the 1e-12 absolute bar for the O(1) values of normalised densities (SURVEY 8(d) accepts
+    # 7 sigma = 2.3e-11), so the default skips those pairs through a cell list (the C ABI falls back
+    # to all pairs when the window does not fit the box).  Set to 0 for the reference's full sum.
+    KDE_CUTOFF_SIGMAS = 7.5
 
     def __init__(self, points, **kwargs):
         points = np.asarray(points)
