@@ -322,21 +322,24 @@ def main():
         bytes_io = {"h2d": 0, "d2h": 0}
 
         def step_e2e():
-            # one frame as a user script runs it: build both Membranes from host arrays, queue the three
-            # stages per leaflet, then read EVERY result back as numpy (downloads included in the timing)
+            # one frame in the order of the reference's own driver (examples/ex_3lipid.py:165-175): build BOTH
+            # membranes from host arrays (Membrane.compute: point normals + surface; the surface is the host
+            # producer's output, injected), then properties and compute_densities([top, bottom], ...) for 'all'
+            # and every lipid type; finally EVERY result is read back as numpy (downloads inside the timing)
             h2d = d2h = 0
             ms = []
             for lf in leaflets:
                 m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=device)
                 pn = m.compute_pnormals(18)
                 h2d += m._pset_nbytes; d2h += pn.nbytes
-                m.memb_smooth = new_mesh(lf, device)            # host producer's output, injected
+                m.memb_smooth = new_mesh(lf, device)
+                ms.append(m)
+            for m, lf in zip(ms, leaflets):
                 m.compute_properties('smooth')
                 h2d += sum(a.nbytes for a in m.memb_smooth._dev['_host'])
-                for l in ['all'] + list(range(len(FRACTIONS))):
-                    Membrane.compute_densities([m], [2], SIGMAS, True, l)
                 h2d += 4 * lf["labels"].shape[0]                # the per-vertex label index
-                ms.append(m)
+            for l in ['all'] + list(range(len(FRACTIONS))):
+                Membrane.compute_densities(ms, [2], SIGMAS, True, l)
             recs = []
             for m in ms:
                 mesh = m.memb_smooth

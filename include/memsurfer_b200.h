@@ -169,6 +169,12 @@ size_t ms_overlap_workspace_bytes(int64_t m);
 int ms_overlapping_pairs(const float *points, int64_t m, double dthreshold, int32_t *pairs, int64_t max_pairs,
                          int64_t *npairs, double *min_above, void *ws, size_t ws_bytes, void *stream);
 
+/* Same search without any read-back: box4 (host, may be NULL = measure on the device, which syncs) = xy extent for
+ * the cell list {xmin, ymin, xmax, ymax}; result_dev (device, 2 x uint64) receives {pair count, IEEE bits of
+ * the smallest distance above the threshold (+inf if none)}.  Asynchronous when box4 is given.          */
+int ms_overlapping_pairs_async(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs,
+                               int64_t max_pairs, unsigned long long *result_dev, void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- closest point / thickness
  * Replaces TriMesh::project_on_surface (memsurfer/src/TriMesh_cgal.cpp:295-363: CGAL AABB tree over the
  * mesh's own faces, closest_point_and_primitive per query, barycentric coordinates by TriMesh::Point2Bary

@@ -49,6 +49,7 @@ _SIGNATURES = {
     "ms_kde_evaluated_pairs": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i32, _i32, _i32, C.POINTER(_f32), _f32, _f64, C.POINTER(_f64), _vp, _sz, _vp]),
     "ms_overlap_workspace_bytes": (_sz, [_i64]),
     "ms_overlapping_pairs": (C.c_int, [_vp, _i64, _f64, _vp, _i64, C.POINTER(_i64), C.POINTER(_f64), _vp, _sz, _vp]),
+    "ms_overlapping_pairs_async": (C.c_int, [_vp, _i64, _f64, C.POINTER(_f32), _vp, _i64, _vp, _vp, _sz, _vp]),
     "ms_closest_point_workspace_bytes": (_sz, [_i64, _i64]),
     "ms_closest_point": (C.c_int, [_vp, _i64, _vp, _i64, C.POINTER(_f32), _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ms_dfma_probe": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp]),

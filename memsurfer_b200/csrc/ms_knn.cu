@@ -386,10 +386,40 @@ __global__ void __launch_bounds__(128) k_overlap(const float4 *__restrict__ sort
 
 extern "C" size_t ms_overlap_workspace_bytes(int64_t n) { return ms_knn_workspace_bytes(n, 19); }
 
+// box4 (host, may be NULL) = xy extent to lay the cell list over {xmin, ymin, xmax, ymax}: with it nothing is read
+// back before the launch (points outside are clamped into the border cells, which costs speed, not pairs);
+// result_dev (device, 2 x u64) receives {pair count, bits of the smallest distance above the threshold}.
+static int overlap_launch(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs, int64_t max_pairs,
+                          unsigned long long *result_dev, void *ws, size_t ws_bytes, cudaStream_t s);
+
+extern "C" int ms_overlapping_pairs_async(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs,
+                                          int64_t max_pairs, unsigned long long *result_dev, void *ws, size_t ws_bytes, void *stream) {
+    MS_REQUIRE(result_dev != NULL, "ms_overlapping_pairs_async: result_dev is required");
+    return overlap_launch(points, m, dthreshold, box4, pairs, max_pairs, result_dev, ws, ws_bytes, (cudaStream_t)stream);
+}
+
 extern "C" int ms_overlapping_pairs(const float *points, int64_t m, double dthreshold, int32_t *pairs, int64_t max_pairs,
                                     int64_t *npairs_out, double *min_above_out, void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(points && npairs_out && m > 0 && dthreshold >= 0.0 && max_pairs >= 0 && (pairs || max_pairs == 0), "ms_overlapping_pairs: bad arguments");
+    MS_REQUIRE(npairs_out != NULL, "ms_overlapping_pairs: npairs is required");
+    const int rc = overlap_launch(points, m, dthreshold, NULL, pairs, max_pairs, NULL, ws, ws_bytes, s);
+    if (rc) return rc;
+    MsArena A(ws, ws_bytes);
+    const int64_t ncell_max = m + 2048;
+    A.take<int32_t>(m); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<float4>(m);
+    A.take<char>(ms_scan_ws_bytes(ncell_max));
+    unsigned *bb = (unsigned*)A.take<unsigned>(64);
+    unsigned long long h2[2];
+    MS_CUDA(cudaMemcpyAsync(h2, (unsigned long long*)(bb + 8), sizeof(h2), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *npairs_out = (int64_t)h2[0];
+    if (min_above_out) memcpy(min_above_out, &h2[1], 8);
+    return 0;
+}
+
+static int overlap_launch(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs, int64_t max_pairs,
+                          unsigned long long *result_dev, void *ws, size_t ws_bytes, cudaStream_t s) {
+    MS_REQUIRE(points && m > 0 && dthreshold >= 0.0 && max_pairs >= 0 && (pairs || max_pairs == 0), "ms_overlapping_pairs: bad arguments");
     MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_overlapping_pairs: too many points");
     MS_REQUIRE(ws_bytes >= ms_overlap_workspace_bytes(m), "ms_overlapping_pairs: workspace too small");
     const int64_t ncell_max = m + 2048;
@@ -399,19 +429,22 @@ extern "C" int ms_overlapping_pairs(const float *points, int64_t m, double dthre
     float4 *sorted = A.take<float4>(m);
     void *scan_ws = A.take<char>(ms_scan_ws_bytes(ncell_max));
     unsigned *bb = (unsigned*)A.take<unsigned>(64);
-    unsigned long long *res = (unsigned long long*)(bb + 8);            // [0] = pair count, [1] = min distance bits
-    const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
-    const unsigned long long rinit[2] = { 0ull, 0x7ff0000000000000ull };
-    MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
+    unsigned long long *res = result_dev ? result_dev : (unsigned long long*)(bb + 8);   // [0] = pair count, [1] = min distance bits
+    static const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
+    static const unsigned long long rinit[2] = { 0ull, 0x7ff0000000000000ull };
     MS_CUDA(cudaMemcpyAsync(res, rinit, sizeof(rinit), cudaMemcpyHostToDevice, s));
-    MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points, m, bb);
-    unsigned hb[4];
-    MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaStreamSynchronize(s));
     float lo[2], hi[2];
-    for (int d = 0; d < 2; d++) {
-        unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
-        u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
+    if (box4) { lo[0] = box4[0]; lo[1] = box4[1]; hi[0] = box4[2]; hi[1] = box4[3]; }
+    else {
+        MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
+        MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points, m, bb);
+        unsigned hb[4];
+        MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
+        MS_CUDA(cudaStreamSynchronize(s));
+        for (int d = 0; d < 2; d++) {
+            unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
+            u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
+        }
     }
     double wx = (double)hi[0] - lo[0], wy = (double)hi[1] - lo[1];
     MS_REQUIRE(wx == wx && wy == wy && wx < 1e30 && wy < 1e30, "ms_overlapping_pairs: non-finite coordinates");
@@ -434,11 +467,6 @@ extern "C" int ms_overlapping_pairs(const float *points, int64_t m, double dthre
     MS_K("overlap", s); k_overlap<<<ms_blocks(m, 128), 128, 0, s>>>(sorted, m, g, start, dthreshold, pairs, (unsigned long long)max_pairs, res, res + 1);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
-    unsigned long long h2[2];
-    MS_CUDA(cudaMemcpyAsync(h2, res, sizeof(h2), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaStreamSynchronize(s));
-    *npairs_out = (int64_t)h2[0];
-    if (min_above_out) memcpy(min_above_out, &h2[1], 8);
     return 0;
 }
 

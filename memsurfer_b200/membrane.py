@@ -105,7 +105,7 @@ class Membrane(object):
         # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
         # later fit_points_to_box_xy(): normals are computed on these coordinates.  The PointSet copy
         # lives in HBM: the upload starts now and self.points is not touched before it has landed.
-        self._pset_dev, self._pset_event, self._stream = None, None, None
+        self._pset_dev, self._pset_event, self._stream, self._overlap = None, None, None, None
         self._pset_nbytes = self.points.nbytes
         if torch.cuda.is_available():
             self._stream = _lib.next_stream(self.device)
@@ -129,10 +129,18 @@ class Membrane(object):
         self._pset_dev = _lib.h2d(self.points, self.device)
         self._pset_event = torch.cuda.Event()
         self._pset_event.record(torch.cuda.current_stream(self.device))
-        # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist)
+        # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist).  The
+        # search is only queued here (cell list over the given box, no read-back); the verdict is fetched at
+        # the first point where this membrane synchronises anyway (compute_pnormals) or by check_overlaps().
+        self._overlap = None
         if check_overlaps:
-            from .utils import test_overlapping_points
-            test_overlapping_points(self.points, fix=False, points_dev=self._pset_dev)
+            from .utils import OverlapCheck
+            b = self.bbox
+            self._overlap = OverlapCheck(self._pset_dev, (b[0, 0], b[0, 1], b[1, 0], b[1, 1]))
+
+    def check_overlaps(self):
+        """True if no two input points are closer than 1e-5 (the reference's constructor check, membrane.py:84)."""
+        return True if self._overlap is None else self._overlap.report()
 
     def _adopt(self, mesh):
         """The meshes this membrane drives run on its stream."""
@@ -180,6 +188,7 @@ class Membrane(object):
             LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
                            "Some normals may be incorrectly oriented!")
         self.pnormals = _lib.d2h(o32)
+        self.check_overlaps()
         self._pnormals_f64_dev, self._pnormals_f64 = o64, None      # fp64 twin stays in HBM until asked for
         if self.pnormals.shape != (self.npoints, 3):
             raise ValueError(f'PointSet computed incorrect normals (got {self.pnormals.size} values')

@@ -39,6 +39,38 @@ def overlapping_pairs_device(points_dev, dthreshold):
     return p, float(dmin.value)
 
 
+class OverlapCheck(object):
+    """The detection queued on the current stream without any read-back; `report()` fetches the verdict (and
+    warns like the reference) once the caller synchronises anyway."""
+
+    def __init__(self, points_dev, box4, dthreshold=0.00001, max_pairs=4096):
+        _lib.require_cuda()
+        L = _lib.lib()
+        dev = points_dev.device
+        n = int(points_dev.shape[0])
+        self.pairs = torch.empty((max_pairs, 2), dtype=torch.int32, device=dev)
+        self.result = torch.empty(2, dtype=torch.int64, device=dev)
+        self.ws = _lib.workspace(L.ms_overlap_workspace_bytes(n), dev)
+        self.max_pairs, self.done = max_pairs, False
+        b = (C.c_float * 4)(*[float(x) for x in box4])
+        _lib.check(L.ms_overlapping_pairs_async(points_dev.data_ptr(), n, float(dthreshold), b, self.pairs.data_ptr(), max_pairs,
+                                                self.result.data_ptr(), self.ws.data_ptr(), self.ws.numel(), _lib.stream_ptr(dev)),
+                   'ms_overlapping_pairs_async')
+
+    def report(self):
+        """True if no two points overlap; else warn (memsurfer/utils.py:121) and return False."""
+        if self.done:
+            return self.ok
+        nzero = int(self.result[0].item())
+        self.done, self.ok = True, nzero == 0
+        if nzero:
+            p = self.pairs[:min(nzero, self.max_pairs)].cpu().numpy()
+            p = p[np.lexsort((p[:, 1], p[:, 0]))]
+            LOGGER.warning(f'Found {nzero} overlapping points: {[(int(x), int(y)) for x, y in p]}')
+        self.ws = self.pairs = None
+        return self.ok
+
+
 def test_overlapping_points(points, dthreshold=0.00001, fix=False, device='cuda:0', points_dev=None):
     """True if no two points are closer than dthreshold; else warn and return False, or (fix=True) move one point of
     every coincident pair in place exactly as memsurfer/utils.py:118-159 does.  `points_dev`: the same points

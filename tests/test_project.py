@@ -132,4 +132,6 @@ def test_overlapping_points_vs_pdist():
     assert (fixed != bad).any(axis=1).sum() <= 3
     # 2-D input (ppoints) and the Membrane constructor hook
     assert test_overlapping_points(pts[:, :2].copy()) is True
-    Membrane(bad, labels=labels, periodic=True, bbox=bbox)        # warns, does not raise (membrane.py:84)
+    mb = Membrane(bad, labels=labels, periodic=True, bbox=bbox)   # warns, does not raise (membrane.py:84)
+    assert mb.check_overlaps() is False
+    assert Membrane(pts, labels=labels, periodic=True, bbox=bbox).check_overlaps() is True

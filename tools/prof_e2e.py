@@ -34,4 +34,4 @@ def step():
 step(); step()
 pr = cProfile.Profile()
 pr.enable(); step(); pr.disable()
-pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
+pstats.Stats(pr).sort_stats("tottime").print_stats(28)
