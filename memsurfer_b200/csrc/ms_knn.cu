@@ -228,6 +228,64 @@ __device__ __forceinline__ void knn_scan(const float4 *__restrict__ sorted, int 
     }
 }
 
+// Same scan ordered by the squared distance ALONE (one fp64 compare per list slot, all independent, instead of
+// the serial two-compare exchange chain above).  Exact as long as no two distances tie; `tie` is raised
+// whenever a tie could have mattered -- a rejected candidate equal to the current worst, or a pushed-out worst
+// equal to its neighbour -- and the caller then repeats the query with knn_scan (ties are decided by index).
+template <int K>
+__device__ __forceinline__ void knn_scan_fast(const float4 *__restrict__ sorted, int pb, int pe, double qx, double qy, double qz,
+                                              double (&bd)[K], int (&bi)[K], bool &tie) {
+    for (int p = pb; p < pe; p++) {
+        const float4 c = __ldg(sorted + p);
+        const double dx = qx - (double)c.x, dy = qy - (double)c.y, dz = qz - (double)c.z;
+        double cd = dx * dx; cd += dy * dy; cd += dz * dz;
+        const int ci = __float_as_int(c.w);
+        if (!(cd < bd[K - 1])) { tie |= (cd == bd[K - 1]); continue; }
+        if (K > 1) tie |= (bd[K - 1] == bd[K - 2]) && bd[K - 1] < DBL_MAX;
+        // new b[j] = (c < b[j]) ? ((c < b[j-1]) ? b[j-1] : c) : b[j]   (the list is ascending, so the tests are monotone)
+        double last_d = cd; int last_i = ci; bool prev = false;
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            const double cur_d = bd[j]; const int cur_i = bi[j];
+            const bool lt = cd < cur_d;
+            bd[j] = lt ? (prev ? last_d : cd) : cur_d;
+            bi[j] = lt ? (prev ? last_i : ci) : cur_i;
+            last_d = cur_d; last_i = cur_i; prev = lt;
+        }
+    }
+}
+
+// ring-by-ring search around cell (cx,cy) until the K-th distance lies inside the explored square
+template <int K, bool FAST>
+__device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, const Grid &g, const int32_t *__restrict__ start,
+                                           int cx, int cy, double qx, double qy, double qz, double (&bd)[K], int (&bi)[K], bool &tie) {
+    const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
+    for (int r = 0; ; r++) {
+        for (int yy = cy - r; yy <= cy + r; yy++) {
+            if (yy < 0 || yy >= g.ny) continue;
+            const bool full_row = (yy == cy - r) || (yy == cy + r);
+            const int nseg = full_row ? 1 : 2;
+            for (int sg = 0; sg < nseg; sg++) {
+                int x0, x1;
+                if (full_row) { x0 = cx - r; x1 = cx + r; } else { x0 = x1 = (sg == 0 ? cx - r : cx + r); }
+                x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
+                if (x0 > x1) continue;
+                const int pb = __ldg(start + yy * g.nx + x0), pe = __ldg(start + yy * g.nx + x1 + 1);
+                if (FAST) knn_scan_fast<K>(sorted, pb, pe, qx, qy, qz, bd, bi, tie);
+                else      knn_scan<K>(sorted, pb, pe, qx, qy, qz, bd, bi);
+            }
+        }
+        if (cx - r <= 0 && cy - r <= 0 && cx + r >= g.nx - 1 && cy + r >= g.ny - 1) break;
+        // distance to the unexplored region; a side on which the window already reaches the grid edge has none
+        const double b0 = cx - r > 0 ? rx - (double)(cx - r) * g.h : DBL_MAX;
+        const double b1 = cx + r < g.nx - 1 ? (double)(cx + r + 1) * g.h - rx : DBL_MAX;
+        const double b2 = cy - r > 0 ? ry - (double)(cy - r) * g.h : DBL_MAX;
+        const double b3 = cy + r < g.ny - 1 ? (double)(cy + r + 1) * g.h - ry : DBL_MAX;
+        const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
+        if (bm > 0.0 && bd[K - 1] < DBL_MAX && sqrt(bd[K - 1]) < bm * (1.0 - 1e-9)) break;
+    }
+}
+
 template <int K>
 __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict__ sorted, int64_t m, Grid g,
                                                        const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr) {
@@ -243,28 +301,14 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
         qi = __float_as_int(me.w);
         const double qx = me.x, qy = me.y, qz = me.z;
         int cx, cy; cell_of(g, me.x, me.y, cx, cy);
-        const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
-        for (int r = 0; ; r++) {
-            for (int yy = cy - r; yy <= cy + r; yy++) {
-                if (yy < 0 || yy >= g.ny) continue;
-                const bool full_row = (yy == cy - r) || (yy == cy + r);
-                const int nseg = full_row ? 1 : 2;
-                for (int sg = 0; sg < nseg; sg++) {
-                    int x0, x1;
-                    if (full_row) { x0 = cx - r; x1 = cx + r; } else { x0 = x1 = (sg == 0 ? cx - r : cx + r); }
-                    x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
-                    if (x0 > x1) continue;
-                    knn_scan<K>(sorted, __ldg(start + yy * g.nx + x0), __ldg(start + yy * g.nx + x1 + 1), qx, qy, qz, bd, bi);
-                }
-            }
-            if (cx - r <= 0 && cy - r <= 0 && cx + r >= g.nx - 1 && cy + r >= g.ny - 1) break;
-            // distance to the unexplored region; a side on which the window already reaches the grid edge has none
-            const double b0 = cx - r > 0 ? rx - (double)(cx - r) * g.h : DBL_MAX;
-            const double b1 = cx + r < g.nx - 1 ? (double)(cx + r + 1) * g.h - rx : DBL_MAX;
-            const double b2 = cy - r > 0 ? ry - (double)(cy - r) * g.h : DBL_MAX;
-            const double b3 = cy + r < g.ny - 1 ? (double)(cy + r + 1) * g.h - ry : DBL_MAX;
-            const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
-            if (bm > 0.0 && bd[K - 1] < DBL_MAX && sqrt(bd[K - 1]) < bm * (1.0 - 1e-9)) break;
+        bool tie = false;
+        knn_search<K, true>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
+#pragma unroll
+        for (int j = 1; j < K; j++) tie |= (bd[j] == bd[j - 1]) && bd[j] < DBL_MAX;      // ties inside the kept list
+        if (tie) {             // rare: repeat with the exact (distance, index) order
+#pragma unroll
+            for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
+            knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
         }
     }
     sm_q[threadIdx.x] = qi;
