@@ -41,7 +41,7 @@ FRACTIONS = [0.4, 0.3, 0.3]
 METRIC = "membrane_frames_per_sec"
 # fp64 FLOP per evaluated 2-D periodic pair / algorithmic bytes per vertex
 FLOP_PER_PAIR_2D = 32.0
-FP64_INSTR_PER_PAIR = {"kde_pairs": 15, "kde_cells": 11, "kde_groups": 11}
+FP64_INSTR_PER_PAIR = {"kde_pairs": 14, "kde_cells": 10, "kde_groups": 10}
 GEOM_BYTES_PER_VERTEX = 84.0
 
 
@@ -386,7 +386,7 @@ def main():
     roof = None
     if kp["launches"]:
         # fp64-pipe instructions per pair, counted in the SASS of the 2-D kernels (cuobjdump):
-        # k_kde_pairs periodic 7 DADD + 5 DFMA + 2 DSETP + 1 DMUL = 15; k_kde_cells 5 DADD + 5 DFMA + 1 DMUL = 11
+        # k_kde_pairs periodic 7 DADD + 4 DFMA + 2 DSETP + 1 DMUL = 14; k_kde_cells / k_kde_groups 5 DADD + 4 DFMA + 1 DMUL = 10
         instr = FP64_INSTR_PER_PAIR[kname]
         pairs_per_launch = pairs_step * psteps / kp["launches"]
         avg_ms = kp["ms"] / kp["launches"]

@@ -112,11 +112,37 @@ def pinned_empty(shape, dtype):
     return torch.empty(tuple(int(x) for x in np.atleast_1d(shape)), dtype=tdt, pin_memory=True).numpy()
 
 
+_copy_pool = None
+COPY_THREADS = int(os.environ.get("MS_COPY_THREADS", "4"))
+COPY_MIN_BYTES = 1 << 20
+
+
+def fast_copy(dst, src):
+    """np.copyto(dst, src, casting='unsafe'); arrays of a megabyte and more are split over a few threads
+    (numpy releases the GIL inside the copy loop, and one core does not saturate host memory)."""
+    import numpy as np
+    global _copy_pool
+    n = dst.size
+    if (COPY_THREADS < 2 or dst.nbytes < COPY_MIN_BYTES or dst.shape != src.shape
+            or not (dst.flags.c_contiguous and src.flags.c_contiguous)):
+        np.copyto(dst, src, casting='unsafe')
+        return
+    if _copy_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _copy_pool = ThreadPoolExecutor(COPY_THREADS - 1, thread_name_prefix="ms_copy")
+    d, s_ = dst.reshape(-1), src.reshape(-1)
+    step = -(-n // COPY_THREADS)
+    futs = [_copy_pool.submit(np.copyto, d[i:i + step], s_[i:i + step], 'unsafe') for i in range(step, n, step)]
+    np.copyto(d[:step], s_[:step], casting='unsafe')
+    for f in futs:
+        f.result()
+
+
 def pinned_copy(a, dtype):
     import numpy as np
     a = np.asarray(a)
     out = pinned_empty(a.shape, dtype)
-    np.copyto(out, a, casting='unsafe')
+    fast_copy(out, a)
     return out
 
 

@@ -32,16 +32,17 @@
 #define KDE_STAGE_BYTES 16384    // all-pairs: bytes per shared-memory stage (1024 double2 / 512 double4)
 #define CELL_STAGE_BYTES 8192    // cell list: bytes per stage
 #define KDE_MAGIC 6755399441055744.0   // 1.5 * 2^52
-#define KDE_TAB 256
+#define KDE_TAB_LOG 9
+#define KDE_TAB (1 << KDE_TAB_LOG)
 #define KDE_RMAX 2147483000.0    // the scaled r must stay below 2^31 (host check or in-kernel clamp)
 
 __device__ const double c_exp2_tab[KDE_TAB] = {
 #include "ms_exp2_table.inc"
 };
-// 2^(-f/256) on [-1/2,1/2], near-minimax, relative error 3.5e-14 (tools/gen_exp2_table.py)
-#define KDE_C1 (-0x1.62e42fefa39dap-9)
-#define KDE_C2 (0x1.ebfbe3a9ac803p-19)
-#define KDE_C3 (-0x1.c6b0902b2f6c8p-29)
+// 2^(-f/512) on [-1/2,1/2] as 1 + f*(C1 + f*C2): near-minimax, relative error 1.3e-11 (tools/gen_exp2_table.py).
+// The 512-entry table buys one DFMA per pair: with 256 entries the same accuracy class needs degree 3.
+#define KDE_C1 (-0x1.62e43144a09e5p-10)
+#define KDE_C2 (0x1.ebfbdff816ce7p-21)
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -67,11 +68,10 @@ __device__ __forceinline__ void kde_term(double r, const double *__restrict__ ta
     const double t = r + KDE_MAGIC;
     const int n = __double2loint(t);
     const double f = r - (t - KDE_MAGIC);             // in [-1/2, 1/2]
-    double p = fma(KDE_C3, f, KDE_C2);
-    p = fma(p, f, KDE_C1);
+    double p = fma(KDE_C2, f, KDE_C1);
     p = fma(p, f, 1.0);
     const double T = tab[n & (KDE_TAB - 1)];          // (1/2, 1]
-    const int e = min(n >> 8, 1021);                  // beyond 2^-1021 the term is held at ~1e-308 (i.e. dropped)
+    const int e = min(n >> KDE_TAB_LOG, 1021);                  // beyond 2^-1021 the term is held at ~1e-308 (i.e. dropped)
     const double sc = __hiloint2double(__double2hiint(T) - (e << 20), __double2loint(T));
     acc = fma(sc, p, acc);
 }
@@ -460,10 +460,10 @@ __device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, doub
 template <bool ECLAMP>
 __device__ __forceinline__ double kde_scale_t(int n, uint32_t tbase) {
     int lo, hi;
-    asm("{ .reg .b32 i, a; and.b32 i, %2, 255; mad.lo.u32 a, i, 128, %3; ld.shared.v2.b32 {%0, %1}, [a]; }"
-        : "=r"(lo), "=r"(hi) : "r"(n), "r"(tbase));
-    if (ECLAMP) hi -= min(n >> 8, 1021) << 20;
-    else        hi -= n << 12;
+    asm("{ .reg .b32 i, a; and.b32 i, %2, %4; mad.lo.u32 a, i, 128, %3; ld.shared.v2.b32 {%0, %1}, [a]; }"
+        : "=r"(lo), "=r"(hi) : "r"(n), "r"(tbase), "n"(KDE_TAB - 1));
+    if (ECLAMP) hi -= min(n >> KDE_TAB_LOG, 1021) << 20;
+    else        hi -= n << (20 - KDE_TAB_LOG);
     return __hiloint2double(hi, lo);
 }
 template <bool ECLAMP>
@@ -471,8 +471,7 @@ __device__ __forceinline__ void kde_term_t(double r, uint32_t tbase, double &acc
     const double t = r + KDE_MAGIC;
     const int n = __double2loint(t);
     const double f = r - (t - KDE_MAGIC);
-    double p = fma(KDE_C3, f, KDE_C2);
-    p = fma(p, f, KDE_C1);
+    double p = fma(KDE_C2, f, KDE_C1);
     p = fma(p, f, 1.0);
     acc = fma(kde_scale_t<ECLAMP>(n, tbase), p, acc);
 }
@@ -588,7 +587,7 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < KDE_TAB * 16; i += GR_THREADS) {
         const double v = c_exp2_tab[i >> 4];
-        tab[i] = CLAMP ? v : __hiloint2double(__double2hiint(v) + ((i >> 4) << 12), __double2loint(v));
+        tab[i] = CLAMP ? v : __hiloint2double(__double2hiint(v) + ((i >> 4) << (20 - KDE_TAB_LOG)), __double2loint(v));
     }
     S *buf = buf_all + (size_t)warp * 2 * GR_CAP;
     uint64_t *bar = bar_all + warp * 2;
@@ -978,7 +977,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
                 const double ex = (double)(2 * mxmax + 2) * T.cxs + 2.0 * tside, ey = (B + T.mf + 1) * T.cys;
                 rwin = ex * ex + ey * ey;
                 // the exponent shift n>>8 is not clamped in the kernel unless CLAMP: keep it far below 1021
-                if (rwin >= 256.0 * 1000.0) rwin = 2.0 * KDE_RMAX;
+                if (rwin >= (double)KDE_TAB * 1000.0) rwin = 2.0 * KDE_RMAX;
             }
         }
     }
@@ -1060,6 +1059,8 @@ static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t
     static int per_sm = 0;                     // resident CTAs per SM of this instantiation (set once; same on every B200)
     if (per_sm == 0) {
         MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // two 2-D CTAs (64 KB table + 48 KB of stages each) only fit with the whole 228 KB carved out as shared memory
+        MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         int n = 0;
         MS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_kde_groups<DIM, CLAMP>, GR_THREADS, smem));
         MS_REQUIRE(n >= 1, "ms_kde: k_kde_groups does not fit an SM (%zu bytes of shared memory)", smem);
@@ -1215,7 +1216,7 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
             const double tside = T.cys * T.B;
             const double ex = (double)(2 * mxmax + 2) * T.cxs + 2.0 * tside, ey = (T.B + T.mf + 1) * T.cys;
             const double rwin = ex * ex + ey * ey;
-            clamps[i] = type == 3 || !periodic || !(rwin < 256.0 * 1000.0);
+            clamps[i] = type == 3 || !periodic || !(rwin < (double)KDE_TAB * 1000.0);
             Ts[i] = T;
             (void)rho;
         }

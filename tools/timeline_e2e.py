@@ -17,14 +17,17 @@ def step(log):
         m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=dev); mark(f"L{i} init")
         m.compute_pnormals(18); mark(f"L{i} pnormals")
         m.memb_smooth = bench.new_mesh(lf, dev); mark(f"L{i} new_mesh")
-        m.compute_properties('smooth'); mark(f"L{i} properties(queue)")
-        m._label_table(); mark(f"L{i}   label table")
-        m._prefetch_densities([2], bench.SIGMAS); mark(f"L{i}   prefetch (labels upload + ms_kde_labels_multi)")
-        for l in ['all', 0, 1, 2]:
-            Membrane.compute_densities([m], [2], bench.SIGMAS, True, l); mark(f"L{i}   densities {l}")
         ms.append(m)
     for i, m in enumerate(ms):
-        m.memb_smooth.attributes.resolve(); m.attributes.resolve(); mark(f"L{i} resolve")
+        m.compute_properties('smooth'); mark(f"L{i} properties(queue)")
+    for l in ['all', 0, 1, 2]:
+        Membrane.compute_densities(ms, [2], bench.SIGMAS, True, l); mark(f"densities {l}")
+    for i, m in enumerate(ms):
+        mesh = m.memb_smooth
+        for k in ('pnormal', 'parea', 'mean_curv', 'gaus_curv'):
+            mesh.attributes[k]
+        mark(f"L{i} read mesh fields")
+        list(m.attributes.values()); mark(f"L{i} read densities")
     torch.cuda.synchronize(); mark("sync")
 
 for _ in range(3): step([])

@@ -28,9 +28,17 @@ __device__ __forceinline__ void term(double r, uint32_t tbase, double &acc) {
     const double t = r + MAGIC;
     const int n = __double2loint(t);
     const double f = r - (t - MAGIC);
-    double p = fma(C3, f, C2);
-    p = fma(p, f, C1);
-    p = fma(p, f, 1.0);
+    double p;
+    if (MODE == 5) { p = fma(C2, f, C1); p = fma(p, f, 1.0); }
+    else { p = fma(C3, f, C2); p = fma(p, f, C1); p = fma(p, f, 1.0); }
+    if (MODE == 5) {
+        int lo, hi;
+        asm("{ .reg .b32 i, a; and.b32 i, %2, 511; mad.lo.u32 a, i, 128, %3; ld.shared.v2.b32 {%0, %1}, [a]; }"
+            : "=r"(lo), "=r"(hi) : "r"(n), "r"(tbase));
+        hi -= n << 11;
+        acc = fma(__hiloint2double(hi, lo), p, acc);
+        return;
+    }
     if (MODE == 1 || MODE == 3) { acc = fma(p, MODE == 1 ? __hiloint2double(0x3ff00000 - (n << 12), 0) : 1.0, acc); return; }
     int lo, hi;
     asm("{ .reg .b32 i, a; and.b32 i, %2, 255; mad.lo.u32 a, i, 128, %3; ld.shared.v2.b32 {%0, %1}, [a]; }"
@@ -43,8 +51,8 @@ template <int MODE, int U, int R>
 __global__ void __launch_bounds__(1024 / (R > 2 ? 2 : 1)) k_loop(int reps, double *out, long long *clk) {
     extern __shared__ __align__(128) unsigned char sm[];
     double *tab = (double*)sm;                  // [256][16]
-    double2 *src = (double2*)(sm + 32768);      // [NSRC]
-    for (int i = threadIdx.x; i < 4096; i += blockDim.x) tab[i] = 1.0 / (1.0 + (i >> 4) / 256.0);
+    double2 *src = (double2*)(sm + (MODE == 5 ? 65536 : 32768));      // [NSRC]
+    for (int i = threadIdx.x; i < (MODE == 5 ? 8192 : 4096); i += blockDim.x) tab[i] = 1.0 / (1.0 + (i >> 4) / 256.0);
     for (int i = threadIdx.x; i < NSRC; i += blockDim.x) src[i] = make_double2(3.0 * (i % 23), 2.5 * (i % 17));
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -79,7 +87,7 @@ static void run(const char *what, int warps_per_sm) {
     const int reps = 40, nblk = 148;
     double *out; long long *clk;
     cudaMalloc(&out, sizeof(double) * nblk * 1024); cudaMalloc(&clk, sizeof(long long) * nblk);
-    const int smem = 32768 + NSRC * 16;
+    const int smem = (MODE == 5 ? 65536 : 32768) + NSRC * 16;
     cudaFuncSetAttribute(k_loop<MODE, U, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     k_loop<MODE, U, R><<<nblk, warps_per_sm * 32, smem>>>(2, out, clk);
     k_loop<MODE, U, R><<<nblk, warps_per_sm * 32, smem>>>(reps, out, clk);
@@ -96,6 +104,7 @@ int main() {
     run<0, 2, 2>("full term", 16); run<0, 2, 2>("full term", 20); run<0, 2, 2>("full term", 24); run<0, 2, 2>("full term", 32);
     run<0, 1, 4>("full term", 8); run<0, 1, 4>("full term", 12); run<0, 1, 4>("full term", 16); run<0, 2, 4>("full term", 16);
     run<0, 1, 3>("full term", 16); run<0, 2, 3>("full term", 16); run<0, 2, 3>("full term", 20);
+    run<5, 2, 2>("deg 2 / 512 table", 16); run<5, 2, 2>("deg 2 / 512 table", 24); run<5, 2, 2>("deg 2 / 512 table", 32);
     run<3, 1, 4>("fp64 only", 16); run<1, 1, 4>("no table", 16);
     return 0;
 }
