@@ -174,27 +174,28 @@ __global__ void __launch_bounds__(128) k_face_records(const float *__restrict__ 
     rec[g] = r;
 }
 
-// Mean curvature, edge pass (vtkCurvatures::GetMeanCurvature): thread (g, ed) owns edge ed of kept face
-// g.  If exactly one other kept face n shares it and n > g, Hf = 3 * len * dihedral / (A_g + A_n) is
-// stored in He[3g+ed] and bit ed of hflag[g] is set; both end points pick it up in the gather.  The
+// Mean curvature, edge pass (vtkCurvatures::GetMeanCurvature): one thread per HALF-EDGE (g, ed) of a kept
+// face g.  If exactly one other kept face n shares the edge and n > g, Hf = 3 * len * dihedral / (A_g + A_n)
+// is stored in He[3g+ed] and hflag[3g+ed] is set; both end points pick it up in the gather.  The
 // neighbour search walks the incident list of an end point that is an original vertex (every face
 // on the edge is in that list); edges between two duplicated vertices feed dropped rows only.
 __global__ void __launch_bounds__(128) k_edge_mean(const float *__restrict__ verts, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
                                                    const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
                                                    const uint8_t *__restrict__ keep, const FaceRec *__restrict__ rec,
                                                    double *__restrict__ He, uint8_t *__restrict__ hflag) {
-    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= nf) return;
+    const int64_t he = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (he >= 3 * nf) return;
+    const int64_t g = he / 3;
+    const int ed = (int)(he - 3 * g);
     uint8_t flag = 0;
     if (__ldg(keep + g)) {
         const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
-#pragma unroll 1
-        for (int ed = 0; ed < 3; ed++) {
-            const int il = ed, ir = (ed + 1) % 3, io = (ed + 2) % 3;
-            const uint32_t vl = t[il], vr = t[ir];
-            uint32_t a = vl, u = vr;                       // walk a's list, look for u
-            if ((int64_t)a >= nv) { a = vr; u = vl; }
-            if ((int64_t)a >= nv) continue;
+        const uint32_t vl = ed == 0 ? t[0] : (ed == 1 ? t[1] : t[2]);
+        const uint32_t vr = ed == 0 ? t[1] : (ed == 1 ? t[2] : t[0]);
+        const uint32_t vo = ed == 0 ? t[2] : (ed == 1 ? t[0] : t[1]);
+        uint32_t a = vl, u = vr;                       // walk a's list, look for u
+        if ((int64_t)a >= nv) { a = vr; u = vl; }
+        if ((int64_t)a < nv) {
             const int b = __ldg(off + a), e = __ldg(off + a + 1);
             int cnt = 0, nb = -1;
             for (int j = b; j < e; j++) {
@@ -203,26 +204,27 @@ __global__ void __launch_bounds__(128) k_edge_mean(const float *__restrict__ ver
                 const uint32_t *th = faces + 3 * (size_t)h;
                 if (__ldg(th) == u || __ldg(th + 1) == u || __ldg(th + 2) == u) { nb = h; cnt++; }
             }
-            if (cnt != 1 || nb <= (int)g) continue;
-            const D3 ore = ldv(verts, vl), end = ldv(verts, vr), oth = ldv(verts, t[io]);
-            const D3 d0 = tri_dir(ore, end, oth);
-            const D3 nfu = unit_or_same(d0);
-            const double Af0 = 0.5 * sqrt(dot(d0, d0));
-            const FaceRec *rn = rec + nb;
-            D3 nn; nn.x = rn->nn[0]; nn.y = rn->nn[1]; nn.z = rn->nn[2];
-            const double Af = Af0 + rn->area;
-            D3 ev = sub(end, ore);
-            const double len = sqrt(dot(ev, ev));
-            if (len != 0.0) { ev.x /= len; ev.y /= len; ev.z /= len; }
-            const double cs = dot(nfu, nn);
-            const double sn = dot(cross(nfu, nn), ev);
-            double Hf = (sn != 0.0 || cs != 0.0) ? len * atan2(sn, cs) : 0.0;
-            if (Af != 0.0) Hf = Hf / Af * 3.0;
-            He[3*g + ed] = Hf;
-            flag |= (uint8_t)(1u << ed);
+            if (cnt == 1 && nb > (int)g) {
+                const D3 ore = ldv(verts, vl), end = ldv(verts, vr), oth = ldv(verts, vo);
+                const D3 d0 = tri_dir(ore, end, oth);
+                const D3 nfu = unit_or_same(d0);
+                const double Af0 = 0.5 * sqrt(dot(d0, d0));
+                const FaceRec *rn = rec + nb;
+                D3 nn; nn.x = rn->nn[0]; nn.y = rn->nn[1]; nn.z = rn->nn[2];
+                const double Af = Af0 + rn->area;
+                D3 ev = sub(end, ore);
+                const double len = sqrt(dot(ev, ev));
+                if (len != 0.0) { ev.x /= len; ev.y /= len; ev.z /= len; }
+                const double cs = dot(nfu, nn);
+                const double sn = dot(cross(nfu, nn), ev);
+                double Hf = (sn != 0.0 || cs != 0.0) ? len * atan2(sn, cs) : 0.0;
+                if (Af != 0.0) Hf = Hf / Af * 3.0;
+                He[he] = Hf;
+                flag = 1;
+            }
         }
     }
-    hflag[g] = flag;
+    hflag[he] = flag;
 }
 
 // One thread per ORIGINAL vertex: walk the incident (face, corner) list in ascending order -- the order
@@ -249,9 +251,8 @@ __global__ void __launch_bounds__(MESH_T) k_vertex_gather(
         if (!__ldg(keep + g)) continue;
         // edges of g that touch v, in ascending edge index: {ci, (ci+2)%3} sorted
         const int e0 = ci == 0 ? 0 : ci - 1, e1 = ci == 0 ? 2 : ci;
-        const unsigned fl = __ldg(hflag + g);
-        if ((fl >> e0) & 1u) { Hsum += He[3*(size_t)g + e0]; hcnt++; }
-        if ((fl >> e1) & 1u) { Hsum += He[3*(size_t)g + e1]; hcnt++; }
+        if (__ldg(hflag + 3*(size_t)g + e0)) { Hsum += He[3*(size_t)g + e0]; hcnt++; }
+        if (__ldg(hflag + 3*(size_t)g + e1)) { Hsum += He[3*(size_t)g + e1]; hcnt++; }
         dA += r->area;
         Ksum -= r->al[ci];
     }
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(MESH_T) k_vertex_gather(
 
 extern "C" size_t ms_mesh_properties_workspace_bytes(int64_t nv, int64_t nf) {
     (void)nv;
-    return ms_align((size_t)(nf + 1) * sizeof(FaceRec)) + ms_align((size_t)(3 * nf + 1) * sizeof(double)) + ms_align((size_t)nf + 1) + 1024;
+    return ms_align((size_t)(nf + 1) * sizeof(FaceRec)) + ms_align((size_t)(3 * nf + 1) * sizeof(double)) + ms_align((size_t)3 * nf + 1) + 1024;
 }
 
 extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
@@ -288,12 +289,12 @@ extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_
     MsArena A(ws, ws_bytes);
     FaceRec *rec = A.take<FaceRec>(nf + 1);
     double *He = A.take<double>(3 * nf + 1);
-    uint8_t *hflag = A.take<uint8_t>(nf + 1);
+    uint8_t *hflag = A.take<uint8_t>(3 * nf + 1);
     const bool want_curv = mean_curv != NULL || gaus_curv != NULL;
     if (nf > 0) {
         MS_K("face_records", s); k_face_records<<<ms_blocks(nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, rec);
-        if (mean_curv) { MS_K("edge_mean", s); k_edge_mean<<<ms_blocks(nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, nv, csr_off, csr_adj, keep, rec, He, hflag); }
-        else MS_CUDA(cudaMemsetAsync(hflag, 0, (size_t)nf, s));
+        if (mean_curv) { MS_K("edge_mean", s); k_edge_mean<<<ms_blocks(3 * nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, nv, csr_off, csr_adj, keep, rec, He, hflag); }
+        else MS_CUDA(cudaMemsetAsync(hflag, 0, (size_t)nf * 3, s));
     }
     (void)want_curv;
     MS_K("vertex_gather", s);
