@@ -202,6 +202,22 @@ size_t ms_field_summary_workspace_bytes(int nfields);
 int ms_field_summary(const double *const *fields, int nfields, int64_t n, double *out4,
                      void *ws, size_t ws_bytes, void *stream);
 
+/* ---------------------------------------------------------------- vertex neighbours / shells
+ * ms_mesh_neighbors replaces TriMesh::need_neighbors (memsurfer/src/TriMesh.cpp:197-255): per vertex the
+ * distinct vertices it shares a face with, in the order the reference's sequential face loop appends them
+ * (ascending face, corner; next then next-next vertex; first appearance wins).  faces (nf,3) u32 = the mesh's
+ * own faces (corners >= nv are ignored), nbr_off (nv+1) i32 offsets, nbr i32 with room for 6*nf entries (may be
+ * NULL: offsets only); *total_out = nbr_off[nv].  Synchronises the stream once.
+ * ms_mesh_shells replaces the breadth-first loop of TriMesh.compute_shells (memsurfer/trimesh.py:364-416):
+ * shells[v] = hop distance to the nearest of the nref reference vertices (-1: not connected to any);
+ * ref (nref) i32 on the device.  *n_unreached = vertices left at -1, *max_shell = largest shell.        */
+size_t ms_mesh_neighbors_workspace_bytes(int64_t nv, int64_t nf);
+int ms_mesh_neighbors(const uint32_t *faces, int64_t nf, int64_t nv, int32_t *nbr_off, int32_t *nbr, int64_t *total_out,
+                      void *ws, size_t ws_bytes, void *stream);
+size_t ms_mesh_shells_workspace_bytes(int64_t nv);
+int ms_mesh_shells(const int32_t *nbr_off, const int32_t *nbr, int64_t nv, const int32_t *ref, int64_t nref,
+                   int32_t *shells, int64_t *n_unreached, int32_t *max_shell, void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- diagnostics
  * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).
  * ms_launch_count: kernels launched by the library since the last reset (process-wide).

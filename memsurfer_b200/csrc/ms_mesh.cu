@@ -304,3 +304,151 @@ extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_
     MS_LAUNCH_CHECK();
     return 0;
 }
+
+// ------------------------------------------------------------------ vertex neighbours and shells
+// TriMesh::need_neighbors (TriMesh.cpp:197-255): the sequential face loop appends, for corner j of face i, the
+// two other vertices of the face to the list of vertex faces[i][j] unless already present.  The list of a
+// vertex is therefore its incident (face, corner) pairs in ascending order, each contributing (next, next-next),
+// de-duplicated by first appearance -- reproduced here by one thread per vertex over the sorted CSR list.
+__global__ void __launch_bounds__(256) k_corner_degree(const uint32_t *__restrict__ faces, int64_t nf, int64_t nv, int32_t *deg) {
+    const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nf) return;
+#pragma unroll
+    for (int i = 0; i < 3; i++) { const uint32_t v = faces[3*f+i]; if ((int64_t)v < nv) atomicAdd(deg + v, 1); }
+}
+
+// FILL == false: cnt[v] = number of distinct neighbours; FILL == true: write them to nbr[noff[v]..]
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_vertex_neighbors(const uint32_t *__restrict__ faces, int64_t nv,
+                                                          const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
+                                                          const int32_t *__restrict__ noff, int32_t *__restrict__ cnt, int32_t *__restrict__ nbr) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nv) return;
+    const int b = off[v], e = off[v + 1];
+    int32_t *mine = FILL ? nbr + noff[v] : NULL;
+    int n = 0;
+    for (int j = b; j < e; j++) {
+        const int packed = adj[j];
+        const int64_t f = packed >> 2; const int c = packed & 3;
+        for (int k = 1; k <= 2; k++) {
+            const int32_t u = (int32_t)faces[3*f + (c + k) % 3];
+            bool seen = false;
+            if (FILL) { for (int q = 0; q < n; q++) seen |= mine[q] == u; }
+            else {
+                // first appearance among the entries before (j, k): rescan them (lists are ~6 faces long)
+                for (int jj = b; jj <= j && !seen; jj++) {
+                    const int p2 = adj[jj]; const int64_t f2 = p2 >> 2; const int c2 = p2 & 3;
+                    const int kend = jj < j ? 2 : k - 1;
+                    for (int kk = 1; kk <= kend; kk++) seen |= (int32_t)faces[3*f2 + (c2 + kk) % 3] == u;
+                }
+            }
+            if (!seen) { if (FILL) mine[n] = u; n++; }
+        }
+    }
+    if (!FILL) cnt[v] = n;
+}
+
+extern "C" size_t ms_mesh_neighbors_workspace_bytes(int64_t nv, int64_t nf) {
+    return 3 * ms_align((size_t)(nv + 1) * sizeof(int32_t)) + ms_align((size_t)(3 * nf + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(nv) + 1024;
+}
+
+// nbr_off: (nv+1) offsets, nbr: up to 6*nf entries (2 per corner), *total_out = nbr_off[nv] (synchronises the stream)
+extern "C" int ms_mesh_neighbors(const uint32_t *faces, int64_t nf, int64_t nv, int32_t *nbr_off, int32_t *nbr, int64_t *total_out,
+                                 void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(nv >= 0 && nf >= 0 && nf < ((int64_t)1 << 29) && nbr_off && total_out, "ms_mesh_neighbors: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_mesh_neighbors_workspace_bytes(nv, nf), "ms_mesh_neighbors: workspace too small");
+    MsArena A(ws, ws_bytes);
+    int32_t *deg = A.take<int32_t>(nv + 1), *cursor = A.take<int32_t>(nv + 1), *off = A.take<int32_t>(nv + 1);
+    int32_t *adj = A.take<int32_t>(3 * nf + 1);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(nv));
+    MS_CUDA(cudaMemsetAsync(deg, 0, sizeof(int32_t) * (nv + 1), s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (nv + 1), s));
+    if (nf > 0) { MS_K("corner_degree", s); k_corner_degree<<<ms_blocks(nf, 256), 256, 0, s>>>(faces, nf, nv, deg); }
+    if (ms_exclusive_scan_i32(deg, off, nv, scan_ws, s)) return 2;
+    if (nf > 0) { MS_K("face_fill", s); k_face_fill<<<ms_blocks(nf, 256), 256, 0, s>>>(faces, nf, nv, off, cursor, adj); }
+    if (nv > 0) {
+        MS_K("sort_lists", s); k_sort_lists<<<ms_blocks(nv, 256), 256, 0, s>>>(nv, off, adj);
+        MS_K("vertex_neighbors", s); k_vertex_neighbors<false><<<ms_blocks(nv, 128), 128, 0, s>>>(faces, nv, off, adj, NULL, deg, NULL);
+    }
+    if (ms_exclusive_scan_i32(deg, nbr_off, nv, scan_ws, s)) return 2;
+    if (nv > 0 && nbr) { MS_K("vertex_neighbors", s); k_vertex_neighbors<true><<<ms_blocks(nv, 128), 128, 0, s>>>(faces, nv, off, adj, nbr_off, NULL, nbr); }
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    int32_t tot = 0;
+    MS_CUDA(cudaMemcpyAsync(&tot, nbr_off + nv, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *total_out = tot;
+    return 0;
+}
+
+// TriMesh.compute_shells (trimesh.py:364-416): breadth-first hop count from the reference vertices.  A FIFO
+// breadth-first search yields the graph distance to the nearest reference vertex, so the level-synchronous
+// sweep below (all vertices of level L label their unvisited neighbours L+1; concurrent writers store the same
+// value) gives identical shells whatever the visiting order.
+__global__ void __launch_bounds__(256) k_shell_init(int64_t nv, int32_t *shells) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < nv) shells[v] = -1;
+}
+__global__ void __launch_bounds__(256) k_shell_seed(const int32_t *__restrict__ ref, int64_t nref, int64_t nv, int32_t *shells, int32_t *bad) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nref) return;
+    const int32_t r = ref[i];
+    if (r < 0 || (int64_t)r >= nv) { atomicAdd(bad, 1); return; }
+    shells[r] = 0;
+}
+__global__ void __launch_bounds__(256) k_shell_level(const int32_t *__restrict__ off, const int32_t *__restrict__ nbr, int64_t nv, int32_t level,
+                                                     int32_t *shells, int32_t *changed) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nv || shells[v] != level) return;
+    bool any = false;
+    for (int j = off[v]; j < off[v + 1]; j++) {
+        const int32_t u = nbr[j];
+        if (((volatile int32_t*)shells)[u] == -1) { shells[u] = level + 1; any = true; }
+    }
+    if (any) *changed = 1;
+}
+__global__ void __launch_bounds__(256) k_shell_stats(int64_t nv, const int32_t *__restrict__ shells, int32_t *stats) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nv) return;
+    const int32_t s = shells[v];
+    if (s < 0) atomicAdd(stats, 1); else atomicMax(stats + 1, s);
+}
+
+#define SHELL_BATCH 16
+extern "C" size_t ms_mesh_shells_workspace_bytes(int64_t nv) { (void)nv; return 4096; }
+
+extern "C" int ms_mesh_shells(const int32_t *nbr_off, const int32_t *nbr, int64_t nv, const int32_t *ref, int64_t nref,
+                              int32_t *shells, int64_t *n_unreached, int32_t *max_shell, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(nv > 0 && nref > 0 && nbr_off && ref && shells, "ms_mesh_shells: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_mesh_shells_workspace_bytes(nv), "ms_mesh_shells: workspace too small");
+    int32_t *flags = (int32_t*)ws;                 // [0] bad seeds, [1] unreached, [2] max shell, [8..8+SHELL_BATCH) changed per level
+    MS_CUDA(cudaMemsetAsync(flags, 0, 4096, s));
+    const int nb = ms_blocks(nv, 256);
+    MS_K("shell_init", s); k_shell_init<<<nb, 256, 0, s>>>(nv, shells);
+    MS_K("shell_seed", s); k_shell_seed<<<ms_blocks(nref, 256), 256, 0, s>>>(ref, nref, nv, shells, flags);
+    int32_t h[8 + SHELL_BATCH];
+    for (int64_t level = 0; level < nv; level += SHELL_BATCH) {
+        MS_CUDA(cudaMemsetAsync(flags + 8, 0, sizeof(int32_t) * SHELL_BATCH, s));
+        for (int k = 0; k < SHELL_BATCH; k++) {
+            MS_K("shell_level", s); k_shell_level<<<nb, 256, 0, s>>>(nbr_off, nbr, nv, (int32_t)(level + k), shells, flags + 8 + k);
+        }
+        MS_K(NULL, s);
+        MS_LAUNCH_CHECK();
+        MS_CUDA(cudaMemcpyAsync(h, flags, sizeof(h), cudaMemcpyDeviceToHost, s));
+        MS_CUDA(cudaStreamSynchronize(s));
+        MS_REQUIRE(h[0] == 0, "ms_mesh_shells: %d reference vertices are out of range", h[0]);
+        bool done = false;
+        for (int k = 0; k < SHELL_BATCH; k++) done |= h[8 + k] == 0;
+        if (done) break;
+    }
+    MS_K("shell_stats", s); k_shell_stats<<<nb, 256, 0, s>>>(nv, shells, flags + 1);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    MS_CUDA(cudaMemcpyAsync(h, flags, sizeof(int32_t) * 8, cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    if (n_unreached) *n_unreached = h[1];
+    if (max_shell) *max_shell = h[2];
+    return 0;
+}

@@ -367,6 +367,65 @@ class TriMesh(object):
             self.attributes_f64.park('distance_to_surface', d64)
             return _lib.d2h(d32)
 
+    # ---------------------------------------------------------------------- vertex neighbours / shells
+    @_lib.home_stream
+    def neighbors_device(self):
+        """(nbr_off (V+1,) i32, nbr (total,) i32) device tensors: TriMesh::need_neighbors (TriMesh.cpp:197-255) on
+        the mesh's own faces, lists in the reference's order."""
+        _lib.require_cuda()
+        if self.faces is None:
+            raise ValueError(f'{self.tag()} has no faces (call compute_delaunay or pass faces=)')
+        d = self._dev
+        if 'nbr' not in d:
+            L = _lib.lib()
+            dev = self.device
+            V, F = self.vertices.shape[0], self.faces.shape[0]
+            faces = _lib.h2d(np.ascontiguousarray(self.faces, np.uint32).view(np.int32), dev)
+            off = torch.empty(V + 1, dtype=torch.int32, device=dev)
+            nbr = torch.empty(max(1, 6 * F), dtype=torch.int32, device=dev)
+            ws = _lib.workspace(L.ms_mesh_neighbors_workspace_bytes(V, F), dev)
+            total = _lib.C.c_int64(0)
+            _lib.check(L.ms_mesh_neighbors(faces.data_ptr(), F, V, off.data_ptr(), nbr.data_ptr(), _lib.C.byref(total),
+                                           ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_mesh_neighbors')
+            d['nbr'] = (off, nbr[:int(total.value)].clone())
+        return d['nbr']
+
+    def need_neighbors(self):
+        """Linearised neighbour lists as TriMesh::need_neighbors returns them (TriMesh.cpp:241-254): the first V
+        values are the list lengths, followed by the lists."""
+        off, nbr = self.neighbors_device()
+        with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
+            off_h, nbr_h = _lib.d2h(off), _lib.d2h(nbr)
+        return np.concatenate([np.diff(off_h), nbr_h]).astype(np.int32)
+
+    @_lib.home_stream
+    def compute_shells(self, ref_pts):
+        """(V,) int shell index = hop distance to the nearest reference vertex (trimesh.py:364-416)."""
+        key = 'shell'
+        if key in self.attributes:
+            return self.attributes[key]
+        assert isinstance(ref_pts, (list, np.ndarray))
+        assert len(ref_pts) > 0
+        L = _lib.lib()
+        dev = self.device
+        V = self.vertices.shape[0]
+        off, nbr = self.neighbors_device()
+        ref = _lib.h2d(_lib.pinned_copy(np.asarray(ref_pts).reshape(-1), np.int32), dev)
+        shells = torch.empty(V, dtype=torch.int32, device=dev)
+        ws = _lib.workspace(L.ms_mesh_shells_workspace_bytes(V), dev)
+        bad, top = _lib.C.c_int64(0), _lib.C.c_int(0)
+        _lib.check(L.ms_mesh_shells(off.data_ptr(), nbr.data_ptr(), V, ref.data_ptr(), int(ref.numel()), shells.data_ptr(),
+                                    _lib.C.byref(bad), _lib.C.byref(top), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)),
+                   'ms_mesh_shells')
+        out = _lib.d2h(shells)
+        if bad.value > 0:
+            wrong = np.where(out < 0)[0]
+            LOGGER.error(f'Failed to assign shell id for {wrong.shape[0]} vertices: '
+                         f'ids = {wrong}, verts = {self.vertices[wrong]}')
+            assert out.min() == 0, 'Failed to assign shell id for some vertices'
+        self.attributes[key] = out.astype(int)
+        return self.attributes[key]
+
     # ---------------------------------------------------------------------- KDE
     def _kde_box(self, cutoff_sigmas):
         if self.periodic:

@@ -657,3 +657,55 @@ void orc_closest_point(const float *verts, int64_t nv, const uint32_t *faces, in
         if (dist) dist[i] = bf >= 0 ? sqrt(best) : 0.0;
     }
 }
+
+/* ---------------------------------------------------------------- vertex neighbours / shells
+ * orc_need_neighbors follows TriMesh::need_neighbors (memsurfer/src/TriMesh.cpp:197-255): the sequential face
+ * loop appends the two other vertices of corner j of face i to the list of faces[i][j] unless present.
+ * off (nv+1) offsets and lists (cap entries); returns the total length or -1 when cap is too small.       */
+int64_t orc_need_neighbors(const uint32_t *faces, int64_t nf, int64_t nv, int32_t *off, int32_t *lists, int64_t cap) {
+    int32_t *cnt = (int32_t*)calloc((size_t)nv + 1, sizeof(int32_t));
+    int32_t *room = (int32_t*)calloc((size_t)nv + 1, sizeof(int32_t));
+    for (int64_t i = 0; i < 3 * nf; i++) if ((int64_t)faces[i] < nv) room[faces[i]] += 2;
+    int64_t *start = (int64_t*)malloc(((size_t)nv + 1) * sizeof(int64_t));
+    start[0] = 0;
+    for (int64_t v = 0; v < nv; v++) start[v + 1] = start[v] + room[v];
+    int32_t *tmp = (int32_t*)malloc(((size_t)start[nv] + 1) * sizeof(int32_t));
+    for (int64_t i = 0; i < nf; i++)
+        for (int j = 0; j < 3; j++) {
+            const int64_t me = faces[3*i + j];
+            if (me >= nv) continue;
+            int32_t *lst = tmp + start[me];
+            for (int k = 1; k <= 2; k++) {
+                const int32_t u = (int32_t)faces[3*i + (j + k) % 3];
+                int seen = 0;
+                for (int q = 0; q < cnt[me]; q++) if (lst[q] == u) { seen = 1; break; }
+                if (!seen) lst[cnt[me]++] = u;
+            }
+        }
+    int64_t tot = 0;
+    for (int64_t v = 0; v < nv; v++) { off[v] = (int32_t)tot; tot += cnt[v]; }
+    off[nv] = (int32_t)tot;
+    if (tot <= cap)
+        for (int64_t v = 0; v < nv; v++) memcpy(lists + off[v], tmp + start[v], sizeof(int32_t) * (size_t)cnt[v]);
+    free(cnt); free(room); free(start); free(tmp);
+    return tot <= cap ? tot : -1;
+}
+
+/* orc_shells follows the FIFO breadth-first loop of TriMesh.compute_shells (memsurfer/trimesh.py:392-404):
+ * reference vertices start at 0 and enter the queue in the given order; an unvisited neighbour gets
+ * 1 + the shell of the vertex that reaches it first.  Unreached vertices stay at -1.                      */
+void orc_shells(const int32_t *off, const int32_t *lists, int64_t nv, const int32_t *ref, int64_t nref, int32_t *shells) {
+    int32_t *queue = (int32_t*)malloc(((size_t)nv + (size_t)nref + 1) * sizeof(int32_t));
+    int64_t head = 0, tail = 0;
+    for (int64_t v = 0; v < nv; v++) shells[v] = -1;
+    for (int64_t i = 0; i < nref; i++) shells[ref[i]] = 0;
+    for (int64_t i = 0; i < nref; i++) queue[tail++] = ref[i];
+    while (head < tail) {
+        const int32_t cur = queue[head++];
+        for (int32_t j = off[cur]; j < off[cur + 1]; j++) {
+            const int32_t u = lists[j];
+            if (shells[u] == -1) { shells[u] = 1 + shells[cur]; queue[tail++] = u; }
+        }
+    }
+    free(queue);
+}

@@ -51,6 +51,9 @@ def lib():
         L.orc_mst_orient.restype = C.c_int64
         L.orc_mst_orient.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p, _u8p]
         L.orc_closest_point.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, _f32p, C.c_int64, _i32p, _f64p, _f64p]
+        L.orc_need_neighbors.restype = C.c_int64
+        L.orc_need_neighbors.argtypes = [_u32p, C.c_int64, C.c_int64, _i32p, _i32p, C.c_int64]
+        L.orc_shells.argtypes = [_i32p, _i32p, C.c_int64, _i32p, C.c_int64, _i32p]
         _LIB = L
     return _LIB
 
@@ -67,6 +70,9 @@ def ref():
         R.msref_need_pointareas.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _f32p]
         R.msref_kde.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, C.c_int,
                                 _i32p, C.c_int, _f32p]
+        if hasattr(R, "msref_need_neighbors"):
+            R.msref_need_neighbors.restype = C.c_int64
+            R.msref_need_neighbors.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _i32p, C.c_int64]
         _REF = R
     return _REF
 
@@ -221,3 +227,33 @@ def closest_point(verts, faces, queries):
     fid = np.zeros(nq, np.int32); bary = np.zeros((nq, 3), np.float64); dist = np.zeros(nq, np.float64)
     lib().orc_closest_point(verts, verts.shape[0], faces, faces.shape[0], queries, nq, fid, bary, dist)
     return fid, bary, dist
+
+
+def need_neighbors(faces, nv):
+    """(off (nv+1,), lists) int32: TriMesh::need_neighbors restated (TriMesh.cpp:197-255)."""
+    faces = _faces(faces)
+    off = np.zeros(nv + 1, np.int32)
+    lists = np.zeros(max(1, 6 * faces.shape[0]), np.int32)
+    tot = lib().orc_need_neighbors(faces, faces.shape[0], nv, off, lists, lists.shape[0])
+    assert tot >= 0
+    return off, lists[:tot].copy()
+
+
+def shells(off, lists, ref_pts):
+    """(nv,) int32 shell index by the FIFO breadth-first loop of trimesh.py:392-404 (-1: unreached)."""
+    off = np.ascontiguousarray(off, np.int32); lists = np.ascontiguousarray(lists, np.int32)
+    ref = np.ascontiguousarray(ref_pts, np.int32).reshape(-1)
+    nv = off.shape[0] - 1
+    out = np.zeros(nv, np.int32)
+    lib().orc_shells(off, lists, nv, ref, ref.shape[0], out)
+    return out
+
+
+def ref_need_neighbors(verts, faces):
+    """The compiled reference's TriMesh::need_neighbors(): linearised [counts..., lists...] (int32)."""
+    R = ref()
+    verts = _f32(verts); faces = _faces(faces)
+    out = np.zeros(verts.shape[0] + 6 * faces.shape[0] + 1, np.int32)
+    n = R.msref_need_neighbors(verts, verts.shape[0], faces, faces.shape[0], out, out.shape[0])
+    assert n >= 0
+    return out[:n].copy()

@@ -39,6 +39,19 @@ int msref_need_pointareas(const float *verts, int nv, const uint32_t *faces, int
     } catch (const std::exception &e) { std::cerr << e.what(); return 1; }
 }
 
+// TriMesh::need_neighbors() (TriMesh.cpp:197-255): linearised [counts..., lists...]; returns its length
+// (-1: out too small, -2: exception).
+long long msref_need_neighbors(const float *verts, int nv, const uint32_t *faces, int nf, int32_t *out, long long cap) {
+    try {
+        TriMesh m(const_cast<float*>(verts), nv, 3);
+        m.set_faces(const_cast<uint32_t*>(faces), nf, 3);
+        const std::vector<TypeIndexI> r = m.need_neighbors();
+        if ((long long)r.size() > cap) return -1;
+        std::memcpy(out, r.data(), sizeof(int32_t) * r.size());
+        return (long long)r.size();
+    } catch (const std::exception &e) { std::cerr << e.what(); return -2; }
+}
+
 // type: 2 (kde_2d, GaussianKernel2D) or 3 (kde_3d, GaussianKernel3D), as
 // memsurfer/trimesh.py:337-349 picks them.  periodic != 0 ->
 // DistancePeriodicXYSquared(bbox, nbbox) else DistanceSquared().
