@@ -218,6 +218,21 @@ size_t ms_mesh_shells_workspace_bytes(int64_t nv);
 int ms_mesh_shells(const int32_t *nbr_off, const int32_t *nbr, int64_t nv, const int32_t *ref, int64_t nref,
                    int32_t *shells, int64_t *n_unreached, int32_t *max_shell, void *ws, size_t ws_bytes, void *stream);
 
+/* ---------------------------------------------------------------- periodic Delaunay (first slice)
+ * Replaces TriMesh::periodicDelaunay (memsurfer/src/TriMesh_cgal.cpp:160-281; CGAL periodic triangulation,
+ * 9-sheeted covering): the faces with at least one vertex in the original sheet, counter-clockwise, as
+ * dfaces (cap,3) i32 original vertex ids and doffs (cap,3,2) i8 periodic offsets in {-1,0,1} (the
+ * PeriodicVertex triples of :223-233).  Inputs: points_all (m,3) f32 = the n planar points (z ignored) followed
+ * by their ghost images and ghost_src (m) i32 from ms_ghosts; nbr (m,k1) i32 from ms_knn on points_all with
+ * z = 0; box widths; ghost_layer = width of the ghost layer (blayer * the smaller box width).  Faces are
+ * ordered by their smallest vertex id, then counter-clockwise around it.  *n_incomplete = points whose Voronoi
+ * cell cannot be closed inside the ghost layer (then nothing is written); *nfaces = faces found.  dfaces == NULL: count only.  Syncs the stream once.     */
+size_t ms_delaunay_periodic_workspace_bytes(int64_t n);
+int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t n, const int32_t *ghost_src,
+                         const int32_t *nbr, int k1, double box_wx, double box_wy, double ghost_layer,
+                         int32_t *dfaces, int8_t *doffs, int64_t cap, int64_t *nfaces, int64_t *n_incomplete,
+                         void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- diagnostics
  * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).
  * ms_launch_count: kernels launched by the library since the last reset (process-wide).

@@ -1,0 +1,184 @@
+// ms_delaunay.cu -- periodic 2-D Delaunay triangulation on B200 (first slice).
+//
+// Replaces (LLNL/MemSurfer): TriMesh::periodicDelaunay memsurfer/src/TriMesh_cgal.cpp:160-281
+// (CGAL::Periodic_2_Delaunay_triangulation_2, converted to the 9-sheeted covering; the loop at :212-262 keeps
+// every face with at least one vertex in the original sheet as three PeriodicVertex{origVidx, offx, offy}).
+//
+// Design: no incremental insertion, no global data structure.  The periodic images the faces around the
+// original sheet can touch are the ghost points ms_ghosts already makes (0.2 box widths per side), the
+// candidate neighbours of a point are its k nearest ones from ms_knn (sorted by distance).  One thread per
+// ORIGINAL point builds its Voronoi cell by clipping a square with the bisector of each neighbour in turn and
+// stops at the security radius (a neighbour farther than twice the cell's circumradius cannot cut it; the
+// list is sorted, so neither can any later one).  The generators of consecutive cell edges, taken
+// counter-clockwise, are the point's Delaunay neighbours in angular order: every cell vertex is one
+// triangle.  A triangle is written by its smallest point index (ghosts come after the originals, so that is
+// always an original vertex): count pass -> exclusive scan -> fill pass, i.e. a deterministic face order.
+// A point whose list ends before the security radius is reached scans all points for the remaining cutters
+// (rare: very uneven density); a cell that cannot be closed inside the ghost layer is counted in
+// *n_incomplete (the caller falls back to its host producer).
+//
+// Arithmetic: fp64 on float32 inputs, compiled without FMA contraction.  The Delaunay triangulation is
+// unique unless four points are cocircular; inputs that close to degenerate (|incircle| below fp64 rounding)
+// may come out with a different diagonal than an exact-predicate code would choose.
+#include "ms_common.cuh"
+
+#define DL_MAXV 24          // cell vertices kept per thread (a Voronoi cell has ~6)
+
+struct DlCell { double x[DL_MAXV], y[DL_MAXV]; int g[DL_MAXV]; int n; };
+
+// clip the convex cell (counter-clockwise) with the half-plane {v : v.d <= |d|^2/2}; the new edge gets generator q
+__device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q) {
+    const double h = 0.5 * (dx * dx + dy * dy);
+    double s[DL_MAXV];
+    bool any_out = false;
+    for (int i = 0; i < c.n; i++) { s[i] = c.x[i] * dx + c.y[i] * dy - h; any_out |= s[i] > 0.0; }
+    if (!any_out) return true;
+    DlCell o; o.n = 0;
+    for (int i = 0; i < c.n; i++) {
+        const int j = i + 1 == c.n ? 0 : i + 1;
+        const bool in_i = !(s[i] > 0.0), in_j = !(s[j] > 0.0);
+        if (in_i) {
+            if (o.n >= DL_MAXV) return false;
+            o.x[o.n] = c.x[i]; o.y[o.n] = c.y[i];
+            o.g[o.n] = in_j ? c.g[i] : c.g[i];            // edge i survives (whole or up to the cut)
+            o.n++;
+        }
+        if (in_i != in_j) {
+            const double t = s[i] / (s[i] - s[j]);
+            if (o.n >= DL_MAXV) return false;
+            o.x[o.n] = c.x[i] + t * (c.x[j] - c.x[i]); o.y[o.n] = c.y[i] + t * (c.y[j] - c.y[i]);
+            // leaving the half-plane: the next edge runs along the bisector (generator q);
+            // entering it: the rest of edge i continues with its own generator
+            o.g[o.n] = in_i ? q : c.g[i];
+            o.n++;
+        }
+    }
+    c = o;
+    return true;
+}
+
+__device__ __forceinline__ double dl_radius2(const DlCell &c) {
+    double r2 = 0.0;
+    for (int i = 0; i < c.n; i++) { const double v = c.x[i] * c.x[i] + c.y[i] * c.y[i]; r2 = v > r2 ? v : r2; }
+    return r2;
+}
+
+// the Voronoi cell of point p; returns the number of cell vertices (0: cannot be closed).
+// When the sorted neighbour list ends before the security radius is reached (very uneven density) the cell
+// clipped so far is a superset of the true one, so only points within twice its radius can still cut it: the
+// thread scans ALL m points for those (order does not matter: the cell is an intersection of half-planes).
+// reach2 = (width of the ghost layer)^2: a cell whose security disc leaves the ghost layer could be cut by a
+// periodic image that was never made -- reported as not closed.
+__device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int32_t *__restrict__ nbr, int k1, int64_t p, int64_t m,
+                                       double reach2, DlCell &c) {
+    const double px = (double)pts[3*p], py = (double)pts[3*p + 1];
+    const int32_t *row = nbr + p * k1;
+    // start from a square that contains every bisector of the list: half side = distance to the last neighbour
+    double far2 = 0.0;
+    {
+        const int32_t q = row[k1 - 1];
+        const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
+        far2 = dx * dx + dy * dy;
+    }
+    const double R = sqrt(far2);
+    c.n = 4;
+    c.x[0] = -R; c.y[0] = -R; c.x[1] = R; c.y[1] = -R; c.x[2] = R; c.y[2] = R; c.x[3] = -R; c.y[3] = R;
+    c.g[0] = c.g[1] = c.g[2] = c.g[3] = -1;
+    bool complete = false;
+    double r2 = 2.0 * far2;
+    for (int j = 0; j < k1; j++) {
+        const int32_t q = row[j];
+        if ((int64_t)q == p) continue;
+        const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
+        if (dx * dx + dy * dy > 4.0 * r2) { complete = true; break; }
+        if (!dl_clip(c, dx, dy, q)) return 0;
+        r2 = dl_radius2(c);
+    }
+    // list exhausted: every point outside it is at least as far as the last neighbour
+    if (!complete && !(far2 > 4.0 * r2)) {
+        for (int64_t q = 0; q < m; q++) {
+            if (q == p) continue;
+            const double dx = (double)pts[3*q] - px, dy = (double)pts[3*q + 1] - py;
+            const double d2 = dx * dx + dy * dy;
+            if (d2 > 4.0 * r2 || d2 < far2) continue;             // cannot cut / closer than the list's last entry: already used
+            if (!dl_clip(c, dx, dy, (int)q)) return 0;
+            r2 = dl_radius2(c);
+        }
+    }
+    if (4.0 * r2 > reach2) return 0;
+    for (int i = 0; i < c.n; i++) if (c.g[i] < 0) return 0;
+    return c.n;
+}
+
+// FILL == false: cnt[p] = faces owned by p (p is their smallest index), incomplete points counted;
+// FILL == true: faces written to dfaces/doffs from offset start[p]
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_delaunay_star(const float *__restrict__ pts, int64_t n, const int32_t *__restrict__ gsrc,
+                                                       const int32_t *__restrict__ nbr, int k1, int64_t m, double reach2, double wx, double wy,
+                                                       const int32_t *__restrict__ start, int32_t *__restrict__ cnt, int32_t *__restrict__ incomplete,
+                                                       int32_t *__restrict__ dfaces, int8_t *__restrict__ doffs) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    DlCell c;
+    const int nv = dl_cell(pts, nbr, k1, p, m, reach2, c);
+    if (!FILL) {
+        if (nv == 0) { atomicAdd(incomplete, 1); cnt[p] = 0; return; }
+    }
+    int w = FILL ? start[p] : 0, mine = 0;
+    for (int i = 0; i < nv; i++) {
+        // cell vertex i sits between edge i-1 and edge i: triangle (p, g[i-1], g[i]), counter-clockwise
+        const int a = c.g[i == 0 ? nv - 1 : i - 1], b = c.g[i];
+        if (a == b || (int64_t)a < p || (int64_t)b < p) continue;
+        if (FILL) {
+            const int64_t v[3] = { p, a, b };
+            for (int k = 0; k < 3; k++) {
+                const int64_t o = gsrc[v[k]];
+                dfaces[3 * (int64_t)w + k] = (int32_t)o;
+                const double ox = ((double)pts[3*v[k]] - (double)pts[3*o]) / wx, oy = ((double)pts[3*v[k] + 1] - (double)pts[3*o + 1]) / wy;
+                doffs[6 * (int64_t)w + 2*k] = (int8_t)rint(ox);
+                doffs[6 * (int64_t)w + 2*k + 1] = (int8_t)rint(oy);
+            }
+            w++;
+        }
+        mine++;
+    }
+    if (!FILL) cnt[p] = mine;
+}
+
+extern "C" size_t ms_delaunay_periodic_workspace_bytes(int64_t n) {
+    return 2 * ms_align((size_t)(n + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(n) + 1024;
+}
+
+extern "C" int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t n, const int32_t *ghost_src,
+                                    const int32_t *nbr, int k1, double box_wx, double box_wy, double ghost_layer,
+                                    int32_t *dfaces, int8_t *doffs, int64_t cap, int64_t *nfaces, int64_t *n_incomplete,
+                                    void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(points_all && ghost_src && nbr && nfaces && n_incomplete, "ms_delaunay_periodic: bad arguments");
+    MS_REQUIRE(n > 0 && n <= m && k1 >= 4 && k1 <= 32 && m >= k1, "ms_delaunay_periodic: bad sizes (n=%lld, m=%lld, k+1=%d)", (long long)n, (long long)m, k1);
+    MS_REQUIRE(box_wx > 0.0 && box_wy > 0.0, "ms_delaunay_periodic: empty box");
+    MS_REQUIRE(ws_bytes >= ms_delaunay_periodic_workspace_bytes(n), "ms_delaunay_periodic: workspace too small");
+    const double reach2 = ghost_layer * ghost_layer;
+    MsArena A(ws, ws_bytes);
+    int32_t *cnt = A.take<int32_t>(n + 1), *start = A.take<int32_t>(n + 1);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(n));
+    int32_t *flag = (int32_t*)A.take<int32_t>(8);
+    MS_CUDA(cudaMemsetAsync(flag, 0, 8 * sizeof(int32_t), s));
+    MS_K("delaunay_count", s);
+    k_delaunay_star<false><<<ms_blocks(n, 128), 128, 0, s>>>(points_all, n, ghost_src, nbr, k1, m, reach2, box_wx, box_wy, NULL, cnt, flag, NULL, NULL);
+    if (ms_exclusive_scan_i32(cnt, start, n, scan_ws, s)) return 2;
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    int32_t h[2] = { 0, 0 };
+    MS_CUDA(cudaMemcpyAsync(&h[0], start + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaMemcpyAsync(&h[1], flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *nfaces = h[0]; *n_incomplete = h[1];
+    if (h[1] > 0 || dfaces == NULL) return 0;
+    MS_REQUIRE((int64_t)h[0] <= cap, "ms_delaunay_periodic: %d faces do not fit the output (%lld)", h[0], (long long)cap);
+    MS_K("delaunay_fill", s);
+    k_delaunay_star<true><<<ms_blocks(n, 128), 128, 0, s>>>(points_all, n, ghost_src, nbr, k1, m, reach2, box_wx, box_wy, start, NULL, NULL, dfaces, doffs);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,71 @@
+"""Periodic 2-D Delaunay on the GPU (first slice).
+
+Replaces the CGAL call of TriMesh::periodicDelaunay (memsurfer/src/TriMesh_cgal.cpp:160-281) for the mesh
+producer: ghost images (ms_ghosts) -> k nearest neighbours (ms_knn) -> one Voronoi cell per point
+(ms_delaunay_periodic).  Output in the layout of `synth.periodic_delaunay` (the host stand-in): original
+vertex ids + periodic offsets of every face with at least one vertex in the original sheet.
+"""
+import ctypes as C
+import logging
+
+import numpy as np
+import torch
+
+from . import _lib
+
+LOGGER = logging.getLogger(__name__)
+
+
+class IncompleteCells(RuntimeError):
+    """Some Voronoi cells cannot be closed inside the ghost layer (too few points for the box)."""
+
+
+def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0.2):
+    """xy (V,2) planar points, box0/box1 the periodic box.  Returns (dfaces (F,3) int64, doffs (F,3,2) int8);
+    faces are counter-clockwise and ordered by their smallest vertex id."""
+    _lib.require_cuda()
+    L = _lib.lib()
+    dev = torch.device(device)
+    xy = np.asarray(xy)[:, :2]
+    V = xy.shape[0]
+    b0 = np.asarray(box0, np.float32)[:2]
+    b1 = np.asarray(box1, np.float32)[:2]
+    w = (b1 - b0).astype(np.float32)
+    pts = _lib.pinned_empty((V, 3), np.float32)
+    # TriMesh::wrap_vertices (TriMesh_cgal.cpp:191): into [box0, box1)
+    pts[:, :2] = xy
+    for d in range(2):
+        lo = pts[:, d] < b0[d]
+        pts[lo, d] += w[d]
+        hi = pts[:, d] >= b1[d]
+        pts[hi, d] -= w[d]
+    pts[:, 2] = 0.0
+    st = _lib.stream_ptr(dev)
+    pd = _lib.h2d(pts, dev)
+    cap = int(L.ms_pointset_capacity(V, 1))
+    pts_all = torch.empty((cap, 3), dtype=torch.float32, device=dev)
+    gsrc = torch.empty(cap, dtype=torch.int32, device=dev)
+    m_out = C.c_int64(0)
+    ws = _lib.workspace(L.ms_ghosts_workspace_bytes(V), dev)
+    box = _lib.box6(np.array([b0[0], b0[1], -1.0, b1[0], b1[1], 1.0], np.float32))
+    _lib.check(L.ms_ghosts(pd.data_ptr(), V, 1, box, float(blayer), pts_all.data_ptr(), gsrc.data_ptr(),
+                           C.byref(m_out), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
+    m = int(m_out.value)
+    k1 = min(int(knbrs) + 1, 32, m)
+    nbr = torch.empty((m, k1), dtype=torch.int32, device=dev)
+    ws = _lib.workspace(L.ms_knn_workspace_bytes(m, k1), dev)
+    _lib.check(L.ms_knn(pts_all.data_ptr(), m, k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    fcap = 2 * m + 64
+    dfaces = torch.empty((fcap, 3), dtype=torch.int32, device=dev)
+    doffs = torch.empty((fcap, 3, 2), dtype=torch.int8, device=dev)
+    nf, bad = C.c_int64(0), C.c_int64(0)
+    ws = _lib.workspace(L.ms_delaunay_periodic_workspace_bytes(V), dev)
+    _lib.check(L.ms_delaunay_periodic(pts_all.data_ptr(), m, V, gsrc.data_ptr(), nbr.data_ptr(), k1,
+                                      float(w[0]), float(w[1]), float(blayer) * float(min(w)),
+                                      dfaces.data_ptr(), doffs.data_ptr(), fcap,
+                                      C.byref(nf), C.byref(bad), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_periodic')
+    if bad.value > 0:
+        raise IncompleteCells(f'{bad.value} Voronoi cells cannot be closed inside the ghost layer '
+                              f'({blayer} box widths): too few points for this box')
+    F = int(nf.value)
+    return _lib.d2h(dfaces[:F]).astype(np.int64), _lib.d2h(doffs[:F])

@@ -11,6 +11,7 @@ Extras that the reference does not have: `attributes_f64` (fp64 twins of the flo
 `to_device()` (pre-stage inputs in HBM) and `*_device` accessors returning torch tensors.
 """
 import logging
+import os
 
 import numpy as np
 import torch
@@ -143,7 +144,16 @@ class TriMesh(object):
             return
         if self.bbox is None:
             raise ValueError(f'{self.tag()} periodic Delaunay needs a bbox')
-        self._delaunay = synth.periodic_delaunay(self.vertices[:, :2], self.bbox[0], self.bbox[1])
+        self._delaunay = None
+        if torch.cuda.is_available() and os.environ.get('MS_DELAUNAY', 'device') != 'host':
+            from .delaunay import periodic_delaunay_device, IncompleteCells
+            try:
+                with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
+                    self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device)
+            except IncompleteCells as e:
+                LOGGER.warning(f'{self.tag()} {e}: falling back to the host triangulation')
+        if self._delaunay is None:
+            self._delaunay = synth.periodic_delaunay(self.vertices[:, :2], self.bbox[0], self.bbox[1])
         self._retrim()
 
     def copy_triangulation(self, mesh):
