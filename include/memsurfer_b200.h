@@ -233,6 +233,14 @@ int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t n, const in
                          int32_t *dfaces, int8_t *doffs, int64_t cap, int64_t *nfaces, int64_t *n_incomplete,
                          void *ws, size_t ws_bytes, void *stream);
 
+/* First step of TriMesh::trim_periodicDelaunay (memsurfer/src/TriMesh.cpp:493-575): the faces whose three corners
+ * are in the original sheet (all offsets zero) compacted in order into full (nf,3) u32 = mFaces; the others,
+ * also in order, into pfaces (nf,3) i32 / poffs (nf,3,2) i8 for the duplicated-vertex bookkeeping.  All three
+ * outputs sized for nf faces; *nfull = faces in `full` (the rest, nf - *nfull, in pfaces).  Syncs once.    */
+size_t ms_delaunay_split_workspace_bytes(int64_t nf);
+int ms_delaunay_split(const int32_t *dfaces, const int8_t *doffs, int64_t nf, uint32_t *full, int32_t *pfaces, int8_t *poffs,
+                      int64_t *nfull, void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- diagnostics
  * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).
  * ms_launch_count: kernels launched by the library since the last reset (process-wide).

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "ms_delaunay_periodic_workspace_bytes": (_sz, [_i64]),
     "ms_delaunay_periodic": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, _f64, _f64, _f64, _vp, _vp, _i64,
                                        C.POINTER(_i64), C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_delaunay_split_workspace_bytes": (_sz, [_i64]),
+    "ms_delaunay_split": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
     "ms_dfma_probe": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp]),
     "ms_field_summary_workspace_bytes": (_sz, [_i32]),
     "ms_field_summary": (C.c_int, [C.POINTER(_vp), _i32, _i64, _vp, _vp, _sz, _vp]),

@@ -182,3 +182,61 @@ extern "C" int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t 
     MS_LAUNCH_CHECK();
     return 0;
 }
+
+// ------------------------------------------------------------------ split for the trim step
+// TriMesh::trim_periodicDelaunay (TriMesh.cpp:493-575) keeps the faces whose three corners lie in the original
+// sheet as they are (mFaces) and re-indexes the others onto duplicated vertices.  The first group is ~99 % of a
+// large mesh: it is compacted here, in order (flag -> exclusive scan -> scatter); the few faces that cross the
+// box go to the host-side bookkeeping as (vertex ids, offsets), also in order.
+__global__ void __launch_bounds__(256) k_split_flag(const int8_t *__restrict__ doffs, int64_t nf, int32_t *flag) {
+    const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nf) return;
+    int any = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) any |= doffs[6*f + k];
+    flag[f] = any == 0;
+}
+__global__ void __launch_bounds__(256) k_split_scatter(const int32_t *__restrict__ dfaces, const int8_t *__restrict__ doffs, int64_t nf,
+                                                       const int32_t *__restrict__ flag, const int32_t *__restrict__ pos,
+                                                       uint32_t *__restrict__ full, int32_t *__restrict__ pfaces, int8_t *__restrict__ poffs) {
+    const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nf) return;
+    if (flag[f]) {
+        const int64_t o = pos[f];
+#pragma unroll
+        for (int k = 0; k < 3; k++) full[3*o + k] = (uint32_t)dfaces[3*f + k];
+    } else {
+        const int64_t o = f - pos[f];
+#pragma unroll
+        for (int k = 0; k < 3; k++) pfaces[3*o + k] = dfaces[3*f + k];
+#pragma unroll
+        for (int k = 0; k < 6; k++) poffs[6*o + k] = doffs[6*f + k];
+    }
+}
+
+extern "C" size_t ms_delaunay_split_workspace_bytes(int64_t nf) {
+    return 2 * ms_align((size_t)(nf + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(nf) + 1024;
+}
+
+// full (nf,3) u32, pfaces (nf,3) i32, poffs (nf,3,2) i8 sized for the worst case; *nfull = faces written to `full`
+extern "C" int ms_delaunay_split(const int32_t *dfaces, const int8_t *doffs, int64_t nf, uint32_t *full, int32_t *pfaces, int8_t *poffs,
+                                 int64_t *nfull, void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(dfaces && doffs && full && pfaces && poffs && nfull && nf >= 0, "ms_delaunay_split: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_delaunay_split_workspace_bytes(nf), "ms_delaunay_split: workspace too small");
+    *nfull = 0;
+    if (nf == 0) return 0;
+    MsArena A(ws, ws_bytes);
+    int32_t *flag = A.take<int32_t>(nf + 1), *pos = A.take<int32_t>(nf + 1);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(nf));
+    MS_K("split_flag", s); k_split_flag<<<ms_blocks(nf, 256), 256, 0, s>>>(doffs, nf, flag);
+    if (ms_exclusive_scan_i32(flag, pos, nf, scan_ws, s)) return 2;
+    MS_K("split_scatter", s); k_split_scatter<<<ms_blocks(nf, 256), 256, 0, s>>>(dfaces, doffs, nf, flag, pos, full, pfaces, poffs);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    int32_t h = 0;
+    MS_CUDA(cudaMemcpyAsync(&h, pos + nf, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *nfull = h;
+    return 0;
+}

@@ -20,9 +20,11 @@ class IncompleteCells(RuntimeError):
     """Some Voronoi cells cannot be closed inside the ghost layer (too few points for the box)."""
 
 
-def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0.2):
+def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0.2, split=False):
     """xy (V,2) planar points, box0/box1 the periodic box.  Returns (dfaces (F,3) int64, doffs (F,3,2) int8);
-    faces are counter-clockwise and ordered by their smallest vertex id."""
+    faces are counter-clockwise and ordered by their smallest vertex id.  split=True: returns instead
+    (faces (F0,3) uint32 inside the sheet, pfaces (Fp,3) int64, poffs (Fp,3,2) int8 crossing the box) --
+    the first step of the trim, done on the device."""
     _lib.require_cuda()
     L = _lib.lib()
     dev = torch.device(device)
@@ -68,4 +70,14 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
         raise IncompleteCells(f'{bad.value} Voronoi cells cannot be closed inside the ghost layer '
                               f'({blayer} box widths): too few points for this box')
     F = int(nf.value)
-    return _lib.d2h(dfaces[:F]).astype(np.int64), _lib.d2h(doffs[:F])
+    if not split:
+        return _lib.d2h(dfaces[:F]).astype(np.int64), _lib.d2h(doffs[:F])
+    full = torch.empty((F, 3), dtype=torch.int32, device=dev)
+    pfaces = torch.empty((F, 3), dtype=torch.int32, device=dev)
+    poffs = torch.empty((F, 3, 2), dtype=torch.int8, device=dev)
+    nfull = C.c_int64(0)
+    ws = _lib.workspace(L.ms_delaunay_split_workspace_bytes(F), dev)
+    _lib.check(L.ms_delaunay_split(dfaces.data_ptr(), doffs.data_ptr(), F, full.data_ptr(), pfaces.data_ptr(), poffs.data_ptr(),
+                                   C.byref(nfull), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_split')
+    F0 = int(nfull.value)
+    return (_lib.d2h(full[:F0]).view(np.uint32), _lib.d2h(pfaces[:F - F0]).astype(np.int64), _lib.d2h(poffs[:F - F0]))

@@ -102,16 +102,20 @@ def trim_periodic(verts, dfaces, doffs, bbox0, bbox1):
     its own box, TriMesh.hpp:301-304).  Returns dict(faces, periodic_faces, trimmed_faces,
     duplicated_vidxs, duplicated_verts) with the dtypes of trimesh.py:421-436.
     """
+    full = (doffs == 0).all(axis=2).all(axis=1)
+    out = trim_partial(verts, dfaces[~full], doffs[~full], bbox0, bbox1)
+    out["faces"] = dfaces[full].astype(np.uint32)
+    return out
+
+
+def trim_partial(verts, pf, po, bbox0, bbox1):
+    """The part of trim_periodicDelaunay that deals with the faces crossing the box (pf (Fp,3) vertex ids,
+    po (Fp,3,2) offsets, at least one corner outside the original sheet): duplicated vertices in
+    first-appearance order of the face/corner scan and the faces re-indexed onto them."""
     verts = np.asarray(verts, dtype=np.float32)
     V, dim = verts.shape
     boxw = (np.asarray(bbox1, np.float32) - np.asarray(bbox0, np.float32)).astype(np.float32)
-    is_orig = (doffs == 0).all(axis=2)                       # (F,3)
-    n_orig = is_orig.sum(axis=1)
-    full = n_orig == 3
-    faces = dfaces[full].astype(np.uint32)
-    pf = dfaces[~full]
-    po = doffs[~full]
-    pis = is_orig[~full]
+    pis = (po == 0).all(axis=2)                              # (Fp,3) corner in the original sheet
     # unique (orig, offx, offy) in first-appearance order of the face/corner scan
     key = (pf.astype(np.int64) * 9 + (po[..., 0].astype(np.int64) + 1) * 3 + (po[..., 1].astype(np.int64) + 1))
     flat_key = key.reshape(-1)
@@ -125,7 +129,7 @@ def trim_periodic(verts, dfaces, doffs, bbox0, bbox1):
     rank[sorter] = np.arange(uniq.shape[0])
     pos = np.searchsorted(uniq[sorter], dup_keys)
     dup_id = sorter[pos]
-    tf = pf.reshape(-1).copy()
+    tf = pf.reshape(-1).astype(np.int64)
     tf[flat_dup] = V + dup_id
     dup_orig = (uniq // 9).astype(np.int64)
     dup_ox = ((uniq % 9) // 3 - 1).astype(np.float32)
@@ -133,8 +137,7 @@ def trim_periodic(verts, dfaces, doffs, bbox0, bbox1):
     dverts = verts[dup_orig].astype(np.float64)
     dverts[:, 0] += (dup_ox * boxw[0]).astype(np.float32)
     dverts[:, 1] += (dup_oy * boxw[1]).astype(np.float32)
-    return dict(faces=faces,
-                periodic_faces=pf.astype(np.uint32),
+    return dict(periodic_faces=pf.astype(np.uint32),
                 trimmed_faces=tf.reshape(-1, 3).astype(np.uint32),
                 duplicated_vidxs=dup_orig.astype(np.uint32),
                 duplicated_verts=dverts.astype(np.float32))

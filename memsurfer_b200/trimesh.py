@@ -126,11 +126,16 @@ class TriMesh(object):
         self._invalidate()
 
     def _retrim(self):
-        dfaces, doffs = self._delaunay
         if self.bbox is None:
             raise ValueError(f'{self.tag()} periodic mesh needs a bbox (set_bbox) before triangulation')
-        t = synth.trim_periodic(self.vertices, dfaces, doffs,
-                                self.bbox[0, :self.vertices.shape[1]], self.bbox[1, :self.vertices.shape[1]])
+        b0, b1 = self.bbox[0, :self.vertices.shape[1]], self.bbox[1, :self.vertices.shape[1]]
+        if len(self._delaunay) == 3:                  # device producer: already split into inside / crossing faces
+            faces, pf, po = self._delaunay
+            t = synth.trim_partial(self.vertices, pf, po, b0, b1)
+            t['faces'] = faces
+        else:
+            dfaces, doffs = self._delaunay
+            t = synth.trim_periodic(self.vertices, dfaces, doffs, b0, b1)
         self.set_periodic_triangulation(t['faces'], t['periodic_faces'], t['trimmed_faces'],
                                         t['duplicated_vidxs'], t['duplicated_verts'])
 
@@ -149,7 +154,7 @@ class TriMesh(object):
             from .delaunay import periodic_delaunay_device, IncompleteCells
             try:
                 with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
-                    self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device)
+                    self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device, split=True)
             except IncompleteCells as e:
                 LOGGER.warning(f'{self.tag()} {e}: falling back to the host triangulation')
         if self._delaunay is None:

@@ -29,6 +29,11 @@ def test_periodic_delaunay_gpu_vs_host(n, seed):
     assert (go == 0).all(axis=2).any(axis=1).all()              # every face touches the original sheet
     a, b = _canonical(gf, go), _canonical(hf, ho)
     assert a.shape == b.shape and np.array_equal(a, b)
+    # the device-side split of the trim step: same faces, same order
+    ff, pf, po = periodic_delaunay_device(xy, bbox[0], bbox[1], split=True)
+    full = (go == 0).all(axis=(1, 2))
+    assert ff.dtype == np.uint32 and np.array_equal(ff, gf[full].astype(np.uint32))
+    assert np.array_equal(pf, gf[~full]) and np.array_equal(po, go[~full])
     # counter-clockwise in the plane
     w = (bbox[1, :2] - bbox[0, :2]).astype(np.float64)
     P = xy[gf].astype(np.float64) + go.astype(np.float64) * w
