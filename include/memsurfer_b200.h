@@ -226,7 +226,9 @@ int ms_mesh_shells(const int32_t *nbr_off, const int32_t *nbr, int64_t nv, const
  * by their ghost images and ghost_src (m) i32 from ms_ghosts; nbr (m,k1) i32 from ms_knn on points_all with
  * z = 0; box widths; ghost_layer = width of the ghost layer (blayer * the smaller box width).  Faces are
  * ordered by their smallest vertex id, then counter-clockwise around it.  *n_incomplete = points whose Voronoi
- * cell cannot be closed inside the ghost layer (then nothing is written); *nfaces = faces found.  dfaces == NULL: count only.  Syncs the stream once.     */
+ * cell cannot be closed inside the ghost layer, or -1 when the stars do not add up to a triangulation of the
+ * torus (6n corners: exactly cocircular points, e.g. an unperturbed lattice); nothing is written then.
+ * *nfaces = faces found.  dfaces == NULL: count only.  Syncs the stream once.     */
 size_t ms_delaunay_periodic_workspace_bytes(int64_t n);
 int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t n, const int32_t *ghost_src,
                          const int32_t *nbr, int k1, double box_wx, double box_wy, double ghost_layer,

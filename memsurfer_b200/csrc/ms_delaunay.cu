@@ -101,6 +101,11 @@ __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int3
             const double dx = (double)pts[3*q] - px, dy = (double)pts[3*q + 1] - py;
             const double d2 = dx * dx + dy * dy;
             if (d2 > 4.0 * r2 || d2 < far2) continue;             // cannot cut / closer than the list's last entry: already used
+            if (d2 == far2) {                                      // the last entry itself (or a tie with it): clip a point only once
+                bool used = false;
+                for (int j = 0; j < k1; j++) used |= (int64_t)row[j] == q;
+                if (used) continue;
+            }
             if (!dl_clip(c, dx, dy, (int)q)) return 0;
             r2 = dl_radius2(c);
         }
@@ -118,12 +123,16 @@ __global__ void __launch_bounds__(128) k_delaunay_star(const float *__restrict__
                                                        const int32_t *__restrict__ start, int32_t *__restrict__ cnt, int32_t *__restrict__ incomplete,
                                                        int32_t *__restrict__ dfaces, int8_t *__restrict__ doffs) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
     DlCell c;
-    const int nv = dl_cell(pts, nbr, k1, p, m, reach2, c);
+    const int nv = p < n ? dl_cell(pts, nbr, k1, p, m, reach2, c) : 0;
     if (!FILL) {
+        // corners of all stars: 6n on a torus (Euler); less when a cocircular quadruple was left without a diagonal
+        const int tot = __reduce_add_sync(0xffffffffu, nv);
+        if ((threadIdx.x & 31) == 0) atomicAdd(incomplete + 1, tot);
+        if (p >= n) return;
         if (nv == 0) { atomicAdd(incomplete, 1); cnt[p] = 0; return; }
     }
+    if (p >= n) return;
     int w = FILL ? start[p] : 0, mine = 0;
     for (int i = 0; i < nv; i++) {
         // cell vertex i sits between edge i-1 and edge i: triangle (p, g[i-1], g[i]), counter-clockwise
@@ -169,12 +178,16 @@ extern "C" int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t 
     if (ms_exclusive_scan_i32(cnt, start, n, scan_ws, s)) return 2;
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
-    int32_t h[2] = { 0, 0 };
+    int32_t h[3] = { 0, 0, 0 };
     MS_CUDA(cudaMemcpyAsync(&h[0], start + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaMemcpyAsync(&h[1], flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaMemcpyAsync(&h[1], flag, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
     MS_CUDA(cudaStreamSynchronize(s));
     *nfaces = h[0]; *n_incomplete = h[1];
-    if (h[1] > 0 || dfaces == NULL) return 0;
+    if (h[1] == 0 && (int64_t)h[2] != 6 * n) {      // degenerate input (exactly cocircular points): not a triangulation
+        *n_incomplete = -1;
+        return 0;
+    }
+    if (h[1] != 0 || dfaces == NULL) return 0;
     MS_REQUIRE((int64_t)h[0] <= cap, "ms_delaunay_periodic: %d faces do not fit the output (%lld)", h[0], (long long)cap);
     MS_K("delaunay_fill", s);
     k_delaunay_star<true><<<ms_blocks(n, 128), 128, 0, s>>>(points_all, n, ghost_src, nbr, k1, m, reach2, box_wx, box_wy, start, NULL, NULL, dfaces, doffs);

@@ -17,7 +17,8 @@ LOGGER = logging.getLogger(__name__)
 
 
 class IncompleteCells(RuntimeError):
-    """Some Voronoi cells cannot be closed inside the ghost layer (too few points for the box)."""
+    """The cell-by-cell construction does not apply: cells not closed inside the ghost layer (too few points for the
+    box) or exactly cocircular points.  Callers fall back to the host triangulation."""
 
 
 def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0.2, split=False):
@@ -66,6 +67,9 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
                                       float(w[0]), float(w[1]), float(blayer) * float(min(w)),
                                       dfaces.data_ptr(), doffs.data_ptr(), fcap,
                                       C.byref(nf), C.byref(bad), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_periodic')
+    if bad.value < 0:
+        raise IncompleteCells('the Voronoi cells do not add up to a triangulation (exactly cocircular points, '
+                              'e.g. an unperturbed lattice)')
     if bad.value > 0:
         raise IncompleteCells(f'{bad.value} Voronoi cells cannot be closed inside the ghost layer '
                               f'({blayer} box widths): too few points for this box')

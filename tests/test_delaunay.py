@@ -77,3 +77,23 @@ def test_periodic_delaunay_random_points_and_mesh_flow():
     assert np.array_equal(np.sort(np.sort(d.faces, axis=1), axis=0), np.sort(np.sort(h.faces, axis=1), axis=0))
     assert np.array_equal(np.sort(d._duplicated_vidxs), np.sort(h._duplicated_vidxs))
     assert np.allclose(np.sort(d.compute_pointareas()), np.sort(h.compute_pointareas()), rtol=0, atol=0)
+
+
+@pytest.mark.gpu
+def test_periodic_delaunay_degenerate_inputs_are_reported():
+    """An unperturbed lattice (every quadruple cocircular) and a box with far too few points: the device
+    producer reports them and TriMesh.compute_delaunay falls back to the host triangulation."""
+    from memsurfer_b200 import TriMesh
+    from memsurfer_b200.delaunay import periodic_delaunay_device, IncompleteCells
+    g = (np.arange(40) + 0.5) * 2.5
+    X, Y = np.meshgrid(g, g, indexing="xy")
+    xy = np.stack([X.ravel(), Y.ravel()], axis=1).astype(np.float32)
+    b0, b1 = np.array([0.0, 0.0], np.float32), np.array([100.0, 100.0], np.float32)
+    with pytest.raises(IncompleteCells):
+        periodic_delaunay_device(xy, b0, b1)
+    with pytest.raises(IncompleteCells):
+        periodic_delaunay_device(xy[:7] * 0.37 + 3.0, b0, b1)
+    m = TriMesh(xy, periodic=True)
+    m.set_bbox(b0, b1)
+    m.compute_delaunay()                                         # host fallback
+    assert m.faces.shape[0] + m._periodic_faces.shape[0] >= 2 * xy.shape[0]
