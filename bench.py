@@ -304,8 +304,15 @@ def main():
         clocks.start()
     # nvidia-smi takes a few hundred ms to come up (NVML init stalls kernel submission while it does): keep
     # warming up until its first sample has arrived, so that the timed steps run next to a settled sampler
+    # (step_device ends in a collective when world > 1: rank 0 decides, every rank follows)
     t_wait = time.perf_counter()
-    while rank == 0 and clocks.proc is not None and not clocks.lines and time.perf_counter() - t_wait < 3.0:
+    while True:
+        go = torch.tensor([int(rank == 0 and clocks.proc is not None and not clocks.lines
+                               and time.perf_counter() - t_wait < 3.0)], dtype=torch.int32, device=device)
+        if world > 1:
+            dist.broadcast(go, 0)
+        if int(go.item()) == 0:
+            break
         step_device()
         torch.cuda.synchronize()
     total_ms, launches, _ = timed(step_device, args.warmup, args.steps, profile=False)
