@@ -419,6 +419,7 @@ struct KdeTiling {
     int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
     double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
     double gscale;            // factor on the stored group x extents (1 unless the binning is shared between sigmas)
+    double oscale;            // factor on every sum before it is added to the output (the kernel's sfactor, or 1)
 };
 struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; double xlo, xhi; };   // targets [t0,t1), fine columns [ca,cb], x extent
 
@@ -664,7 +665,7 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
 #pragma unroll
             for (int r = 0; r < 2; r++) {
                 const int j = a0 + lane + r * 32;
-                if (j < a1) atomicAdd(out + __ldg(tperm + j), acc[r]);
+                if (j < a1) atomicAdd(out + __ldg(tperm + j), acc[r] * T.oscale);
             }
         }
     }
@@ -964,7 +965,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             }
             KdeGrid gs = g;
             gs.ncx = (int)ncxd; gs.ncy = T.nty * B; gs.m = 0;
-            T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut; T.gscale = 1.0;
+            T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut; T.gscale = 1.0; T.oscale = 1.0;
             T.mf = (int)ceil(rcut / T.cys);
             const int mxmax = (int)ceil(rcut / T.cxs);
             gs.b0x = (double)box6[0] * scale; gs.b0y = (double)box6[1] * scale;
@@ -1125,9 +1126,10 @@ extern "C" int ms_kde_labels(const float *verts, int64_t nv, const int32_t *labe
     int rc = kde_front(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
     if (c.cells) {
+        if (c.tiles) c.tl.oscale = (double)c.sfactor;
         rc = kde_launch_cells(c, nv, raw, s);
         if (rc) return rc;
-        MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(raw, nv * nlabels, (double)c.sfactor);
+        if (!c.tiles) { MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(raw, nv * nlabels, (double)c.sfactor); }
         MS_K(NULL, s);
         MS_LAUNCH_CHECK();
         return 0;
@@ -1267,9 +1269,10 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
         // group x extents were measured on the reference staging: they scale with the coordinates
         c.tl.gscale = scales[i] / c.scale;
         double *out = raw + (size_t)i * per;
+        if (c.tiles) c.tl.oscale = (double)sfac[i];                // the groups kernel applies the kernel's sfactor itself
         const int rc = kde_launch_cells(c, nv, out, s, false);
         if (rc) return rc;
-        MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(out, nv * nlabels, (double)sfac[i]);
+        if (!c.tiles) { MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(out, nv * nlabels, (double)sfac[i]); }
     }
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
