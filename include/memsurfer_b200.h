@@ -243,6 +243,22 @@ size_t ms_delaunay_split_workspace_bytes(int64_t nf);
 int ms_delaunay_split(const int32_t *dfaces, const int8_t *doffs, int64_t nf, uint32_t *full, int32_t *pfaces, int8_t *poffs,
                       int64_t *nfull, void *ws, size_t ws_bytes, void *stream);
 
+/* ---------------------------------------------------------------- geodesic (type 1) KDE
+ * ms_geodesics replaces TriMesh::compute_geodesics_fw (memsurfer/src/TriMesh_kde.cpp:196-332): all-pairs
+ * shortest paths along the edges of `faces` (for a periodic mesh: its faces followed by its periodic faces,
+ * :487-489), edge length = sqrt of the periodic-xy 3-D squared distance (DistanceKernels.hpp:120-135).
+ * D: pitch x pitch fp64 on the device, pitch = ms_geodesic_pitch(nv) (rows/columns >= nv are padding);
+ * unreachable pairs hold DBL_MAX (FLT_MAX in the reference).  nv <= 46 000 (17 GB).
+ * ms_kde_geodesic replaces kde_2m (:394-437) + the normalisation of TriMesh::kde (:504-524) with
+ * GaussianKernel2D(sigma): all vertices (nids == 0): sum_i k(D[i][j]^2); selected ids: sum_i k(D[ids[i]][j])
+ * -- the reference does not square the distance in that branch (:432) and neither does this.           */
+int64_t ms_geodesic_pitch(int64_t nv);
+int ms_geodesics(const float *verts, int64_t nv, const uint32_t *faces, int64_t nf, int periodic, const float *box6,
+                 double *D, void *stream);
+size_t ms_kde_geodesic_workspace_bytes(int64_t nv);
+int ms_kde_geodesic(const double *D, int64_t nv, const int32_t *ids, int64_t nids, float sigma, int get_counts,
+                    double *density_f64, float *density_f32, void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- diagnostics
  * No reference counterpart (the reference times whole steps with utils.Timer, utils.py:209-241).
  * ms_launch_count: kernels launched by the library since the last reset (process-wide).

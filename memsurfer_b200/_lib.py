@@ -61,6 +61,10 @@ _SIGNATURES = {
                                        C.POINTER(_i64), C.POINTER(_i64), _vp, _sz, _vp]),
     "ms_delaunay_split_workspace_bytes": (_sz, [_i64]),
     "ms_delaunay_split": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_geodesic_pitch": (_i64, [_i64]),
+    "ms_geodesics": (C.c_int, [_vp, _i64, _vp, _i64, _i32, C.POINTER(_f32), _vp, _vp]),
+    "ms_kde_geodesic_workspace_bytes": (_sz, [_i64]),
+    "ms_kde_geodesic": (C.c_int, [_vp, _i64, _vp, _i64, _f32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "ms_dfma_probe": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp]),
     "ms_field_summary_workspace_bytes": (_sz, [_i32]),
     "ms_field_summary": (C.c_int, [C.POINTER(_vp), _i32, _i64, _vp, _vp, _sz, _vp]),

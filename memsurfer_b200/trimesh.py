@@ -478,6 +478,46 @@ class TriMesh(object):
         return ws
 
     @_lib.home_stream
+    def geodesics_device(self):
+        """(pitch, pitch) f64 device tensor of graph distances along the mesh edges (TriMesh::compute_geodesics_fw,
+        TriMesh_kde.cpp:196-332; periodic meshes: faces ++ periodic faces, :487-489).  Computed once per mesh."""
+        _lib.require_cuda()
+        d = self._dev
+        if 'geodesics' not in d:
+            L = _lib.lib()
+            dev = self.device
+            if self.faces is None:
+                raise ValueError(f'{self.tag()} has no faces (call compute_delaunay or pass faces=)')
+            faces = np.ascontiguousarray(self.faces, np.uint32)
+            if self.periodic and self._periodic_faces is not None and self._periodic_faces.shape[0] > 0:
+                faces = np.concatenate([faces, np.ascontiguousarray(self._periodic_faces, np.uint32)])
+            V = self.vertices.shape[0]
+            pitch = int(L.ms_geodesic_pitch(V))
+            D = torch.empty((pitch, pitch), dtype=torch.float64, device=dev)
+            fd = _lib.h2d(faces.view(np.int32), dev)
+            _lib.check(L.ms_geodesics(self._kde_verts_device().data_ptr(), V, fd.data_ptr(), faces.shape[0],
+                                      int(bool(self.periodic)), self._kde_box(0.0), D.data_ptr(), _lib.stream_ptr(dev)),
+                       'ms_geodesics')
+            d['geodesics'] = D
+        return d['geodesics']
+
+    @_lib.home_stream
+    def density_geodesic_device(self, sigma, get_nlipids, pidxs_dev=None):
+        """Type-1 density on device-resident inputs; returns (f64 tensor, f32 tensor)."""
+        L = _lib.lib()
+        dev = self.device
+        D = self.geodesics_device()
+        nv = self.vertices.shape[0]
+        nids = 0 if pidxs_dev is None else int(pidxs_dev.numel())
+        o64 = torch.empty(nv, dtype=torch.float64, device=dev)
+        o32 = torch.empty(nv, dtype=torch.float32, device=dev)
+        ws = self._workspace('kde_geo_ws', L.ms_kde_geodesic_workspace_bytes(nv))
+        _lib.check(L.ms_kde_geodesic(D.data_ptr(), nv, _lib.ptr(pidxs_dev) if nids else None, nids, float(sigma),
+                                     int(bool(get_nlipids)), o64.data_ptr(), o32.data_ptr(), ws.data_ptr(), ws.numel(),
+                                     _lib.stream_ptr(dev)), 'ms_kde_geodesic')
+        return o64, o32
+
+    @_lib.home_stream
     def density_device(self, type, sigma, get_nlipids, pidxs_dev=None, cutoff_sigmas=0.0):
         """Run ms_kde on device-resident inputs; returns (f64 tensor, f32 tensor)."""
         _lib.require_cuda()
@@ -599,19 +639,20 @@ class TriMesh(object):
     def compute_density(self, type, sigma, name, get_nlipids, pidxs, cutoff_sigmas=0.0, lazy=False):
         """(V,) float32 density (trimesh.py:324-361 -> TriMesh::kde TriMesh_kde.cpp:443-532).
 
-        type 2: 2-D Gaussian on (x,y); type 3: 3-D Gaussian.  type 1 (geodesic, Floyd-Warshall
-        O(V^3), TriMesh_kde.cpp:196-332) is not part of the GPU path.
+        type 2: 2-D Gaussian on (x,y); type 3: 3-D Gaussian; type 1: Gaussian of the graph distance along the
+        mesh edges (Floyd-Warshall, TriMesh_kde.cpp:196-332 -- O(V^3) work and a V x V matrix: small meshes).
         """
         if type < 1 or type > 3:
             raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
-        if type == 1:
-            raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
         if name not in self._fields:                  # TriMesh_kde.cpp:455-460: name-keyed cache
             pidxs = np.asarray(pidxs)
             pd = None
             if pidxs.shape[0] > 0:
                 pd = _lib.h2d(_lib.pinned_copy(pidxs, np.int32), self.device)
-            o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
+            if type == 1:                             # geodesic: Floyd-Warshall distances + kde_2m
+                o64, o32 = self.density_geodesic_device(sigma, get_nlipids, pd)
+            else:
+                o64, o32 = self.density_device(type, sigma, get_nlipids, pd, cutoff_sigmas)
             self._fields.park(name, o32)
             self.attributes_f64.park(name, o64)
             if LOGGER.isEnabledFor(logging.INFO):

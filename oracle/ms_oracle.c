@@ -22,6 +22,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
+#include <float.h>
 
 #ifndef M_PI
 #define M_PI 3.14159265358979323846
@@ -708,4 +709,55 @@ void orc_shells(const int32_t *off, const int32_t *lists, int64_t nv, const int3
         }
     }
     free(queue);
+}
+
+/* ---------------------------------------------------------------- geodesic KDE, type 1
+ * orc_geodesics follows TriMesh::compute_geodesics_fw (memsurfer/src/TriMesh_kde.cpp:196-332, the non-PDIST
+ * branch): D = "infinity" (FLT_MAX there, DBL_MAX here), 0 on the diagonal; every face edge gets the square
+ * root of the (periodic-xy, 3-D) squared distance of its end points; then Floyd-Warshall in k, i, j order.
+ * The symmetric write of :287 is redundant (both candidates are the same two addends).  fp64 throughout.   */
+void orc_geodesics(const float *verts, int64_t nv, const uint32_t *faces, int64_t nf, int periodic, const float *bbox, double *D) {
+    double boxw[2] = { 0.0, 0.0 };
+    if (periodic) { boxw[0] = (double)(float)(bbox[3] - bbox[0]); boxw[1] = (double)(float)(bbox[4] - bbox[1]); }
+    for (int64_t i = 0; i < nv * nv; i++) D[i] = DBL_MAX;
+    for (int64_t i = 0; i < nv; i++) D[i * nv + i] = 0.0;
+    for (int64_t f = 0; f < nf; f++)
+        for (int d = 0; d < 3; d++) {
+            const int64_t a = faces[3*f + d], b = faces[3*f + (d == 2 ? 0 : d + 1)];
+            const double val = sqrt(orc_dist2(verts + 3*a, verts + 3*b, 3, periodic, boxw));
+            D[a * nv + b] = val; D[b * nv + a] = val;
+        }
+    for (int64_t k = 0; k < nv; k++) {
+        const double *Dk = D + k * nv;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < nv; i++) {
+            double *Di = D + i * nv;
+            const double dik = Di[k];
+            if (i == k || dik == DBL_MAX) continue;
+            for (int64_t j = 0; j < nv; j++) if (dik + Dk[j] < Di[j]) Di[j] = dik + Dk[j];
+        }
+    }
+}
+
+/* orc_kde_geodesic follows kde_2m (TriMesh_kde.cpp:394-437) + the normalisation of TriMesh::kde (:504-524):
+ * all vertices: density[j] = sum_i k(D[i][j]^2); selected ids: density[j] = sum_i k(D[ids[i]][j]) -- the
+ * reference does NOT square the distance in that branch (:432), reproduced as is.  k = GaussianKernel2D.   */
+void orc_kde_geodesic(const double *D, int64_t nv, const int32_t *ids, int64_t nids, float sigma, int get_counts, double *density) {
+    float ef, sf; orc_kde_constants(sigma, 2, &ef, &sf);
+    const double efactor = ef, sfactor = sf;
+#pragma omp parallel for schedule(static)
+    for (int64_t j = 0; j < nv; j++) {
+        double acc = 0.0;
+        if (nids == 0) for (int64_t i = 0; i < nv; i++) { const double d = D[i * nv + j]; acc += sfactor * exp(d * d * efactor); }
+        else for (int64_t i = 0; i < nids; i++) acc += sfactor * exp(D[(int64_t)ids[i] * nv + j] * efactor);
+        density[j] = acc;
+    }
+    const double norm1 = 1.0 / (double)nv;
+    for (int64_t j = 0; j < nv; j++) density[j] *= norm1;
+    if (get_counts) {
+        double dsm = 0.0;
+        for (int64_t j = 0; j < nv; j++) dsm += density[j];
+        const double norm2 = (double)(nids > 0 ? nids : nv) / dsm;
+        for (int64_t j = 0; j < nv; j++) density[j] *= norm2;
+    }
 }

@@ -51,6 +51,8 @@ def lib():
         L.orc_mst_orient.restype = C.c_int64
         L.orc_mst_orient.argtypes = [_f32p, C.c_int64, _i32p, C.c_int, _f64p, _u8p]
         L.orc_closest_point.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, _f32p, C.c_int64, _i32p, _f64p, _f64p]
+        L.orc_geodesics.argtypes = [_f32p, C.c_int64, _u32p, C.c_int64, C.c_int, _f32p, _f64p]
+        L.orc_kde_geodesic.argtypes = [_f64p, C.c_int64, _i32p, C.c_int64, C.c_float, C.c_int, _f64p]
         L.orc_need_neighbors.restype = C.c_int64
         L.orc_need_neighbors.argtypes = [_u32p, C.c_int64, C.c_int64, _i32p, _i32p, C.c_int64]
         L.orc_shells.argtypes = [_i32p, _i32p, C.c_int64, _i32p, C.c_int64, _i32p]
@@ -70,6 +72,9 @@ def ref():
         R.msref_need_pointareas.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _f32p]
         R.msref_kde.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, C.c_int,
                                 _i32p, C.c_int, _f32p]
+        if hasattr(R, "msref_kde_geodesic"):
+            R.msref_kde_geodesic.argtypes = [_f32p, C.c_int, _u32p, C.c_int, C.c_int, C.c_float, C.c_int, _f32p, C.c_int,
+                                             _i32p, C.c_int, _f32p]
         if hasattr(R, "msref_need_neighbors"):
             R.msref_need_neighbors.restype = C.c_int64
             R.msref_need_neighbors.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _i32p, C.c_int64]
@@ -257,3 +262,35 @@ def ref_need_neighbors(verts, faces):
     n = R.msref_need_neighbors(verts, verts.shape[0], faces, faces.shape[0], out, out.shape[0])
     assert n >= 0
     return out[:n].copy()
+
+
+def geodesics(verts, faces, bbox=None):
+    """(V,V) f64 graph distances along the mesh edges (TriMesh::compute_geodesics_fw restated)."""
+    verts = _f32(verts); faces = _faces(faces)
+    nv = verts.shape[0]
+    D = np.zeros((nv, nv), np.float64)
+    bb = np.zeros(6, np.float32) if bbox is None else np.ascontiguousarray(bbox, np.float32).reshape(-1)
+    lib().orc_geodesics(verts, nv, faces, faces.shape[0], int(bbox is not None), bb, D)
+    return D
+
+
+def kde_geodesic(verts, faces, ids, sigma, get_counts, bbox=None):
+    """(V,) f64 type-1 density (kde_2m + normalisation) on the geodesic distances of `faces`."""
+    D = geodesics(verts, faces, bbox)
+    ids = np.ascontiguousarray(ids, np.int32).reshape(-1)
+    out = np.zeros(D.shape[0], np.float64)
+    lib().orc_kde_geodesic(D, D.shape[0], ids, ids.shape[0], float(sigma), int(bool(get_counts)), out)
+    return out
+
+
+def ref_kde_geodesic(verts, faces, ids, sigma, get_counts, bbox=None):
+    """The compiled reference's TriMesh::kde(type 1) (float32)."""
+    R = ref()
+    verts = _f32(verts); faces = _faces(faces)
+    ids = np.ascontiguousarray(ids, np.int32).reshape(-1)
+    bb = np.zeros(6, np.float32) if bbox is None else np.ascontiguousarray(bbox, np.float32).reshape(-1)
+    out = np.zeros(verts.shape[0], np.float32)
+    rc = R.msref_kde_geodesic(verts, verts.shape[0], faces, faces.shape[0], int(bool(get_counts)), float(sigma),
+                              int(bbox is not None), bb, 6, ids, ids.shape[0], out)
+    assert rc == 0
+    return out

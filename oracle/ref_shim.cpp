@@ -52,6 +52,25 @@ long long msref_need_neighbors(const float *verts, int nv, const uint32_t *faces
     } catch (const std::exception &e) { std::cerr << e.what(); return -2; }
 }
 
+// type 1 (geodesic, TriMesh_kde.cpp:484-498): Floyd-Warshall over the edges of `faces` (the caller passes the
+// mesh's faces followed by its periodic faces, which is what the periodic branch concatenates), then kde_2m.
+int msref_kde_geodesic(const float *verts, int nv, const uint32_t *faces, int nf, int get_counts, float sigma,
+                       int periodic, const float *bbox, int nbbox, const int32_t *ids, int nids, float *out_density) {
+    try {
+        TriMesh m(const_cast<float*>(verts), nv, 3);
+        m.set_faces(const_cast<uint32_t*>(faces), nf, 3);
+        std::vector<TypeIndexI> vids(ids, ids + nids);
+        const std::vector<TypeFunction> *r = 0;
+        GaussianKernel2D gk(sigma);
+        if (periodic) { DistancePeriodicXYSquared dk(const_cast<float*>(bbox), nbbox);
+                        r = &m.kde("d", 1, get_counts != 0, gk, dk, vids, false); }
+        else          { DistanceSquared dk;
+                        r = &m.kde("d", 1, get_counts != 0, gk, dk, vids, false); }
+        std::memcpy(out_density, r->data(), sizeof(float)*r->size());
+        return 0;
+    } catch (const std::exception &e) { std::cerr << e.what(); return 1; }
+}
+
 // type: 2 (kde_2d, GaussianKernel2D) or 3 (kde_3d, GaussianKernel3D), as
 // memsurfer/trimesh.py:337-349 picks them.  periodic != 0 ->
 // DistancePeriodicXYSquared(bbox, nbbox) else DistanceSquared().
