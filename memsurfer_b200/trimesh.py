@@ -171,6 +171,21 @@ class TriMesh(object):
         self._delaunay = mesh._delaunay
         self._retrim()
 
+    def copy_densities(self, mesh):
+        """Adopt the cached density fields of another mesh (trimesh.py:125-126 -> TriMesh::set_fields,
+        TriMesh.hpp:277-284: every field whose name STARTS with 'density')."""
+        for name in list(mesh._fields.keys()):
+            if name.find('density') == 0:
+                self._fields[name] = mesh._fields[name]
+                if name in mesh.attributes_f64:
+                    self.attributes_f64[name] = mesh.attributes_f64[name]
+
+    def parameterization_bbox(self):
+        """(min, max) of the parameterised vertices (trimesh.py:131-134)."""
+        bb0 = self._parameterized_verts.min(axis=0)
+        bb1 = self._parameterized_verts.max(axis=0)
+        return bb0, bb1
+
     # ---------------------------------------------------------------------- device staging
     def _concat_host(self):
         """verts ++ dup verts (z = 0 for planar meshes) and faces ++ trimmed faces, page-locked."""
