@@ -347,3 +347,25 @@ class Membrane(object):
         m.compute_approx_surface()
         m.compute_membrane_surface()
         return m
+
+    # ---------------------------------------------------------------------- export (host)
+    def write_all(self, outprefix, params={}):
+        """VTP files of the points and of every surface, as membrane.py:319-345 writes them
+        (`_points`, `_surface_poisson` when a Poisson surface exists, `_planar`, `_membrane_exact`,
+        `_membrane_smooth`); written by memsurfer_b200.export, VTK is not required."""
+        params = dict(params)
+        pparams = {'normals': self.pnormals}
+        if self.labels is not None and self.labels.shape != (0, 0):
+            pparams['labels'] = self.labels
+        if 'shells' in self.memb_smooth.attributes:
+            pparams['shells'] = self.memb_smooth.attributes['shells']
+        TriMesh(self.points, device=self.device).write_vtp(outprefix + '_points.vtp', pparams)
+        if self.surf_poisson is not None:
+            self.surf_poisson.write_vtp(outprefix + '_surface_poisson.vtp')
+        for key in list(self.attributes.keys()):
+            params[key] = self.attributes[key]
+        if 'labels' in pparams.keys():
+            params['labels'] = pparams['labels']
+        self.memb_planar.write_vtp(outprefix + '_planar.vtp', params)
+        self.memb_exact.write_vtp(outprefix + '_membrane_exact.vtp', params)
+        self.memb_smooth.write_vtp(outprefix + '_membrane_smooth.vtp', params)

@@ -676,3 +676,27 @@ class TriMesh(object):
         if lazy:
             return dict.__getitem__(self._fields, name)
         return self._fields[name]
+
+    # ---------------------------------------------------------------------- export (host)
+    def as_vtkpolydata(self, include_attributes=KNOWN_ATTRIBUTES, additional_attributes={}):
+        """Content of the vtkPolyData of trimesh.py:441-567 as an `export.PolyData` (VTK is not required):
+        vertices + duplicated vertices, faces + trimmed faces minus the ones spanning the box, attributes
+        sorted into point / cell / field data by their length."""
+        from . import export
+        return export.as_polydata(self, include_attributes, additional_attributes)
+
+    def as_pddataframe(self, include_attributes=KNOWN_ATTRIBUTES, additional_attributes={}):
+        """pandas.DataFrame of positions and per-vertex attributes (trimesh.py:570-617)."""
+        from . import export
+        return export.as_pddataframe(self, include_attributes, additional_attributes)
+
+    def write_vtp(self, filename, additional_attrs={}, ascii=False):
+        """VTK XML PolyData file (trimesh.py:620-628), written without VTK."""
+        from . import export
+        export.write_vtp(self.as_vtkpolydata(TriMesh.KNOWN_ATTRIBUTES, additional_attrs), filename, ascii=ascii)
+        LOGGER.info(f'{self.tag()} Written to ({filename})')
+
+    def write_pd(self, filename, additional_attrs={}):
+        """CSV through pandas (trimesh.py:630-635)."""
+        self.as_pddataframe(TriMesh.KNOWN_ATTRIBUTES, additional_attrs).to_csv(filename)
+        LOGGER.info(f'{self.tag()} Written to ({filename})')

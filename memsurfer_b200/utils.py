@@ -114,3 +114,55 @@ def test_overlapping_points(points, dthreshold=0.00001, fix=False, device='cuda:
 
 
 test_overlapping_points.__test__ = False      # not a pytest test
+
+
+# ------------------------------------------------------------------------------ small host helpers of memsurfer/utils.py
+def get_order_param(a2, a3, b2, b3, z=np.array([0, 0, 1])):
+    """Lipid tail order parameter P2 = (3 cos^2(theta) - 1) / 2 per tail, theta between the bond a2-a3 (b2-b3)
+    and the normal z (one normal or one per lipid); (n, 2) array, one column per tail (memsurfer/utils.py:163-204).
+    O(n) host arithmetic on caller-supplied bead positions; not part of the timed path."""
+    z = np.asarray(z)
+    if z.ndim == 1:
+        z = z[None, :]
+    if not (a2.shape == a3.shape == b2.shape == b3.shape):
+        raise AssertionError("Tail's shapes must match")
+    if not (z.shape == (1, 3) or z.shape == a2.shape):
+        raise AssertionError('Should provide a single normal or a normal per lipid')
+    zn = np.linalg.norm(z, axis=1)
+
+    def _p2(bond):
+        c = (bond * z).sum(axis=1) / (np.linalg.norm(bond, axis=1) * zn)
+        return 0.5 * (3.0 * c * c - 1)
+
+    return np.stack((_p2(a2 - a3), _p2(b2 - b3)), axis=1)
+
+
+class Timer(object):
+    """Wall-clock timer with the reference's text form (memsurfer/utils.py:209-241)."""
+
+    def __init__(self):
+        self.stime = self.etime = None
+        self.start()
+
+    def start(self):
+        import timeit
+        self.stime = timeit.default_timer()
+
+    def end(self, print_time=False):
+        import timeit
+        self.etime = timeit.default_timer()
+        if print_time:
+            print(self)
+
+    def __str__(self):
+        t = self.etime - self.stime
+        if t < 1e-6:
+            return '%.3f micro-sec.' % (t * 1e6)
+        if t < 1e-3:
+            return '%.3f milli-sec.' % (t * 1e3)
+        if t < 60.0:
+            return '%.3f sec.' % t
+        m = int(t / 60.0)
+        return '%d min. %.3f sec.' % (m, t - 60 * m)
+
+    __repr__ = __str__
