@@ -176,3 +176,21 @@ def test_membrane_write_all(tmp_path):
     for suffix in ('_planar', '_membrane_exact'):
         q = export.read_vtp(prefix + suffix + '.vtp')
         assert np.array_equal(q['Polys'], s['Polys'])
+
+
+@pytest.mark.gpu
+def test_example_ex_simple_runs_and_writes(tmp_path):
+    """examples/ex_simple.py (the reference's ex_simple flow, configs[0]) end to end with string labels."""
+    import importlib.util, os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location('ex_simple', os.path.join(root, 'examples', 'ex_simple.py'))
+    ex = importlib.util.module_from_spec(spec); spec.loader.exec_module(ex)
+    m, prefix = ex.main(['--out', str(tmp_path / 'noisy')])
+    s = export.read_vtp(prefix + '_membrane_smooth.vtp')
+    V = m.npoints
+    assert s['FieldData']['frame'][0] == 0 and s['FieldData']['time'][0] == 0.0
+    assert np.array_equal(s['PointData']['labels'][:V], m.labels)
+    d = s['PointData']['density_type2_all_k0.2'][:V]
+    assert abs(float(d.sum()) - V) < 1e-2 * V                          # get_nlipdis: the density sums to the lipid count
+    assert 'density_type2_1_k0.2' in s['PointData']
+    assert np.array_equal(s['PointData']['gaus_curv'][:V], m.memb_smooth.attributes['gaus_curv'])
