@@ -166,3 +166,32 @@ class Timer(object):
         return '%d min. %.3f sec.' % (m, t - 60 * m)
 
     __repr__ = __str__
+
+
+LFORMAT = '%(asctime)s [%(levelname)s] %(name)s:%(funcName)s - %(message)s'
+_LEVELS = {1: logging.DEBUG, 2: logging.INFO, 3: logging.WARNING, 4: logging.ERROR, 5: logging.CRITICAL}
+
+
+def create_logger(loglevel, logstdout, logfile, logpath, logfname):
+    """Configure the root logger like memsurfer/utils.py:35-78: `loglevel` 1 (debug) ... 5 (critical), a stream
+    handler when `logstdout == 1`, a file handler on `<logpath>/<logfname>[.log]` when `logfile == 1`."""
+    import os
+    if loglevel not in _LEVELS:
+        raise AssertionError(f'loglevel must be 1..5, got {loglevel}')
+    level = _LEVELS[loglevel]
+    root = logging.getLogger()
+    root.setLevel(level)
+    handlers = []
+    if logstdout == 1:
+        handlers.append(logging.StreamHandler())
+    if logfile == 1:
+        logpath = os.path.expanduser(logpath)
+        os.makedirs(logpath, exist_ok=True)
+        if logfname[-4:] != '.log':
+            logfname += '.log'
+        handlers.append(logging.FileHandler(os.path.join(logpath, logfname)))
+    for h in handlers:
+        h.setLevel(level)
+        h.setFormatter(logging.Formatter(LFORMAT))
+        root.addHandler(h)
+    return LOGGER

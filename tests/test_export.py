@@ -194,3 +194,24 @@ def test_example_ex_simple_runs_and_writes(tmp_path):
     assert abs(float(d.sum()) - V) < 1e-2 * V                          # get_nlipdis: the density sums to the lipid count
     assert 'density_type2_1_k0.2' in s['PointData']
     assert np.array_equal(s['PointData']['gaus_curv'][:V], m.memb_smooth.attributes['gaus_curv'])
+
+
+def test_create_logger(tmp_path):
+    from memsurfer_b200.utils import create_logger
+    root = logging.getLogger()
+    before, level = list(root.handlers), root.level
+    try:
+        lg = create_logger(2, 0, 1, str(tmp_path / 'logs'), 'run')
+        lg.info('hello from the test')
+        lg.debug('not shown at level 2')
+        for h in root.handlers:
+            h.flush()
+        text = open(tmp_path / 'logs' / 'run.log').read()
+        assert 'hello from the test' in text and '[INFO]' in text and 'not shown' not in text
+        with pytest.raises(AssertionError):
+            create_logger(0, 1, 0, '', '')
+    finally:
+        for h in list(root.handlers):
+            if h not in before:
+                root.removeHandler(h); h.close()
+        root.setLevel(level)
