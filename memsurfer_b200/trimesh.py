@@ -361,10 +361,13 @@ class TriMesh(object):
             raise ValueError(f'{self.tag()} expects one parameterized vertex per vertex')
         self._parameterized_verts = pverts
 
-    def parameterize(self):
-        """Planar parameterisation of the vertices.  The CGAL producer (trimesh.py:129-156) is a host step that
-        is not available here: unless one was injected, the xy projection (TriMesh::parameterize_xy) is used."""
-        if self._parameterized_verts is None:
+    def parameterize(self, xy=False):
+        """Planar parameterisation of the vertices (trimesh.py:136-156; `xy=True` is TriMesh::parameterize_xy, the
+        projection on the xy plane).  The CGAL producer behind `xy=False` is a host step that is not available
+        here: unless a parameterisation was injected (`set_parameterization`), the xy projection is used too."""
+        if xy or self._parameterized_verts is None:
+            if not xy:
+                LOGGER.info(f'{self.tag()} no injected parameterization: using the xy projection')
             self._parameterized_verts = np.ascontiguousarray(self.vertices[:, :2], np.float32)
         return self._parameterized_verts
 
