@@ -236,3 +236,26 @@ def test_example_ex_3lipid_runs_and_writes(tmp_path):
             for n in names:
                 assert np.array_equal(s['PointData'][n][:V], m.attributes[n]), n
             assert set(np.unique(s['PointData']['labels'])) == {'DPPC', 'DIPC', 'CHOL'}
+
+
+def test_write_vtp_edge_cases(tmp_path):
+    """A mesh with an empty face list, a 2-D non-periodic mesh, and a point cloud (Verts only)."""
+    pts, _, _ = synth.make_leaflet(64, seed=9)
+    empty = TriMesh(pts, faces=np.zeros((0, 3), np.uint32))
+    fn = str(tmp_path / 'empty.vtp')
+    empty.write_vtp(fn)
+    back = export.read_vtp(fn)
+    assert back['Points'].shape == (pts.shape[0], 3) and back['Polys'].shape == (0, 3)
+    flat = TriMesh(pts[:, :2])
+    flat.compute_delaunay()
+    fn = str(tmp_path / 'flat.vtp')
+    flat.write_vtp(fn, {'id': np.arange(pts.shape[0], dtype=np.int64)}, ascii=True)
+    back = export.read_vtp(fn)
+    assert np.array_equal(back['Points'][:, :2], pts[:, :2]) and not back['Points'][:, 2].any()
+    assert np.array_equal(back['Polys'], flat.faces) and np.array_equal(back['PointData']['id'], np.arange(pts.shape[0]))
+    cloud = TriMesh(pts)
+    fn = str(tmp_path / 'cloud.vtp')
+    cloud.write_vtp(fn, {'normals': np.tile([0., 0., 1.], (pts.shape[0], 1))})
+    back = export.read_vtp(fn)
+    assert back['Polys'] is None or back['Polys'].shape[0] == 0
+    assert np.array_equal(back['Verts'], np.arange(pts.shape[0])) and back['PointData']['normals'].shape == (pts.shape[0], 3)
