@@ -51,6 +51,10 @@ size_t ms_knn_workspace_bytes(int64_t m, int k1);
 int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
            void *ws, size_t ws_bytes, void *stream);
 
+/* Diagnostic (no reference counterpart): queries of the last ms_knn call on workspace `ws` that met an exact
+ * distance tie and were redone in (distance, index) order.  Syncs the stream.                    */
+int ms_knn_tie_queries(const void *ws, size_t ws_bytes, int64_t m, int k1, int64_t *tie_queries, void *stream);
+
 /* Stage 3: PCA normal of every point from its k1 neighbours (unit eigenvector of the smallest
  * eigenvalue of the 3x3 covariance; sign arbitrary).  normals (m,3) f64.                      */
 int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,

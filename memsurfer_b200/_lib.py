@@ -4,6 +4,7 @@ This is the only door between the Python host code and the sm_100a kernels.  The
 fallback: if the shared library is missing or a call fails, an exception is raised.
 PyTorch is used purely as the device-buffer / stream provider.
 """
+import collections.abc
 import ctypes as C
 import os
 
@@ -28,6 +29,7 @@ _SIGNATURES = {
     "ms_ghosts": (C.c_int, [_vp, _i64, _i32, C.POINTER(_f32), _f32, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
     "ms_knn_workspace_bytes": (_sz, [_i64, _i32]),
     "ms_knn": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _sz, _vp]),
+    "ms_knn_tie_queries": (C.c_int, [_vp, _sz, _i64, _i32, C.POINTER(_i64), _vp]),
     "ms_pca_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
     "ms_orient_workspace_bytes": (_sz, [_i64, _i32]),
     "ms_orient_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
@@ -240,52 +242,62 @@ def d2h_async(t):
     return Pending(host, ev)
 
 
-class LazyResults(dict):
-    """dict of numpy results whose values may still be downloading: `park(name, tensor)` starts the
-    device->host copy and returns at once; any read access (`d[name]`, get, values, items, pop) waits
-    for that copy and hands out the numpy array.  Lets the host queue a whole frame without stalling
-    on every field, while callers still see plain numpy arrays."""
+class LazyResults(collections.abc.MutableMapping):
+    """Mapping of numpy results whose values may still be downloading: `park(name, tensor)` starts the
+    device->host copy and returns at once; ANY read access (`d[name]`, get, values, items, pop, iteration by
+    `dict(d)` / `{**d}` / `other.update(d)`, pickling) waits for that copy and hands out the numpy array.  Lets the
+    host queue a whole frame without stalling on every field, while callers only ever see plain numpy arrays.
+    Not a `dict` subclass on purpose: CPython's fast paths for real dicts would bypass the resolution."""
+
+    def __init__(self, *a, **k):
+        self._d = dict(*a, **k)
 
     def park(self, name, tensor):
         p = d2h_async(tensor)
-        dict.__setitem__(self, name, p)
+        self._d[name] = p
         return p
 
     def adopt(self, name, pending):
-        dict.__setitem__(self, name, pending)
+        self._d[name] = pending
 
-    def _res(self, k, v):
-        if isinstance(v, Pending):
-            v = v.result()
-            dict.__setitem__(self, k, v)
-        return v
+    def raw(self, k):
+        """The stored value as it is: a Pending download or the finished array."""
+        return self._d[k]
 
     def __getitem__(self, k):
-        return self._res(k, dict.__getitem__(self, k))
+        v = self._d[k]
+        if isinstance(v, Pending):
+            v = self._d[k] = v.result()
+        return v
 
-    def get(self, k, default=None):
-        return self[k] if k in self else default
+    def __setitem__(self, k, v):
+        self._d[k] = v
 
-    def pop(self, k, *a):
-        if k in self:
-            v = self[k]
-            dict.__delitem__(self, k)
-            return v
-        return dict.pop(self, k, *a)
+    def __delitem__(self, k):
+        del self._d[k]
 
-    def values(self):
-        return [self[k] for k in list(self.keys())]
+    def __iter__(self):
+        return iter(list(self._d))
 
-    def items(self):
-        return [(k, self[k]) for k in list(self.keys())]
+    def __len__(self):
+        return len(self._d)
+
+    def __contains__(self, k):
+        return k in self._d
+
+    def __repr__(self):
+        return f'LazyResults({list(self._d)})'
 
     def resolve(self):
-        for k in list(self.keys()):
+        for k in list(self._d):
             self[k]
         return self
 
     def copy(self):
         return dict(self.items())
+
+    def __reduce__(self):
+        return (dict, (self.copy(),))
 
 
 def box6(a):

@@ -11,7 +11,13 @@ void ms_set_error(const char *fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
 }
 
-extern "C" int ms_version(void) { return 101; }
+int ms_sm_count(void) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 148;
+    return sms;
+}
+
+extern "C" int ms_version(void) { return 200; }
 extern "C" const char *ms_last_error(void) { return g_err; }
 
 // ------------------------------------------------------------------ launch accounting / profiling
@@ -157,8 +163,8 @@ __global__ void __launch_bounds__(256) k_dfma_probe(double *out, int64_t iters) 
     out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
 }
 
-#define PROBE_BLOCKS (MS_SM_COUNT * 8)
 extern "C" int ms_dfma_probe(double *out, int64_t iters, double *flop, void *stream) {
+    const int PROBE_BLOCKS = ms_sm_count() * 8;
     MS_REQUIRE(out != NULL && iters > 0, "ms_dfma_probe: out must hold %d doubles", PROBE_BLOCKS * 256);
     MS_K("dfma_probe", (cudaStream_t)stream); k_dfma_probe<<<PROBE_BLOCKS, 256, 0, (cudaStream_t)stream>>>(out, iters);
     MS_K(NULL, (cudaStream_t)stream);
@@ -172,7 +178,7 @@ extern "C" int ms_dfma_probe(double *out, int64_t iters, double *flop, void *str
 // (sum, sum|x|, min, max) of an fp64 field in a fixed reduction order (deterministic): the record
 // that ranks exchange when trajectory frames are sharded across GPUs.
 #define SUM_T 256
-#define SUM_BLOCKS (MS_SM_COUNT * 4)
+#define SUM_BLOCKS 592            // partial sums per field: fixed, so that the reduction order (and the result) does not depend on the device
 struct Sum4 { double s, a, mn, mx; };
 __device__ __forceinline__ Sum4 sum4_merge(const Sum4 &x, const Sum4 &y) {
     Sum4 r; r.s = x.s + y.s; r.a = x.a + y.a; r.mn = fmin(x.mn, y.mn); r.mx = fmax(x.mx, y.mx); return r;

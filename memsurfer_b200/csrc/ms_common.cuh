@@ -6,9 +6,11 @@
 #include <stdio.h>
 #include "../../include/memsurfer_b200.h"
 
-#define MS_SM_COUNT 148
 
 void ms_set_error(const char *fmt, ...);
+
+// SMs of the CURRENT device (queried on every call; 148 on a B200): grids of the grid-stride kernels are sized from it
+int ms_sm_count(void);
 
 // Launch accounting / optional per-kernel event timing (ms_profile_* in the C ABI).  Call
 // ms_prof_mark("kernel name", stream) right before every kernel launch and

@@ -6,31 +6,28 @@
 // DistanceSquared / DistancePeriodicXYSquared DistanceKernels.hpp:75-136 (fused in).
 //
 // Design (not a contraction -> no tensor cores; bound = the fp64 pipe, 64 DFMA/clk/SM):
-//   * coordinates are pre-scaled by sqrt(-efactor*log2(e)*256) once per field, so the pair term is
-//     2^-(r/256) with r = dx^2+dy^2[+dz^2]: no per-pair multiply by efactor; sfactor is applied
+//   * coordinates are pre-scaled by sqrt(-efactor*log2(e)*512) once per field, so the pair term is
+//     2^-(r/512) with r = dx^2+dy^2[+dz^2]: no per-pair multiply by efactor; sfactor is applied
 //     once per target;
-//   * software exp2 in 7 fp64 instructions: round-to-nearest split of r with the 1.5*2^52 trick
-//     (n = round(r), f = r - n in [-1/2,1/2]), 2^-(f/256) by a degree-3 near-minimax polynomial
-//     (3.5e-14 relative), 2^-((n&255)/256) from a 256-entry shared-memory table, 2^-(n>>8) by an
-//     integer subtraction from the table value's exponent field, all folded into the accumulating
-//     DFMA;
+//   * software exp2 in 6 fp64 instructions: round-to-nearest split of r with the 1.5*2^52 trick
+//     (n = round(r), f = r - n in [-1/2,1/2]), 2^-(f/512) by a degree-2 near-minimax polynomial
+//     (1.3e-11 relative; every term is positive, so this also bounds the sum), 2^-((n&511)/512) from a
+//     512-entry shared-memory table, 2^-(n>>9) by an integer subtraction from the table value's exponent
+//     field, all folded into the accumulating DFMA;
 //   * two pair-sum kernels share that core:
-//       k_kde_pairs  all V x n_ids pairs (the reference's sum).  Single-wrap minimum image as
-//                    min(|dx|, boxw-|dx|): the reference adds boxw to the smaller coordinate when
-//                    |dx| >= boxw/2, and (|dx|-boxw)^2 == min(|dx|, boxw-|dx|)^2;
-//       k_kde_cells  pairs inside a window of (2m+1)^2 cells of a uniform xy cell list (covers every
-//                    pair closer than cutoff_sigmas*sigma; dropped relative tail mass
-//                    <= exp(-cutoff_sigmas^2/2)); the periodic image shift is applied once per staged
-//                    row segment, so there is no per-pair wrap arithmetic at all;
+//       k_kde_pairs   all V x n_ids pairs (the reference's sum).  Single-wrap minimum image as
+//                     min(|dx|, boxw-|dx|): the reference adds boxw to the smaller coordinate when
+//                     |dx| >= boxw/2, and (|dx|-boxw)^2 == min(|dx|, boxw-|dx|)^2;
+//       k_kde_groups  pairs inside the window box(32 targets) (+) disc(cutoff_sigmas*sigma) of a fine cell list
+//                     (dropped relative tail mass <= exp(-cutoff_sigmas^2/2)); the periodic image shift is
+//                     applied once per staged batch, so there is no per-pair wrap arithmetic at all;
 //   * source points are staged into shared memory by the TMA engine (cp.async.bulk + mbarrier,
-//     double buffered); every thread keeps R targets in registers so one broadcast LDS.128 feeds R
-//     independent DFMA chains.
+//     double buffered); one broadcast LDS.128 per source feeds the lanes' DFMA chains.
 #include "ms_common.cuh"
 #include <math.h>
 #include <stdlib.h>
 
 #define KDE_STAGE_BYTES 16384    // all-pairs: bytes per shared-memory stage (1024 double2 / 512 double4)
-#define CELL_STAGE_BYTES 8192    // cell list: bytes per stage
 #define KDE_MAGIC 6755399441055744.0   // 1.5 * 2^52
 #define KDE_TAB_LOG 9
 #define KDE_TAB (1 << KDE_TAB_LOG)
@@ -178,7 +175,7 @@ struct KdeGrid {
     double b0x, b0y;          // scaled origin of the grid
     double inv_cx, inv_cy;    // 1 / scaled cell size per axis
     double wx, wy;            // scaled extent (the period when periodic): ncx*cell_x, ncy*cell_y
-    int ncx, ncy, m, periodic;
+    int ncx, ncy, periodic;
 };
 
 template <int DIM>
@@ -282,109 +279,7 @@ __global__ void __launch_bounds__(256) k_kde_cell_gather(const typename SrcT<DIM
     sorted[i] = p;
 }
 
-// Enumerates the source window of one target cell as contiguous ranges of the cell-sorted source
-// array (one per row of cells, two when the row wraps around the period), cut into stage-sized
-// chunks, each with the periodic image shift to ADD TO THE TARGET coordinates.
-struct KdeWindow {
-    int dy, piece, np, row, o, e;
-    int xa[2], xb[2];
-    double shx[2], shy;
-};
-__device__ __forceinline__ void kde_window_init(KdeWindow &w, const KdeGrid &g) { w.dy = -g.m - 1; w.piece = 0; w.np = 0; w.o = w.e = 0; }
-__device__ __forceinline__ bool kde_window_next(KdeWindow &w, const KdeGrid &g, int cx, int cy, const int32_t *__restrict__ sstart,
-                                                int cap, int &off, int &cnt, double &shx, double &shy) {
-    for (;;) {
-        if (w.o < w.e) { off = w.o; cnt = min(cap, w.e - w.o); w.o += cnt; shx = w.shx[w.piece]; shy = w.shy; return true; }
-        w.piece++;
-        if (w.piece >= w.np) {
-            w.dy++; w.piece = 0; w.np = 0;
-            if (w.dy > g.m) return false;
-            int row = cy + w.dy; w.shy = 0.0;
-            if (row < 0) { if (!g.periodic) { w.piece = 0; continue; } row += g.ncy; w.shy = g.wy; }
-            else if (row >= g.ncy) { if (!g.periodic) { w.piece = 0; continue; } row -= g.ncy; w.shy = -g.wy; }
-            w.row = row; w.np = 1;
-            w.xa[0] = cx - g.m; w.xb[0] = cx + g.m; w.shx[0] = 0.0;
-            if (!g.periodic) { w.xa[0] = max(w.xa[0], 0); w.xb[0] = min(w.xb[0], g.ncx - 1); }
-            else if (w.xa[0] < 0) { w.xa[1] = 0; w.xb[1] = w.xb[0]; w.shx[1] = 0.0; w.xa[0] += g.ncx; w.xb[0] = g.ncx - 1; w.shx[0] = g.wx; w.np = 2; }
-            else if (w.xb[0] >= g.ncx) { w.xa[1] = 0; w.xb[1] = w.xb[0] - g.ncx; w.shx[1] = -g.wx; w.xb[0] = g.ncx - 1; w.np = 2; }
-        }
-        w.o = __ldg(sstart + w.row * g.ncx + w.xa[w.piece]);
-        w.e = __ldg(sstart + w.row * g.ncx + w.xb[w.piece] + 1);
-    }
-}
-
-// One CTA per target cell; 64 threads x 2 register targets (chunks of 128 targets).  The sources are
-// sorted by (label, cell): sstart holds nlabels*ncell+1 offsets and out[l*out_stride + vertex] receives
-// the sum over the sources of label l (nlabels == 1: a plain source set).
-#define CELL_T 64
-template <int DIM, bool CLAMP>
-__global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::type *__restrict__ tgt, const int32_t *__restrict__ tstart,
-                                                      const int32_t *__restrict__ tperm,
-                                                      const typename SrcT<DIM>::type *__restrict__ src, const int32_t *__restrict__ sstart_all,
-                                                      int nlabels, int64_t out_stride, KdeGrid g, double *__restrict__ out_all) {
-    typedef typename SrcT<DIM>::type S;
-    constexpr int CAP = CELL_STAGE_BYTES / (int)sizeof(S);
-    __shared__ __align__(128) S buf[2][CAP];
-    __shared__ __align__(16) double tab[KDE_TAB];
-    __shared__ __align__(8) uint64_t bar[2];
-    const int tid = threadIdx.x;
-    const int cell = blockIdx.x, cx = cell % g.ncx, cy = cell / g.ncx;
-    const int t0 = __ldg(tstart + cell), t1 = __ldg(tstart + cell + 1);
-    if (t0 == t1) return;
-    for (int i = tid; i < KDE_TAB; i += CELL_T) tab[i] = c_exp2_tab[i];
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-    __syncthreads();
-    uint32_t phase = 0u;                  // bit s = parity to wait for on stage s
-    int stage = 0;
-    const int ncell = g.ncx * g.ncy;
-    for (int c0 = t0; c0 < t1; c0 += CELL_T * 2)
-    for (int lab = 0; lab < nlabels; lab++) {
-        const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
-        double *__restrict__ out = out_all + (size_t)lab * out_stride;
-        double tx[2], ty[2], tz[2], acc[2];
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const int j = c0 + tid + r * CELL_T;
-            S q; q.x = 0.0; q.y = 0.0; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
-            if (j < t1) q = tgt[j];
-            tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0; acc[r] = 0.0;
-        }
-        const bool two = c0 + (tid & ~31) + CELL_T < t1;     // warp-uniform: any target in this warp's second slot?
-        KdeWindow w; kde_window_init(w, g);
-        int off, cnt, noff, ncnt; double shx, shy, nshx, nshy;
-        bool have = kde_window_next(w, g, cx, cy, sstart, CAP, off, cnt, shx, shy);
-        if (have && tid == 0) {
-            mbar_expect_tx(&bar[stage], (uint32_t)cnt * (uint32_t)sizeof(S));
-            bulk_g2s(buf[stage], src + off, (uint32_t)cnt * (uint32_t)sizeof(S), &bar[stage]);
-        }
-        while (have) {
-            const bool more = kde_window_next(w, g, cx, cy, sstart, CAP, noff, ncnt, nshx, nshy);
-            if (more && tid == 0) {          // the other stage was released by the __syncthreads of the previous round
-                mbar_expect_tx(&bar[stage ^ 1], (uint32_t)ncnt * (uint32_t)sizeof(S));
-                bulk_g2s(buf[stage ^ 1], src + noff, (uint32_t)ncnt * (uint32_t)sizeof(S), &bar[stage ^ 1]);
-            }
-            mbar_wait(&bar[stage], (phase >> stage) & 1u); phase ^= 1u << stage;
-            if (two) {
-                const double sx[2] = { tx[0] + shx, tx[1] + shx }, sy[2] = { ty[0] + shy, ty[1] + shy };
-                kde_accumulate<DIM, false, CLAMP, 2>(buf[stage], cnt, tab, sx, sy, tz, acc, 0.0, 0.0);
-            } else {
-                const double sx[1] = { tx[0] + shx }, sy[1] = { ty[0] + shy }, tz1[1] = { tz[0] };
-                double a1[1] = { acc[0] };
-                kde_accumulate<DIM, false, CLAMP, 1>(buf[stage], cnt, tab, sx, sy, tz1, a1, 0.0, 0.0);
-                acc[0] = a1[0];
-            }
-            __syncthreads();
-            stage ^= 1; have = more; off = noff; cnt = ncnt; shx = nshx; shy = nshy;
-        }
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const int j = c0 + tid + r * CELL_T;
-            if (j < t1) out[__ldg(tperm + j)] = acc[r];
-        }
-    }
-}
-
-// ------------------------------------------------------------------ target groups (cut-off variant, current)
+// ------------------------------------------------------------------ target groups (cut-off variant)
 // Sources live in FINE cells (pitch ~rcut/8) sorted by (label, cell).  Targets are sorted by
 // (strip of B fine rows, fine column, index) and cut into GROUPS of 64 consecutive targets of one
 // strip: every lane slot is used (the fixed cell/tile versions wasted 12-25 % of the lanes).  The
@@ -397,7 +292,7 @@ __global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::
 // target: with exactly two addends per output (the two halves) onto zero the result is independent of
 // their order, i.e. bit-reproducible.  The 256-entry exp2 table is replicated 16x (entry e of copy k
 // at double index e*16+k, lane l reads copy l&15): every lane of a half-warp owns its bank pair, so
-// the table LDS.64 costs 2 wavefronts instead of ~6.5 (ncu: 4.1-way conflicts in k_kde_cells).
+// the table LDS.64 costs 2 wavefronts instead of ~6.5 (ncu on the first cell-list kernel: 4.1-way conflicts).
 #ifndef GR_NW
 #define GR_NW 12                 // warps per CTA
 #endif
@@ -415,7 +310,7 @@ __global__ void __launch_bounds__(CELL_T) k_kde_cells(const typename SrcT<DIM>::
 #define GR_TAB_BYTES (KDE_TAB * 16 * 8)
 
 struct KdeTiling {
-    KdeGrid gs;               // fine source grid; gs.m is unused
+    KdeGrid gs;               // fine source grid
     int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
     double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
     double gscale;            // factor on the stored group x extents (1 unless the binning is shared between sigmas)
@@ -743,11 +638,6 @@ __global__ void __launch_bounds__(RED_T) k_kde_emit(const double *__restrict__ d
     if (o32) o32[j] = (float)d;
 }
 
-__global__ void __launch_bounds__(256) k_kde_scale(double *x, int64_t n, double f) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) x[i] *= f;
-}
-
 // stable partition by label (all-pairs, label-fused): flag -> exclusive scan -> scatter, one label at a time
 __global__ void __launch_bounds__(256) k_kde_label_flag(const int32_t *__restrict__ labels, int64_t n, int l, int32_t *flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -785,13 +675,13 @@ struct KdePlan { int64_t ns; int threads, R, nsplit; int64_t blocks_x; };
 static KdePlan kde_plan(int64_t nv, int64_t ns) {
     KdePlan p;
     p.ns = ns;
-    const bool big = nv >= (int64_t)MS_SM_COUNT * 128 * 4 * 2;
+    const bool big = nv >= (int64_t)ms_sm_count() * 128 * 4 * 2;
     p.threads = big ? 128 : 64; p.R = big ? 4 : 1;
     p.blocks_x = (nv + p.threads * p.R - 1) / (p.threads * p.R);
     // enough CTAs for >= 16 full waves (6 resident CTAs per SM) so that the last, partial wave costs
     // a few percent at most; the splits are combined by k_kde_combine
     const int64_t ntiles = (p.ns + 511) / 512;                      // smallest tile (3-D)
-    int64_t want = ((int64_t)MS_SM_COUNT * 6 * 16 + p.blocks_x - 1) / (p.blocks_x > 0 ? p.blocks_x : 1);
+    int64_t want = ((int64_t)ms_sm_count() * 6 * 16 + p.blocks_x - 1) / (p.blocks_x > 0 ? p.blocks_x : 1);
     if (want < 1) want = 1; if (want > 64) want = 64; if (want > ntiles) want = ntiles > 0 ? ntiles : 1;
     p.nsplit = (int)want;
     return p;
@@ -856,31 +746,6 @@ static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, const int32_t 
     return 0;
 }
 
-// pairs the cell-list kernel evaluates: sum over cells of (#targets) x (#sources of every label in the window)
-__global__ void __launch_bounds__(128) k_kde_cells_count(const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart_all,
-                                                         int nlabels, KdeGrid g, unsigned long long *total) {
-    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ncell = g.ncx * g.ncy;
-    unsigned long long mine = 0ull;
-    if (cell < ncell) {
-        const int nt = tstart[cell + 1] - tstart[cell];
-        if (nt > 0) {
-            unsigned long long nsrc = 0ull;
-            for (int l = 0; l < nlabels; l++) {
-                KdeWindow w; kde_window_init(w, g);
-                int off, cnt; double shx, shy;
-                while (kde_window_next(w, g, cell % g.ncx, cell / g.ncx, sstart_all + (size_t)l * ncell, 1 << 30, off, cnt, shx, shy))
-                    nsrc += (unsigned long long)cnt;
-            }
-            mine = nsrc * (unsigned long long)nt;
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(total, mine);
-}
-
-static bool kde_env_flag(const char *name) { const char *v = getenv(name); return v && v[0] && v[0] != '0'; }
-
 struct KdeCtx {
     KdePlan p; bool cells, tiles; KdeGrid g; KdeTiling tl; int type, periodic, nsplit, nlabels; bool clamp;
     double wx, wy; float sfactor;
@@ -943,10 +808,10 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
 
     // ---- cell-list plan: needs the grid extent (box6); periodic grids must tile the period
     bool cells = false; KdeGrid g; double rwin = 0.0;
-    g.ncx = g.ncy = 1; g.m = 0; g.periodic = periodic ? 1 : 0; g.b0x = g.b0y = 0.0; g.inv_cx = g.inv_cy = 0.0; g.wx = wx; g.wy = wy;
+    g.ncx = g.ncy = 1; g.periodic = periodic ? 1 : 0; g.b0x = g.b0y = 0.0; g.inv_cx = g.inv_cy = 0.0; g.wx = wx; g.wy = wy;
     c.tiles = false;
-    if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0 && !kde_env_flag("MS_KDE_NO_TILES")) {
-        // ---- group plan: strips of B fine rows, ~square groups of 64 targets, fine cells of ~rcut/8
+    if (cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
+        // ---- group plan: strips of B fine rows, ~square groups of GR_TGT targets, fine cells of ~rcut/16
         const double rcut = cutoff_sigmas * sg * scale;
         const double tside = sqrt((double)GR_TGT * wx * wy / (double)nv);
         const double ntyd = floor(wy / tside);
@@ -954,9 +819,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             KdeTiling T;
             T.nty = (int)ntyd;
             const double tsy = wy / T.nty;
-            const char *fe = getenv("MS_KDE_FINE");
-            const double fine = fe && atof(fe) > 0.0 ? atof(fe) : 16.0;
-            int B = (int)lround(tsy / (rcut / fine));
+            int B = (int)lround(tsy / (rcut / 16.0));
             B = B < 1 ? 1 : (B > 6 ? 6 : B);
             double ncxd = 0.0;
             for (;; B--) {                                 // fine cells ~square; their count must fit the workspace
@@ -964,7 +827,7 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
                 if (B == 1 || ncxd * ntyd * B <= (double)kde_max_cells(nv)) break;
             }
             KdeGrid gs = g;
-            gs.ncx = (int)ncxd; gs.ncy = T.nty * B; gs.m = 0;
+            gs.ncx = (int)ncxd; gs.ncy = T.nty * B;
             T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut; T.gscale = 1.0; T.oscale = 1.0;
             T.mf = (int)ceil(rcut / T.cys);
             const int mxmax = (int)ceil(rcut / T.cxs);
@@ -981,26 +844,6 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
                 rwin = ex * ex + ey * ey;
                 // the exponent shift n>>8 is not clamped in the kernel unless CLAMP: keep it far below 1021
                 if (rwin >= (double)KDE_TAB * 1000.0) rwin = 2.0 * KDE_RMAX;
-            }
-        }
-    }
-    if (!cells && cutoff_sigmas > 0.0 && box6 != NULL && wx > 0.0 && wy > 0.0) {
-        const double rcut = cutoff_sigmas * sg * scale;                      // scaled cut-off radius
-        double cs = rcut / 4.0;
-        const double cmin = sqrt(56.0 * wx * wy / (double)nv);               // ~56 targets per cell
-        if (cs < cmin) cs = cmin;
-        const double nxd = floor(wx / cs), nyd = floor(wy / cs);
-        if (nxd >= 1.0 && nyd >= 1.0 && nxd * nyd <= (double)kde_max_cells(nv)) {
-            const int ncx = (int)nxd, ncy = (int)nyd;
-            const double cxs = wx / ncx, cys = wy / ncy;
-            const int m = (int)ceil(rcut / (cxs < cys ? cxs : cys));
-            const bool fits = periodic ? (2 * m + 1 <= ncx && 2 * m + 1 <= ncy) : (ncx * ncy >= 4);
-            if (fits) {
-                cells = true;
-                g.b0x = (double)box6[0] * scale; g.b0y = (double)box6[1] * scale;
-                g.inv_cx = 1.0 / cxs; g.inv_cy = 1.0 / cys;
-                g.ncx = ncx; g.ncy = ncy; g.m = m;
-                rwin = (m + 1) * (m + 1) * (cxs * cxs + cys * cys);           // largest in-window xy distance^2
             }
         }
     }
@@ -1059,18 +902,14 @@ template <int DIM, bool CLAMP>
 static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s, bool build = true) {
     typedef typename SrcT<DIM>::type S;
     const size_t smem = GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S) + (size_t)GR_NW * 2 * sizeof(uint64_t);
-    static int per_sm = 0;                     // resident CTAs per SM of this instantiation (set once; same on every B200)
-    if (per_sm == 0) {
-        MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        // two 2-D CTAs (64 KB table + 48 KB of stages each) only fit with the whole 228 KB carved out as shared memory
-        MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        int n = 0;
-        MS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_kde_groups<DIM, CLAMP>, GR_THREADS, smem));
-        MS_REQUIRE(n >= 1, "ms_kde: k_kde_groups does not fit an SM (%zu bytes of shared memory)", smem);
-        per_sm = n;
-    }
-    int sms = MS_SM_COUNT, dev = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // set on every call (idempotent, a few microseconds): no per-process cache, any device, any thread.
+    // Two 2-D CTAs (64 KB table + 48 KB of stages each) only fit with the whole 228 KB carved out as shared memory.
+    MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    int per_sm = 0;
+    MS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_kde_groups<DIM, CLAMP>, GR_THREADS, smem));
+    MS_REQUIRE(per_sm >= 1, "ms_kde: k_kde_groups does not fit an SM (%zu bytes of shared memory)", smem);
+    const int sms = ms_sm_count();
     const KdeTiling &T = c.tl;
     if (build && kde_build_groups(c, s)) return 2;
     unsigned *item_counter = (unsigned*)(c.counter + 2);
@@ -1084,18 +923,8 @@ static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t
 }
 
 static int kde_launch_cells(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s, bool build = true) {
-    if (c.tiles) {
-        if (c.type == 2) return c.clamp ? kde_run_groups<2, true>(c, nv, out, s, build) : kde_run_groups<2, false>(c, nv, out, s, build);
-        return kde_run_groups<3, true>(c, nv, out, s, build);
-    }
-    const int ncell = c.g.ncx * c.g.ncy;
-    MS_K("kde_cells", s);
-    if (c.type == 2) {
-        if (c.clamp) k_kde_cells<2, true><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
-        else         k_kde_cells<2, false><<<ncell, CELL_T, 0, s>>>((const double2*)c.tgt_sorted, c.tstart, c.tperm, (const double2*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
-    } else           k_kde_cells<3, true><<<ncell, CELL_T, 0, s>>>((const double4*)c.tgt_sorted, c.tstart, c.tperm, (const double4*)c.ssorted, c.sst, c.nlabels, nv, c.g, out);
-    MS_LAUNCH_CHECK();
-    return 0;
+    if (c.type == 2) return c.clamp ? kde_run_groups<2, true>(c, nv, out, s, build) : kde_run_groups<2, false>(c, nv, out, s, build);
+    return kde_run_groups<3, true>(c, nv, out, s, build);
 }
 
 extern "C" int ms_kde(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
@@ -1126,10 +955,9 @@ extern "C" int ms_kde_labels(const float *verts, int64_t nv, const int32_t *labe
     int rc = kde_front(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
     if (c.cells) {
-        if (c.tiles) c.tl.oscale = (double)c.sfactor;
+        c.tl.oscale = (double)c.sfactor;
         rc = kde_launch_cells(c, nv, raw, s);
         if (rc) return rc;
-        if (!c.tiles) { MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(raw, nv * nlabels, (double)c.sfactor); }
         MS_K(NULL, s);
         MS_LAUNCH_CHECK();
         return 0;
@@ -1269,10 +1097,9 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
         // group x extents were measured on the reference staging: they scale with the coordinates
         c.tl.gscale = scales[i] / c.scale;
         double *out = raw + (size_t)i * per;
-        if (c.tiles) c.tl.oscale = (double)sfac[i];                // the groups kernel applies the kernel's sfactor itself
+        c.tl.oscale = (double)sfac[i];                // the groups kernel applies the kernel's sfactor itself
         const int rc = kde_launch_cells(c, nv, out, s, false);
         if (rc) return rc;
-        if (!c.tiles) { MS_K("kde_scale", s); k_kde_scale<<<ms_blocks(nv * nlabels, 256), 256, 0, s>>>(out, nv * nlabels, (double)sfac[i]); }
     }
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
@@ -1320,12 +1147,8 @@ extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int3
     if (rc) return rc;
     if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); *pairs = (double)nv * (double)c.p.ns; return 0; }
     MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
-    const int ncell = c.g.ncx * c.g.ncy;
-    if (c.tiles) {
-        if (kde_build_groups(c, s)) return 2;
-        MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
-    }
-    else { MS_K("kde_cells_count", s); k_kde_cells_count<<<ms_blocks(ncell, 128), 128, 0, s>>>(c.tstart, c.sst, c.nlabels, c.g, c.counter); }
+    if (kde_build_groups(c, s)) return 2;
+    MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     unsigned long long h = 0ull;

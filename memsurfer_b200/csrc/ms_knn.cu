@@ -288,7 +288,8 @@ __device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, co
 
 template <int K>
 __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict__ sorted, int64_t m, Grid g,
-                                                       const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr) {
+                                                       const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr,
+                                                       unsigned *__restrict__ tie_queries) {
     extern __shared__ int32_t sm_nbr[];                   // KNNT_T * k1 neighbour ids + KNNT_T query ids
     int32_t *sm_q = sm_nbr + KNNT_T * k1;
     const int64_t q = (int64_t)blockIdx.x * KNNT_T + threadIdx.x;
@@ -306,6 +307,7 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
 #pragma unroll
         for (int j = 1; j < K; j++) tie |= (bd[j] == bd[j - 1]) && bd[j] < DBL_MAX;      // ties inside the kept list
         if (tie) {             // rare: repeat with the exact (distance, index) order
+            atomicAdd(tie_queries, 1u);
 #pragma unroll
             for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
             knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
@@ -323,9 +325,9 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
 }
 
 template <int K>
-static void knn_thread_launch(const float4 *sorted, int64_t m, const Grid &g, const int32_t *start, int k1, int32_t *nbr, cudaStream_t s) {
+static void knn_thread_launch(const float4 *sorted, int64_t m, const Grid &g, const int32_t *start, int k1, int32_t *nbr, unsigned *ties, cudaStream_t s) {
     const size_t smem = (size_t)KNNT_T * (k1 + 1) * sizeof(int32_t);
-    k_knn_thread<K><<<ms_blocks(m, KNNT_T), KNNT_T, smem, s>>>(sorted, m, g, start, k1, nbr);
+    k_knn_thread<K><<<ms_blocks(m, KNNT_T), KNNT_T, smem, s>>>(sorted, m, g, start, k1, nbr, ties);
 }
 
 extern "C" size_t ms_knn_workspace_bytes(int64_t m, int k1) {
@@ -349,7 +351,8 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     unsigned *bb = (unsigned*)A.take<unsigned>(64);
     const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
     MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
-    MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, bb);
+    MS_CUDA(cudaMemsetAsync(bb + 16, 0, sizeof(unsigned), s));          // diagnostic: queries redone in exact tie order
+    MS_K("bbox", s); k_bbox<<<ms_sm_count() * 4, 256, 0, s>>>(points_all, m, bb);
     unsigned hb[4];
     MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
     MS_CUDA(cudaStreamSynchronize(s));
@@ -378,14 +381,31 @@ extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
     MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
     MS_K("knn", s);
     if (m < k1) k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);   // fewer points than k+1
-    else if (k1 <= 8) knn_thread_launch<8>(sorted, m, g, start, k1, nbr, s);
-    else if (k1 <= 12) knn_thread_launch<12>(sorted, m, g, start, k1, nbr, s);
-    else if (k1 <= 16) knn_thread_launch<16>(sorted, m, g, start, k1, nbr, s);
-    else if (k1 <= 19) knn_thread_launch<19>(sorted, m, g, start, k1, nbr, s);
-    else if (k1 <= 24) knn_thread_launch<24>(sorted, m, g, start, k1, nbr, s);
-    else knn_thread_launch<32>(sorted, m, g, start, k1, nbr, s);
+    else if (k1 <= 8) knn_thread_launch<8>(sorted, m, g, start, k1, nbr, bb + 16, s);
+    else if (k1 <= 12) knn_thread_launch<12>(sorted, m, g, start, k1, nbr, bb + 16, s);
+    else if (k1 <= 16) knn_thread_launch<16>(sorted, m, g, start, k1, nbr, bb + 16, s);
+    else if (k1 <= 19) knn_thread_launch<19>(sorted, m, g, start, k1, nbr, bb + 16, s);
+    else if (k1 <= 24) knn_thread_launch<24>(sorted, m, g, start, k1, nbr, bb + 16, s);
+    else knn_thread_launch<32>(sorted, m, g, start, k1, nbr, bb + 16, s);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
+    return 0;
+}
+
+// diagnostic: number of queries of the last ms_knn call on this workspace that met an exact distance tie and
+// were redone in (distance, index) order.  Syncs the stream.
+extern "C" int ms_knn_tie_queries(const void *ws, size_t ws_bytes, int64_t m, int k1, int64_t *tie_queries, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(ws && tie_queries && ws_bytes >= ms_knn_workspace_bytes(m, k1), "ms_knn_tie_queries: bad arguments");
+    const int64_t ncell_max = m + 2048;
+    MsArena A((void*)ws, ws_bytes);
+    A.take<int32_t>(m); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<float4>(m);
+    A.take<char>(ms_scan_ws_bytes(ncell_max));
+    const unsigned *bb = (const unsigned*)A.take<unsigned>(64);
+    unsigned h = 0;
+    MS_CUDA(cudaMemcpyAsync(&h, bb + 16, sizeof(h), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *tie_queries = (int64_t)h;
     return 0;
 }
 
@@ -481,7 +501,7 @@ static int overlap_launch(const float *points, int64_t m, double dthreshold, con
     if (box4) { lo[0] = box4[0]; lo[1] = box4[1]; hi[0] = box4[2]; hi[1] = box4[3]; }
     else {
         MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
-        MS_K("bbox", s); k_bbox<<<MS_SM_COUNT * 4, 256, 0, s>>>(points, m, bb);
+        MS_K("bbox", s); k_bbox<<<ms_sm_count() * 4, 256, 0, s>>>(points, m, bb);
         unsigned hb[4];
         MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
         MS_CUDA(cudaStreamSynchronize(s));

@@ -182,7 +182,7 @@ extern "C" int ms_orient_normals(const float *points_all, int64_t m, const int32
     const int nb = ms_blocks(m, 256);
     MS_K("edge_weights", s); k_edge_weights<<<ms_blocks(m * k1, 256), 256, 0, s>>>(nbr, m, k1, normals, wkey);
     MS_K("orient_init", s); k_orient_init<<<nb, 256, 0, s>>>(m, link, best, hook, alive);
-    MS_K("find_source", s); k_find_source<<<MS_SM_COUNT * 4, 256, 0, s>>>(points_all, m, srckey);
+    MS_K("find_source", s); k_find_source<<<ms_sm_count() * 4, 256, 0, s>>>(points_all, m, srckey);
     MS_K("source_flip", s); k_source_flip<<<1, 1, 0, s>>>(srckey, normals, flip0);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
@@ -251,7 +251,7 @@ extern "C" int ms_finish_pnormals(const double *normals, int64_t n, int ndir_hin
     MS_REQUIRE(pnormals_f64 != normals, "ms_finish_pnormals: output must not alias the input");
     unsigned long long *key = (unsigned long long*)ws;
     MS_CUDA(cudaMemsetAsync(key, 0, 8, s));
-    MS_K("argmax_absz", s); k_argmax_absz<<<MS_SM_COUNT * 4, 256, 0, s>>>(normals, n, key);
+    MS_K("argmax_absz", s); k_argmax_absz<<<ms_sm_count() * 4, 256, 0, s>>>(normals, n, key);
     MS_K("emit_pnormals", s); k_emit_pnormals<<<ms_blocks(n, 256), 256, 0, s>>>(normals, n, key, ndir_hint, pnormals_f32, pnormals_f64);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();

@@ -124,6 +124,8 @@ class LeafletFrame(object):
         st = _lib.stream_ptr(self.device)
         fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
         raws = {}
+        if fused and len(sigmas) > 1 and len(types) > 1:        # checked before anything is launched
+            raise NotImplementedError('run_densities: one density type per call when sigmas share a binning')
         if fused and len(sigmas) > 1:      # all sigmas of a type on one binning of the vertices
             nl = int(self.label_values.shape[0])
             need = len(sigmas) * nl * self.nv
@@ -136,8 +138,6 @@ class LeafletFrame(object):
                                                  int(self.periodic), self._box(cutoff_sigmas), sg, len(sigmas), float(cutoff_sigmas),
                                                  self.kde_raw_multi.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
                            'ms_kde_labels_multi')
-                if len(types) > 1:
-                    raise NotImplementedError('run_densities: one density type per call when sigmas share a binning')
                 for i, s in enumerate(sigmas):
                     raws[(t, float(s))] = self.kde_raw_multi[i * nl * self.nv:(i + 1) * nl * self.nv]
         for t in types:

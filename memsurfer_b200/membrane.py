@@ -60,6 +60,36 @@ def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1
     return o32, o64, dict(m=m, n_unoriented=int(bad.value))
 
 
+def knn_device(points_dev, k1):
+    """(m,k1) int32 neighbour lists of an (m,3) float32 CUDA tensor through ms_knn, plus the number of queries
+    that met an exact distance tie (diagnostic).  Stage 2 of point_normals_device on its own."""
+    import ctypes as C
+    L = _lib.lib()
+    dev = points_dev.device
+    st = _lib.stream_ptr(dev)
+    m = int(points_dev.shape[0])
+    nbr = torch.empty((m, int(k1)), dtype=torch.int32, device=dev)
+    ws = _lib.workspace(L.ms_knn_workspace_bytes(m, int(k1)), dev)
+    _lib.check(L.ms_knn(points_dev.data_ptr(), m, int(k1), nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    ties = C.c_int64(0)
+    _lib.check(L.ms_knn_tie_queries(ws.data_ptr(), ws.numel(), m, int(k1), C.byref(ties), st), 'ms_knn_tie_queries')
+    return nbr, int(ties.value)
+
+
+def orient_normals_device(points_dev, nbr_dev, normals_dev):
+    """MST orientation (stage 4) of given (m,3) float64 normals in place; returns the number of points that are
+    not connected to the source."""
+    import ctypes as C
+    L = _lib.lib()
+    dev = points_dev.device
+    m, k1 = int(nbr_dev.shape[0]), int(nbr_dev.shape[1])
+    ws = _lib.workspace(L.ms_orient_workspace_bytes(m, k1), dev)
+    bad = C.c_int64(0)
+    _lib.check(L.ms_orient_normals(points_dev.data_ptr(), m, nbr_dev.data_ptr(), k1, normals_dev.data_ptr(), C.byref(bad),
+                                   ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_orient_normals')
+    return int(bad.value)
+
+
 class Membrane(object):
     """Create and analyse membrane surfaces (GPU hot path, host surface producer)."""
 
@@ -291,6 +321,10 @@ class Membrane(object):
             if mesh._label_index is None:
                 mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
             select = np.arange(values.shape[0]) if len(labels) == 0 else np.where(np.isin(values, labels))[0]
+            if select.shape[0] == 0:
+                # none of the requested labels occurs in this leaflet: the reference's np.where(np.in1d(...)) is
+                # empty, and an empty id list means ALL vertices (membrane.py:273-274, TriMesh_kde.cpp: ids.empty())
+                select = np.arange(values.shape[0])
             self.attributes.adopt(name, mesh.compute_density_labels(type, sigma, name, get_nlipdis, select, cutoff_sigmas, lazy=True))
             return
         if len(labels) == 0:

@@ -57,6 +57,65 @@ def make_leaflet(npoints, seed=1234, z0=20.0, ntypes=3, fractions=None, bumps=0,
     return pts, labels, bbox
 
 
+def make_leaflet_rect(nx, ny, seed=1234, z0=20.0, ntypes=3, fractions=None, area_per_lipid=64.0, jitter=0.3,
+                      amplitude=1.0):
+    """Rectangular-box variant of make_leaflet: a jittered nx x ny grid in a box Lx x Ly with Lx/Ly = nx/ny
+    (`jitter` = 0 gives the exact lattice: with area_per_lipid = 64 every coordinate is a float32 integer + 4,
+    so squared distances tie EXACTLY).  Same return values as make_leaflet."""
+    rng = np.random.default_rng(seed)
+    n = nx * ny
+    h = float(np.sqrt(area_per_lipid))
+    Lx, Ly = nx * h, ny * h
+    i, j = np.meshgrid(np.arange(nx), np.arange(ny), indexing="xy")
+    jx = rng.uniform(-jitter, jitter, n) if jitter > 0 else np.zeros(n)
+    jy = rng.uniform(-jitter, jitter, n) if jitter > 0 else np.zeros(n)
+    x = (i.reshape(-1) + 0.5 + jx) * h
+    y = (j.reshape(-1) + 0.5 + jy) * h
+    z = np.full(n, z0, dtype=np.float64)
+    for m in range(4):
+        p, q = int(rng.integers(0, 4)), int(rng.integers(0, 4))
+        if p + q == 0:
+            p = 1
+        amp = amplitude * rng.uniform(0.25, 1.0) * 0.02 * min(Lx, Ly) / (p + q)
+        amp = min(amp, 25.0)
+        phi = rng.uniform(0, 2 * np.pi)
+        z += amp * np.sin(2 * np.pi * (p * x / Lx + q * y / Ly) + phi)
+    pts = np.stack([x, y, z], axis=1).astype(np.float32)
+    if fractions is None:
+        fractions = np.full(ntypes, 1.0 / ntypes)
+    labels = rng.choice(len(fractions), size=n, p=np.asarray(fractions) / np.sum(fractions)).astype(np.int32)
+    Lz = max(Lx, Ly)
+    bbox = np.array([[0.0, 0.0, -Lz / 2], [Lx, Ly, Lz / 2]], dtype=np.float32)
+    return pts, labels, bbox
+
+
+def make_leaflet_clustered(ns=80, seed=7, z0=20.0, ntypes=3, void_radius=100.0, cluster=300, area_per_lipid=64.0):
+    """Hostile density: the left half of a square box at the nominal density, the right half at a quarter of it
+    (every other row and column removed), a circular void of `void_radius` in the middle of the dense half and a
+    micro-cluster of `cluster` points inside a 0.5 A disc in the sparse half.  Same return values as make_leaflet."""
+    rng = np.random.default_rng(seed)
+    h = float(np.sqrt(area_per_lipid))
+    L = ns * h
+    i, j = np.meshgrid(np.arange(ns), np.arange(ns), indexing="xy")
+    i, j = i.reshape(-1), j.reshape(-1)
+    keep = (i < ns // 2) | ((i % 2 == 0) & (j % 2 == 0))
+    x = (i + 0.5 + rng.uniform(-0.3, 0.3, i.shape[0])) * h
+    y = (j + 0.5 + rng.uniform(-0.3, 0.3, i.shape[0])) * h
+    cx, cy = 0.25 * L, 0.5 * L
+    keep &= (x - cx) ** 2 + (y - cy) ** 2 > void_radius ** 2
+    x, y = x[keep], y[keep]
+    if cluster > 0:
+        r, t = 0.5 * np.sqrt(rng.uniform(0, 1, cluster)), rng.uniform(0, 2 * np.pi, cluster)
+        x = np.concatenate([x, 0.75 * L + h / 3 + r * np.cos(t)])
+        y = np.concatenate([y, 0.5 * L + h / 3 + r * np.sin(t)])
+    z = z0 + 6.0 * np.sin(2 * np.pi * x / L + 0.3) + 4.0 * np.sin(2 * np.pi * (x + 2 * y) / L + 1.1)
+    perm = rng.permutation(x.shape[0])              # no spatial order in the index either
+    pts = np.stack([x, y, z], axis=1)[perm].astype(np.float32)
+    labels = rng.integers(0, ntypes, pts.shape[0]).astype(np.int32)
+    bbox = np.array([[0.0, 0.0, -L / 2], [L, L, L / 2]], dtype=np.float32)
+    return pts, labels, bbox
+
+
 def periodic_delaunay(xy, box0, box1, margin=None):
     """Host stand-in for TriMesh::periodicDelaunay (TriMesh_cgal.cpp:160-281).
 

@@ -553,6 +553,22 @@ class TriMesh(object):
                             ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_kde')
         return o64, o32
 
+    KDE_RAW_CACHE_BYTES = 4 << 30      # raw per-label pair sums kept per mesh (oldest (type, sigma, cut-off) evicted first)
+
+    def _kde_raw_store(self, key, raw):
+        cache = self._dev.setdefault('kde_raw', {})
+        cache[key] = raw
+        total = sum(v.numel() * 8 for v in cache.values())
+        for k in list(cache.keys()):
+            if total <= self.KDE_RAW_CACHE_BYTES or k == key:
+                continue
+            total -= cache[k].numel() * 8
+            del cache[k]
+
+    def clear_density_cache(self):
+        """Drop the raw per-label pair sums kept for later compute_density_labels calls (device memory)."""
+        self._dev.pop('kde_raw', None)
+
     def set_vertex_labels(self, label_index, nlabels, counts=None):
         """Integer label in [0, nlabels) per vertex (negative: never a KDE source).  Enables the label-fused
         KDE: one pass evaluates every vertex pair once and keeps the sums apart by the source's label."""
@@ -587,7 +603,7 @@ class TriMesh(object):
                                    int(bool(self.periodic)), self._kde_box(cutoff_sigmas), float(sigma),
                                    float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
                                    _lib.stream_ptr(dev)), 'ms_kde_labels')
-        cache[key] = raw
+        self._kde_raw_store(key, raw)
         return raw
 
     @_lib.home_stream
@@ -614,7 +630,7 @@ class TriMesh(object):
                                          float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
                                          _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
         for i, s_ in enumerate(todo):
-            cache[(int(type), s_, float(cutoff_sigmas))] = raw[i]
+            self._kde_raw_store((int(type), s_, float(cutoff_sigmas)), raw[i])
 
     @_lib.home_stream
     def density_select_device(self, raw, select, get_nlipids):
@@ -639,8 +655,10 @@ class TriMesh(object):
         are the sources.  Same result as compute_density with the ids of those vertices."""
         if type < 1 or type > 3:
             raise ValueError('Invalid density type, {}. Should be 1 (geodesic), 2 (2D) or 3 (3D)'.format(type))
-        if type == 1:
-            raise NotImplementedError('geodesic density (type 1) is outside the GPU hot path (SURVEY.md section 2, #5b)')
+        if type == 1:                 # geodesic: no label-fused kernel, the ids of the selected labels go to kde_2m
+            sel = np.zeros(self._nlabels, bool); sel[np.asarray(select, dtype=np.int64)] = True
+            pidxs = np.empty([0]) if sel.all() else np.where(sel[np.maximum(self._label_index, 0)] & (self._label_index >= 0))[0]
+            return self.compute_density(1, sigma, name, get_nlipids, pidxs, cutoff_sigmas, lazy=lazy)
         if name not in self._fields:
             raw = self.density_labels_device(type, sigma, cutoff_sigmas)
             o64, o32 = self.density_select_device(raw, select, get_nlipids)
@@ -650,7 +668,7 @@ class TriMesh(object):
                 dens = self._fields[name]
                 LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         if lazy:                  # hand out the download in flight (or the finished array)
-            return dict.__getitem__(self._fields, name)
+            return self._fields.raw(name)
         return self._fields[name]
 
     @_lib.home_stream
@@ -677,7 +695,7 @@ class TriMesh(object):
                 dens = self._fields[name]
                 LOGGER.info(f'{self.tag()} density [{name}] range = [{dens.min()}, {dens.max()}], sum = {dens.sum()}')
         if lazy:
-            return dict.__getitem__(self._fields, name)
+            return self._fields.raw(name)
         return self._fields[name]
 
     # ---------------------------------------------------------------------- export (host)

@@ -56,11 +56,14 @@ class OverlapCheck(object):
         _lib.check(L.ms_overlapping_pairs_async(points_dev.data_ptr(), n, float(dthreshold), b, self.pairs.data_ptr(), max_pairs,
                                                 self.result.data_ptr(), self.ws.data_ptr(), self.ws.numel(), _lib.stream_ptr(dev)),
                    'ms_overlapping_pairs_async')
+        self.event = torch.cuda.Event()           # report() may run on another stream than the one this was queued on
+        self.event.record(torch.cuda.current_stream(dev))
 
     def report(self):
         """True if no two points overlap; else warn (memsurfer/utils.py:121) and return False."""
         if self.done:
             return self.ok
+        self.event.synchronize()
         nzero = int(self.result[0].item())
         self.done, self.ok = True, nzero == 0
         if nzero:

@@ -127,6 +127,7 @@ def test_overlapping_points_vs_pdist():
     assert np.isclose(dmin, pd[pd > 1e-5].min(), rtol=0, atol=0)
     assert test_overlapping_points(bad) is False
     fixed = bad.copy()
+    np.random.seed(0)          # the reference's fix draws its moves from np.random (utils.py:147-148): ~1 % of draws move < 1e-5
     test_overlapping_points(fixed, fix=True)
     assert test_overlapping_points(fixed) is True                 # every coincident pair was separated
     assert (fixed != bad).any(axis=1).sum() <= 3
