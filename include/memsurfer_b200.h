@@ -8,7 +8,8 @@
  *     returned by the matching *_workspace_bytes(); nothing is allocated or
  *     kept by the library (no global mutable state; re-entrant per stream);
  *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on
- *     it except where "syncs" is noted (a small device->host read-back);
+ *     it except where "syncs" is noted (a small device->host read-back); the
+ *     per-frame hot path (point normals, mesh properties, KDE) never syncs;
  *   - return value: 0 = ok, non-zero = error (see ms_last_error(), a
  *     thread-local string).  Nothing throws across this boundary (the
  *     reference aborts the interpreter on C++ exceptions: memsurfer.i has no
@@ -33,41 +34,54 @@ const char *ms_last_error(void);
  * (PointSet.cpp:156-200), get_normals (PointSet.cpp:70-88) and the global flip
  * of Membrane.compute_pnormals (membrane.py:145-152).                          */
 
+/* Nothing in stages 1-4 is read back by the host: the number of points incl. ghost images stays on the device in
+ * an 8 x int64 status block `info` that the caller allocates and threads through the chain (arrays are sized by
+ * ms_pointset_capacity, kernels are launched over the capacity and leave early).  The caller reads the block
+ * whenever it reads results.                                                                        */
+#define MS_INFO_M           0   /* points incl. ghost images (written by ms_ghosts)                  */
+#define MS_INFO_UNORIENTED  1   /* points not connected to the source (ms_orient_normals)            */
+#define MS_INFO_KNN_TIES    2   /* diagnostic: k-NN queries redone in exact (distance, index) order  */
+#define MS_INFO_MST_ROUNDS  3   /* diagnostic: Boruvka rounds                                         */
+#define MS_INFO_ERROR       4   /* bit flags, 0 = ok                                                  */
+#define MS_INFO_WORDS       8
+#define MS_ERR_NONFINITE    1   /* non-finite coordinates: every neighbour list is -1                */
+
 /* Upper bound of points incl. ghost images (each point gets <= 3 images). */
 int64_t ms_pointset_capacity(int64_t n, int periodic);
 
 /* Stage 1: ghost images.  points (n,3) f32 -> points_all (cap,3) f32 = points ++ ghosts in the
  * reference's order; ghost_src (cap,) i32 = original index of every row.  box6 (host) =
  * {b0x,b0y,b0z,b1x,b1y,b1z} as float32; blayer in (0,1).  periodic == 0 copies the points only.
- * *m_out (host) receives n + #ghosts.  Syncs the stream once.                                  */
+ * info (device, MS_INFO_WORDS x int64): [MS_INFO_M] = n + #ghosts, the other words are cleared.       */
 size_t ms_ghosts_workspace_bytes(int64_t n);
 int ms_ghosts(const float *points, int64_t n, int periodic, const float *box6, float blayer,
-              float *points_all, int32_t *ghost_src, int64_t *m_out,
+              float *points_all, int32_t *ghost_src, int64_t *info,
               void *ws, size_t ws_bytes, void *stream);
 
-/* Stage 2: exact (k1 = k+1)-nearest neighbours incl. self for all m points, sorted by
- * (squared distance in fp64, index), via a uniform xy cell list.  nbr (m,k1) i32.             */
-size_t ms_knn_workspace_bytes(int64_t m, int k1);
-int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
+/* Stage 2: exact (k1 = k+1)-nearest neighbours incl. self for the first m points of points_all (m_cap rows
+ * allocated; m = info[MS_INFO_M] read on the device, or m_cap when info == NULL), sorted by (squared distance
+ * in fp64, index), via a uniform xy cell list whose geometry is worked out on the device.  nbr (m_cap,k1) i32. */
+size_t ms_knn_workspace_bytes(int64_t m_cap, int k1);
+int ms_knn(const float *points_all, int64_t m_cap, int64_t *info, int k1, int32_t *nbr,
            void *ws, size_t ws_bytes, void *stream);
 
-/* Diagnostic (no reference counterpart): queries of the last ms_knn call on workspace `ws` that met an exact
- * distance tie and were redone in (distance, index) order.  Syncs the stream.                    */
-int ms_knn_tie_queries(const void *ws, size_t ws_bytes, int64_t m, int k1, int64_t *tie_queries, void *stream);
-
 /* Stage 3: PCA normal of every point from its k1 neighbours (unit eigenvector of the smallest
- * eigenvalue of the 3x3 covariance; sign arbitrary).  normals (m,3) f64.                      */
-int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
+ * eigenvalue of the 3x3 covariance; sign arbitrary).  normals (m_cap,3) f64.                      */
+int ms_pca_normals(const float *points_all, int64_t m_cap, const int64_t *info, const int32_t *nbr, int k1,
                    double *normals, void *stream);
 
 /* Stage 4: minimum-spanning-tree orientation over the Riemannian graph (edge {a<b} iff b in
- * NN(a), weight float(max(0,1-|na.nb|)), ties by (w,a,b)); source = first max-z point flipped
- * to n_z >= 0.  normals updated in place.  *n_unoriented (host) = points not connected to the
- * source.  Syncs the stream.                                                                   */
-size_t ms_orient_workspace_bytes(int64_t m, int k1);
-int ms_orient_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
-                      double *normals, int64_t *n_unoriented,
-                      void *ws, size_t ws_bytes, void *stream);
+ * NN(a), weight float(max(0,1-|na.nb|)), ties by (w,a,slot)); source = first max-z point flipped
+ * to n_z >= 0.  normals updated in place.  info[MS_INFO_UNORIENTED] = points not connected to the
+ * source.  One cooperative launch; the number of Boruvka rounds is decided on the device.         */
+size_t ms_orient_workspace_bytes(int64_t m_cap, int k1);
+int ms_orient_normals(const float *points_all, int64_t m_cap, int64_t *info, const int32_t *nbr, int k1,
+                      double *normals, void *ws, size_t ws_bytes, void *stream);
+
+/* Diagnostic (no reference counterpart): nanoseconds spent in every phase of the last ms_orient_normals call on
+ * workspace `ws` (init, round 0 edges, round 0 hooks, then edges / hooks of every later round, orientation):
+ * ns_out (host, cap doubles), *nphases = entries written.  Syncs the stream.                          */
+int ms_orient_phase_times(const void *ws, size_t ws_bytes, int64_t m_cap, int k1, double *ns_out, int cap, int *nphases, void *stream);
 
 /* Stage 5: first n normals -> float32, flipped globally if the z of the normal with the largest
  * |n_z| (float32) times ndir_hint is negative (membrane.py:148-152).                            */

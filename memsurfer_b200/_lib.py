@@ -26,13 +26,13 @@ _SIGNATURES = {
     "ms_last_error": (C.c_char_p, []),
     "ms_pointset_capacity": (_i64, [_i64, _i32]),
     "ms_ghosts_workspace_bytes": (_sz, [_i64]),
-    "ms_ghosts": (C.c_int, [_vp, _i64, _i32, C.POINTER(_f32), _f32, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_ghosts": (C.c_int, [_vp, _i64, _i32, C.POINTER(_f32), _f32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ms_knn_workspace_bytes": (_sz, [_i64, _i32]),
-    "ms_knn": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _sz, _vp]),
-    "ms_knn_tie_queries": (C.c_int, [_vp, _sz, _i64, _i32, C.POINTER(_i64), _vp]),
-    "ms_pca_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
+    "ms_knn": (C.c_int, [_vp, _i64, _vp, _i32, _vp, _vp, _sz, _vp]),
+    "ms_pca_normals": (C.c_int, [_vp, _i64, _vp, _vp, _i32, _vp, _vp]),
     "ms_orient_workspace_bytes": (_sz, [_i64, _i32]),
-    "ms_orient_normals": (C.c_int, [_vp, _i64, _vp, _i32, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_orient_normals": (C.c_int, [_vp, _i64, _vp, _vp, _i32, _vp, _vp, _sz, _vp]),
+    "ms_orient_phase_times": (C.c_int, [_vp, _sz, _i64, _i32, C.POINTER(_f64), _i32, C.POINTER(_i32), _vp]),
     "ms_finish_workspace_bytes": (_sz, [_i64]),
     "ms_finish_pnormals": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
     "ms_mesh_topology_workspace_bytes": (_sz, [_i64, _i64]),
@@ -75,6 +75,8 @@ _SIGNATURES = {
     "ms_profile_report": (C.c_int, [C.c_char_p, _sz]),
 }
 EXPORTS = tuple(_SIGNATURES.keys())
+# layout of the device status block of the point-normal chain (include/memsurfer_b200.h)
+INFO_M, INFO_UNORIENTED, INFO_KNN_TIES, INFO_MST_ROUNDS, INFO_ERROR, INFO_WORDS = 0, 1, 2, 3, 4, 8
 
 
 def lib():
@@ -159,6 +161,33 @@ def pinned_copy(a, dtype):
     out = pinned_empty(a.shape, dtype)
     fast_copy(out, a)
     return out
+
+
+def is_pinned(a):
+    """True if the numpy array lives in page-locked host memory (e.g. it came from `pinned()`)."""
+    try:
+        return bool(torch.cuda.is_available() and a.flags.c_contiguous and a.flags.writeable and torch.from_numpy(a).is_pinned())
+    except Exception:
+        return False
+
+
+def pinned(a, dtype=None):
+    """Copy of `a` in page-locked host memory (numpy array).  Arrays handed to Membrane / TriMesh in this form, with
+    the dtype the class stores (float32 points and vertices, uint32 faces), are uploaded by DMA straight from
+    where they are -- no staging copy on the host."""
+    import numpy as np
+    a = np.asarray(a)
+    return pinned_copy(a, a.dtype if dtype is None else dtype)
+
+
+def staged(a, dtype):
+    """(array to upload from, shared): `a` itself when it already is page-locked, C-contiguous and of `dtype`
+    (shared = True: the caller must copy before writing to it), else a page-locked copy."""
+    import numpy as np
+    a = np.asarray(a)
+    if a.dtype == np.dtype(dtype) and is_pinned(a):
+        return a, True
+    return pinned_copy(a, dtype), False
 
 
 def h2d(arr, device):

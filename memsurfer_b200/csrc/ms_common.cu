@@ -101,50 +101,59 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *smem /* 32 */, i
     return woff + x - v;
 }
 
-__global__ void __launch_bounds__(SCAN_T) k_scan_blocksum(const int32_t *in, int64_t n, int32_t *bsum) {
+// Single-pass chained scan with decoupled look-back: one launch (+ one memset of the tile states) instead of
+// the classic three.  Tile ids are handed out by an atomic counter in the order the CTAs start, so a tile only
+// ever waits for tiles that are already running or done.  Tile state = one 64-bit word (flag << 62 | sum):
+// a single store publishes flag and value together.
+#define SCAN_FLAG_A (1ull << 62)       // aggregate of this tile only
+#define SCAN_FLAG_P (2ull << 62)       // inclusive prefix up to and including this tile
+__global__ void __launch_bounds__(SCAN_T) k_scan_lookback(const int32_t *__restrict__ in, int32_t *__restrict__ out, int64_t n,
+                                                          unsigned long long *state /* [0] = tile counter, [1 + t] = tile t */) {
     __shared__ int sm[32];
-    const int64_t base = (int64_t)blockIdx.x * SCAN_B + threadIdx.x * SCAN_I;
-    int s = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_I; i++) if (base + i < n) s += in[base + i];
-    int total; block_exclusive_scan(s, sm, total);
-    if (threadIdx.x == 0) bsum[blockIdx.x] = total;
-}
-
-__global__ void __launch_bounds__(SCAN_T) k_scan_top(int32_t *bsum, int64_t nb) {
-    __shared__ int sm[32];
-    int carry = 0;
-    for (int64_t c = 0; c < nb; c += SCAN_T) {
-        const int64_t i = c + threadIdx.x;
-        const int v = i < nb ? bsum[i] : 0;
-        int total; const int ex = block_exclusive_scan(v, sm, total);
-        if (i < nb) bsum[i] = carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0) bsum[nb] = carry;
-}
-
-__global__ void __launch_bounds__(SCAN_T) k_scan_final(const int32_t *in, int32_t *out, int64_t n, const int32_t *bsum) {
-    __shared__ int sm[32];
-    const int64_t base = (int64_t)blockIdx.x * SCAN_B + threadIdx.x * SCAN_I;
+    __shared__ int s_tile, s_prefix;
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(state, 1ull);
+    __syncthreads();
+    const int t = s_tile;
+    volatile unsigned long long *st = state + 1;
+    const int64_t base = (int64_t)t * SCAN_B + threadIdx.x * SCAN_I;
     int v[SCAN_I]; int s = 0;
 #pragma unroll
     for (int i = 0; i < SCAN_I; i++) { v[i] = base + i < n ? in[base + i] : 0; s += v[i]; }
-    int total; int ex = block_exclusive_scan(s, sm, total) + bsum[blockIdx.x];
+    int total; int ex = block_exclusive_scan(s, sm, total);
+    if (threadIdx.x == 0) {
+        st[t] = (t == 0 ? SCAN_FLAG_P : SCAN_FLAG_A) | (unsigned long long)(unsigned)total;
+        if (t == 0) s_prefix = 0;
+    }
+    if (t > 0 && threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int prefix = 0;
+        for (int j = t - 1; ; j -= 32) {
+            unsigned long long w = SCAN_FLAG_P;              // tiles before tile 0: an empty inclusive prefix
+            if (j - lane >= 0) { do { w = st[j - lane]; } while ((w >> 62) == 0ull); }
+            const unsigned pmask = __ballot_sync(0xffffffffu, (w >> 62) == 2ull);
+            const int first = pmask ? __ffs(pmask) - 1 : 32;  // nearest tile with a full prefix
+            int val = lane <= first ? (int)(unsigned)(w & 0xffffffffull) : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+            prefix += val;
+            if (pmask) break;
+        }
+        if (lane == 0) { st[t] = SCAN_FLAG_P | (unsigned long long)(unsigned)(prefix + total); s_prefix = prefix; }
+    }
+    __syncthreads();
+    ex += s_prefix;
 #pragma unroll
     for (int i = 0; i < SCAN_I; i++) { if (base + i < n) out[base + i] = ex; ex += v[i]; }
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) out[n] = bsum[gridDim.x];
+    if (base <= n - 1 && n - 1 < base + SCAN_I) out[n] = ex;     // the thread that owns the last element (ex = grand total by now)
 }
 
-size_t ms_scan_ws_bytes(int64_t n) { return ms_align(((n + SCAN_B - 1) / SCAN_B + 2) * sizeof(int32_t)); }
+size_t ms_scan_ws_bytes(int64_t n) { return ms_align(((n + SCAN_B - 1) / SCAN_B + 2) * sizeof(unsigned long long)); }
 
 int ms_exclusive_scan_i32(const int32_t *in, int32_t *out, int64_t n, void *ws, cudaStream_t s) {
-    int32_t *bsum = (int32_t*)ws;
     if (n <= 0) { MS_CUDA(cudaMemsetAsync(out, 0, sizeof(int32_t), s)); return 0; }
     const int64_t nb = (n + SCAN_B - 1) / SCAN_B;
-    MS_K("scan_blocksum", s); k_scan_blocksum<<<(unsigned)nb, SCAN_T, 0, s>>>(in, n, bsum);
-    MS_K("scan_top", s); k_scan_top<<<1, SCAN_T, 0, s>>>(bsum, nb);
-    MS_K("scan_final", s); k_scan_final<<<(unsigned)nb, SCAN_T, 0, s>>>(in, out, n, bsum);
+    MS_CUDA(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), s));
+    MS_K("scan", s); k_scan_lookback<<<(unsigned)nb, SCAN_T, 0, s>>>(in, out, n, (unsigned long long*)ws);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;

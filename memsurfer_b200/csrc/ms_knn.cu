@@ -12,6 +12,7 @@
 // ties break by ascending index.
 #include "ms_common.cuh"
 #include <float.h>
+#include <string.h>
 
 // ------------------------------------------------------------------ stage 1: ghosts
 struct GhostCuts { float boxw0, boxw1, l0, l1, r0, r1; };
@@ -59,16 +60,22 @@ extern "C" size_t ms_ghosts_workspace_bytes(int64_t n) {
     return 2 * ms_align((size_t)(n + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(n) + 1024;
 }
 
+// info[MS_INFO_M] = n + total ghosts (or n); the other diagnostic slots are cleared
+__global__ void k_ghost_total(const int32_t *__restrict__ off_n, int64_t n, int64_t *info) {
+    info[MS_INFO_M] = n + (off_n ? (int64_t)*off_n : 0);
+    info[MS_INFO_UNORIENTED] = 0; info[MS_INFO_KNN_TIES] = 0; info[MS_INFO_MST_ROUNDS] = 0; info[MS_INFO_ERROR] = 0;
+}
+
 extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const float *box6, float blayer,
-                         float *points_all, int32_t *ghost_src, int64_t *m_out,
+                         float *points_all, int32_t *ghost_src, int64_t *info,
                          void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(n > 0 && m_out, "ms_ghosts: bad arguments");
+    MS_REQUIRE(n > 0 && info, "ms_ghosts: bad arguments");
     if (!periodic) {
         MS_K("copy_points", s); k_copy_points<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, points_all, ghost_src);
+        MS_K("ghost_total", s); k_ghost_total<<<1, 1, 0, s>>>(NULL, n, info);
         MS_K(NULL, s);
         MS_LAUNCH_CHECK();
-        *m_out = n;
         return 0;
     }
     MS_REQUIRE(box6, "ms_ghosts: periodic point set needs the box");
@@ -85,23 +92,23 @@ extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const flo
     MS_K("ghost_count", s); k_ghost_count<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, cnt);
     if (ms_exclusive_scan_i32(cnt, off, n, scan_ws, s)) return 2;
     MS_K("ghost_fill", s); k_ghost_fill<<<ms_blocks(n, 256), 256, 0, s>>>(points, n, c, off, points_all, ghost_src);
+    MS_K("ghost_total", s); k_ghost_total<<<1, 1, 0, s>>>(off + n, n, info);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
-    int32_t total = 0;
-    MS_CUDA(cudaMemcpyAsync(&total, off + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaStreamSynchronize(s));
-    *m_out = n + (int64_t)total;
     return 0;
 }
 
 // ------------------------------------------------------------------ stage 2: cell list + exact kNN
-struct Grid { float lox, loy; double h, inv_h; int nx, ny; };
+struct Grid { float lox, loy; double h, inv_h; int nx, ny, ok, pad; };
 
 __device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
 
+__device__ __forceinline__ int64_t ms_count(const int64_t *info, int64_t cap) { return info ? min(__ldg(info + MS_INFO_M), cap) : cap; }
+
 // bb[0..3] = ordered-uint (min x, min y, max x, max y)
-__global__ void __launch_bounds__(256) k_bbox(const float *__restrict__ pts, int64_t m, unsigned *bb) {
+__global__ void __launch_bounds__(256) k_bbox(const float *__restrict__ pts, int64_t m_cap, const int64_t *__restrict__ info, unsigned *bb) {
+    const int64_t m = ms_count(info, m_cap);
     unsigned mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0u, mxy = 0u;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (int64_t)gridDim.x * blockDim.x) {
         const unsigned x = f2ord(pts[3*i]), y = f2ord(pts[3*i+1]);
@@ -121,87 +128,51 @@ __device__ __forceinline__ int cell_of(const Grid &g, float x, float y, int &cx,
     return cy * g.nx + cx;
 }
 
-__global__ void __launch_bounds__(256) k_cell_count(const float *__restrict__ pts, int64_t m, Grid g, int32_t *cell, int32_t *cnt) {
+// the cell list's geometry from the measured extent and the point count: one thread, on the device, so that
+// the host never waits for either (ppc = target points per cell; h_min = smallest admissible cell side)
+__global__ void k_make_grid(const unsigned *__restrict__ bb, float4 box4, int has_box, int64_t m_cap, int64_t *info,
+                            double ppc, double h_min, int64_t ncell_max, Grid *gout) {
+    const int64_t m = info ? min(info[MS_INFO_M], m_cap) : m_cap;
+    float lo[2], hi[2];
+    if (has_box) { lo[0] = box4.x; lo[1] = box4.y; hi[0] = box4.z; hi[1] = box4.w; }
+    else { lo[0] = ord2f(bb[0]); lo[1] = ord2f(bb[1]); hi[0] = ord2f(bb[2]); hi[1] = ord2f(bb[3]); }
+    double wx = (double)hi[0] - (double)lo[0], wy = (double)hi[1] - (double)lo[1];
+    Grid g;
+    g.ok = (wx == wx && wy == wy && wx < 1e30 && wy < 1e30) ? 1 : 0;        // non-finite coordinates: every query gives up
+    if (!g.ok) { wx = 1.0; wy = 1.0; lo[0] = lo[1] = 0.f; if (info) info[MS_INFO_ERROR] |= MS_ERR_NONFINITE; }
+    if (!(wx > 0.0)) wx = 1e-6; if (!(wy > 0.0)) wy = 1e-6;
+    double h = sqrt(wx * wy * ppc / (double)(m > 0 ? m : 1));
+    if (h < h_min) h = h_min;
+    for (;;) {
+        const double nxd = floor(wx / h) + 1.0, nyd = floor(wy / h) + 1.0;
+        if (nxd * nyd <= (double)(ncell_max - 1)) { g.nx = (int)nxd; g.ny = (int)nyd; break; }
+        h *= 1.5;
+    }
+    g.lox = lo[0]; g.loy = lo[1]; g.h = h; g.inv_h = 1.0 / h;
+    *gout = g;
+}
+
+__global__ void __launch_bounds__(256) k_cell_count(const float *__restrict__ pts, int64_t m_cap, const int64_t *__restrict__ info,
+                                                    const Grid *__restrict__ gp, int32_t *cell, int32_t *cnt) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
+    if (i >= ms_count(info, m_cap)) return;
+    const Grid g = *gp;
     int cx, cy; const int c = cell_of(g, pts[3*i], pts[3*i+1], cx, cy);
     cell[i] = c; atomicAdd(cnt + c, 1);
 }
 
 // sorted[p] = (x, y, z, original index as int bits) grouped by cell
-__global__ void __launch_bounds__(256) k_cell_scatter(const float *__restrict__ pts, int64_t m, const int32_t *__restrict__ cell,
+__global__ void __launch_bounds__(256) k_cell_scatter(const float *__restrict__ pts, int64_t m_cap, const int64_t *__restrict__ info,
+                                                      const int32_t *__restrict__ cell,
                                                       const int32_t *__restrict__ start, int32_t *cursor, float4 *sorted) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
+    if (i >= ms_count(info, m_cap)) return;
     const int c = cell[i];
     const int p = start[c] + atomicAdd(cursor + c, 1);
     sorted[p] = make_float4(pts[3*i], pts[3*i+1], pts[3*i+2], __int_as_float((int)i));
 }
 
 __device__ __forceinline__ bool key_lt(double d, int i, double e, int j) { return d < e || (d == e && i < j); }
-
-// One warp per query (queries taken in cell order for locality).  Lane l keeps the l-th best
-// (d2, index) so far; candidates are read 32 at a time and inserted by warp shuffles.
-#define KNN_WARPS 8
-__global__ void __launch_bounds__(KNN_WARPS * 32) k_knn(const float4 *__restrict__ sorted, int64_t m, Grid g,
-                                                        const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr) {
-    const int lane = threadIdx.x & 31;
-    const int64_t w = (int64_t)blockIdx.x * KNN_WARPS + (threadIdx.x >> 5);
-    if (w >= m) return;
-    const float4 q = sorted[w];
-    const int qi = __float_as_int(q.w);
-    const double qx = q.x, qy = q.y, qz = q.z;
-    int cx, cy; cell_of(g, q.x, q.y, cx, cy);
-    double bd = DBL_MAX; int bi = 0x7fffffff;            // this lane's slot
-    const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
-    for (int r = 0; ; r++) {
-        for (int yy = cy - r; yy <= cy + r; yy++) {
-            if (yy < 0 || yy >= g.ny) continue;
-            const bool full_row = (yy == cy - r) || (yy == cy + r);
-            const int nseg = full_row ? 1 : 2;
-            for (int sg = 0; sg < nseg; sg++) {
-                int x0, x1;
-                if (full_row) { x0 = cx - r; x1 = cx + r; } else { x0 = x1 = (sg == 0 ? cx - r : cx + r); }
-                x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
-                if (x0 > x1) continue;
-                const int pb = __ldg(start + yy * g.nx + x0), pe = __ldg(start + yy * g.nx + x1 + 1);
-                for (int p0 = pb; p0 < pe; p0 += 32) {
-                    const int p = p0 + lane;
-                    double cd = DBL_MAX; int cidx = 0x7fffffff;
-                    if (p < pe) {
-                        const float4 c = __ldg(sorted + p);
-                        const double dx = qx - (double)c.x, dy = qy - (double)c.y, dz = qz - (double)c.z;
-                        cd = 0.0; cd += dx * dx; cd += dy * dy; cd += dz * dz;
-                        cidx = __float_as_int(c.w);
-                    }
-                    double td = __shfl_sync(0xffffffffu, bd, k1 - 1); int ti = __shfl_sync(0xffffffffu, bi, k1 - 1);
-                    unsigned mask = __ballot_sync(0xffffffffu, key_lt(cd, cidx, td, ti));
-                    while (mask) {
-                        const int srcl = __ffs(mask) - 1;
-                        const double nd = __shfl_sync(0xffffffffu, cd, srcl); const int ni = __shfl_sync(0xffffffffu, cidx, srcl);
-                        const double pd = __shfl_up_sync(0xffffffffu, bd, 1); const int pi = __shfl_up_sync(0xffffffffu, bi, 1);
-                        const bool lt_me = key_lt(nd, ni, bd, bi);
-                        const bool lt_prev = lane > 0 && key_lt(nd, ni, pd, pi);
-                        if (lt_me) { if (lt_prev) { bd = pd; bi = pi; } else { bd = nd; bi = ni; } }
-                        td = __shfl_sync(0xffffffffu, bd, k1 - 1); ti = __shfl_sync(0xffffffffu, bi, k1 - 1);
-                        mask &= ~(1u << srcl);
-                        mask &= __ballot_sync(0xffffffffu, key_lt(cd, cidx, td, ti));
-                    }
-                }
-            }
-        }
-        if (cx - r <= 0 && cy - r <= 0 && cx + r >= g.nx - 1 && cy + r >= g.ny - 1) break;
-        // distance to the unexplored region; a side on which the window already reaches the grid edge has none
-        const double b0 = cx - r > 0 ? rx - (double)(cx - r) * g.h : DBL_MAX;
-        const double b1 = cx + r < g.nx - 1 ? (double)(cx + r + 1) * g.h - rx : DBL_MAX;
-        const double b2 = cy - r > 0 ? ry - (double)(cy - r) * g.h : DBL_MAX;
-        const double b3 = cy + r < g.ny - 1 ? (double)(cy + r + 1) * g.h - ry : DBL_MAX;
-        const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
-        const double td = __shfl_sync(0xffffffffu, bd, k1 - 1);
-        if (bm > 0.0 && td < DBL_MAX && sqrt(td) < bm * (1.0 - 1e-9)) break;
-    }
-    if (lane < k1) nbr[(int64_t)qi * k1 + lane] = (bi == 0x7fffffff) ? -1 : bi;
-}
 
 // One THREAD per query (queries in cell order, so a warp works on neighbouring cells): the K best
 // (d2, index) so far live in registers as a sorted list; a candidate that beats the current worst is
@@ -287,17 +258,21 @@ __device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, co
 }
 
 template <int K>
-__global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict__ sorted, int64_t m, Grid g,
+__global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict__ sorted, int64_t m_cap, const int64_t *__restrict__ info,
+                                                       const Grid *__restrict__ gp,
                                                        const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr,
-                                                       unsigned *__restrict__ tie_queries) {
+                                                       int64_t *__restrict__ info_out) {
     extern __shared__ int32_t sm_nbr[];                   // KNNT_T * k1 neighbour ids + KNNT_T query ids
     int32_t *sm_q = sm_nbr + KNNT_T * k1;
+    const int64_t m = ms_count(info, m_cap);
+    if ((int64_t)blockIdx.x * KNNT_T >= m) return;         // capacity-sized launch: blocks beyond the point count leave at once
+    const Grid g = *gp;
     const int64_t q = (int64_t)blockIdx.x * KNNT_T + threadIdx.x;
     double bd[K]; int bi[K];
 #pragma unroll
     for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
     int qi = -1;
-    if (q < m) {
+    if (q < m && g.ok) {
         const float4 me = sorted[q];
         qi = __float_as_int(me.w);
         const double qx = me.x, qy = me.y, qz = me.z;
@@ -307,12 +282,13 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
 #pragma unroll
         for (int j = 1; j < K; j++) tie |= (bd[j] == bd[j - 1]) && bd[j] < DBL_MAX;      // ties inside the kept list
         if (tie) {             // rare: repeat with the exact (distance, index) order
-            atomicAdd(tie_queries, 1u);
+            if (info_out) atomicAdd((unsigned long long*)(info_out + MS_INFO_KNN_TIES), 1ull);
 #pragma unroll
             for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
             knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
         }
     }
+    if (q < m && !g.ok) qi = __float_as_int(sorted[q].w);      // non-finite input: the row is all -1
     sm_q[threadIdx.x] = qi;
 #pragma unroll
     for (int j = 0; j < K; j++) if (j < k1) sm_nbr[threadIdx.x * k1 + j] = (bi[j] == 0x7fffffff) ? -1 : bi[j];
@@ -325,9 +301,10 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
 }
 
 template <int K>
-static void knn_thread_launch(const float4 *sorted, int64_t m, const Grid &g, const int32_t *start, int k1, int32_t *nbr, unsigned *ties, cudaStream_t s) {
+static void knn_thread_launch(const float4 *sorted, int64_t m_cap, const int64_t *info, const Grid *g, const int32_t *start, int k1, int32_t *nbr,
+                              int64_t *info_out, cudaStream_t s) {
     const size_t smem = (size_t)KNNT_T * (k1 + 1) * sizeof(int32_t);
-    k_knn_thread<K><<<ms_blocks(m, KNNT_T), KNNT_T, smem, s>>>(sorted, m, g, start, k1, nbr, ties);
+    k_knn_thread<K><<<ms_blocks(m_cap, KNNT_T), KNNT_T, smem, s>>>(sorted, m_cap, info, g, start, k1, nbr, info_out);
 }
 
 extern "C" size_t ms_knn_workspace_bytes(int64_t m, int k1) {
@@ -336,76 +313,55 @@ extern "C" size_t ms_knn_workspace_bytes(int64_t m, int k1) {
     return ms_align((size_t)m * 4) + 3 * ms_align(ncell * 4) + ms_align((size_t)m * 16) + ms_scan_ws_bytes((int64_t)ncell) + 4096;
 }
 
-extern "C" int ms_knn(const float *points_all, int64_t m, int k1, int32_t *nbr,
-                      void *ws, size_t ws_bytes, void *stream) {
-    cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(m > 0 && k1 >= 1 && k1 <= 32, "ms_knn: need m > 0 and 1 <= k+1 <= 32 (got m=%lld, k+1=%d)", (long long)m, k1);
-    MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_knn: too many points");
-    MS_REQUIRE(ws_bytes >= ms_knn_workspace_bytes(m, k1), "ms_knn: workspace too small");
-    const int64_t ncell_max = m + 2048;
+// the cell list shared by ms_knn and ms_overlapping_pairs: extent (measured, or box4 given by the caller) -> grid on
+// the device -> counting sort of the points into `sorted` (x, y, z, index).  Nothing is read back.
+struct CellList { int32_t *start; float4 *sorted; Grid *grid; unsigned *bb; };
+static int build_cell_list(const float *points, int64_t m_cap, int64_t *info, const float *box4_host, double ppc, double h_min,
+                           void *ws, size_t ws_bytes, cudaStream_t s, CellList &cl) {
+    const int64_t ncell_max = m_cap + 2048;
     MsArena A(ws, ws_bytes);
-    int32_t *cell = A.take<int32_t>(m);
+    int32_t *cell = A.take<int32_t>(m_cap);
     int32_t *cnt = A.take<int32_t>(ncell_max), *start = A.take<int32_t>(ncell_max), *cursor = A.take<int32_t>(ncell_max);
-    float4 *sorted = A.take<float4>(m);
+    float4 *sorted = A.take<float4>(m_cap);
     void *scan_ws = A.take<char>(ms_scan_ws_bytes(ncell_max));
-    unsigned *bb = (unsigned*)A.take<unsigned>(64);
-    const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
-    MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
-    MS_CUDA(cudaMemsetAsync(bb + 16, 0, sizeof(unsigned), s));          // diagnostic: queries redone in exact tie order
-    MS_K("bbox", s); k_bbox<<<ms_sm_count() * 4, 256, 0, s>>>(points_all, m, bb);
-    unsigned hb[4];
-    MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaStreamSynchronize(s));
-    float lo[2], hi[2];
-    for (int d = 0; d < 2; d++) {
-        unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
-        u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
+    unsigned *bb = (unsigned*)A.take<unsigned>(64);          // [0..3] extent, [8..11] overlap result, [32..] Grid
+    Grid *grid = (Grid*)(bb + 32);
+    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (box4_host) b4 = make_float4(box4_host[0], box4_host[1], box4_host[2], box4_host[3]);
+    else {
+        MS_CUDA(cudaMemsetAsync(bb, 0xff, 2 * sizeof(unsigned), s));        // min x, min y (ordered uints)
+        MS_CUDA(cudaMemsetAsync(bb + 2, 0, 2 * sizeof(unsigned), s));       // max x, max y
+        MS_K("bbox", s); k_bbox<<<ms_sm_count() * 4, 256, 0, s>>>(points, m_cap, info, bb);
     }
-    double wx = (double)hi[0] - lo[0], wy = (double)hi[1] - lo[1];
-    MS_REQUIRE(wx == wx && wy == wy && wx < 1e30 && wy < 1e30, "ms_knn: non-finite coordinates");
-    if (!(wx > 0.0)) wx = 1e-6; if (!(wy > 0.0)) wy = 1e-6;
-    double ppc = 0.37 * (double)k1; if (ppc < 2.0) ppc = 2.0;
-    double h = sqrt(wx * wy * ppc / (double)m);
-    Grid g;
-    for (;;) {
-        const double nxd = floor(wx / h) + 1.0, nyd = floor(wy / h) + 1.0;
-        if (nxd * nyd <= (double)(ncell_max - 1)) { g.nx = (int)nxd; g.ny = (int)nyd; break; }
-        h *= 1.5;
-    }
-    g.lox = lo[0]; g.loy = lo[1]; g.h = h; g.inv_h = 1.0 / h;
-    const int64_t ncell = (int64_t)g.nx * g.ny;
-    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_K("cell_count", s); k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, g, cell, cnt);
-    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
-    MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points_all, m, cell, start, cursor, sorted);
-    MS_K("knn", s);
-    if (m < k1) k_knn<<<ms_blocks(m, KNN_WARPS), KNN_WARPS * 32, 0, s>>>(sorted, m, g, start, k1, nbr);   // fewer points than k+1
-    else if (k1 <= 8) knn_thread_launch<8>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    else if (k1 <= 12) knn_thread_launch<12>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    else if (k1 <= 16) knn_thread_launch<16>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    else if (k1 <= 19) knn_thread_launch<19>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    else if (k1 <= 24) knn_thread_launch<24>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    else knn_thread_launch<32>(sorted, m, g, start, k1, nbr, bb + 16, s);
-    MS_K(NULL, s);
+    MS_K("make_grid", s); k_make_grid<<<1, 1, 0, s>>>(bb, b4, box4_host != NULL, m_cap, info, ppc, h_min, ncell_max, grid);
+    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * ncell_max, s));
+    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * ncell_max, s));
+    MS_K("cell_count", s); k_cell_count<<<ms_blocks(m_cap, 256), 256, 0, s>>>(points, m_cap, info, grid, cell, cnt);
+    if (ms_exclusive_scan_i32(cnt, start, ncell_max - 1, scan_ws, s)) return 2;      // cells beyond nx*ny are empty
+    MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m_cap, 256), 256, 0, s>>>(points, m_cap, info, cell, start, cursor, sorted);
     MS_LAUNCH_CHECK();
+    cl.start = start; cl.sorted = sorted; cl.grid = grid; cl.bb = bb;
     return 0;
 }
 
-// diagnostic: number of queries of the last ms_knn call on this workspace that met an exact distance tie and
-// were redone in (distance, index) order.  Syncs the stream.
-extern "C" int ms_knn_tie_queries(const void *ws, size_t ws_bytes, int64_t m, int k1, int64_t *tie_queries, void *stream) {
+extern "C" int ms_knn(const float *points_all, int64_t m_cap, int64_t *info, int k1, int32_t *nbr,
+                      void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
-    MS_REQUIRE(ws && tie_queries && ws_bytes >= ms_knn_workspace_bytes(m, k1), "ms_knn_tie_queries: bad arguments");
-    const int64_t ncell_max = m + 2048;
-    MsArena A((void*)ws, ws_bytes);
-    A.take<int32_t>(m); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<float4>(m);
-    A.take<char>(ms_scan_ws_bytes(ncell_max));
-    const unsigned *bb = (const unsigned*)A.take<unsigned>(64);
-    unsigned h = 0;
-    MS_CUDA(cudaMemcpyAsync(&h, bb + 16, sizeof(h), cudaMemcpyDeviceToHost, s));
-    MS_CUDA(cudaStreamSynchronize(s));
-    *tie_queries = (int64_t)h;
+    MS_REQUIRE(m_cap > 0 && k1 >= 1 && k1 <= 32, "ms_knn: need m > 0 and 1 <= k+1 <= 32 (got m=%lld, k+1=%d)", (long long)m_cap, k1);
+    MS_REQUIRE(m_cap < ((int64_t)1 << 31) - 4096, "ms_knn: too many points");
+    MS_REQUIRE(ws_bytes >= ms_knn_workspace_bytes(m_cap, k1), "ms_knn: workspace too small");
+    double ppc = 0.37 * (double)k1; if (ppc < 2.0) ppc = 2.0;
+    CellList cl;
+    if (build_cell_list(points_all, m_cap, info, NULL, ppc, 0.0, ws, ws_bytes, s, cl)) return 2;
+    MS_K("knn", s);
+    if (k1 <= 8) knn_thread_launch<8>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    else if (k1 <= 12) knn_thread_launch<12>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    else if (k1 <= 16) knn_thread_launch<16>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    else if (k1 <= 19) knn_thread_launch<19>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    else if (k1 <= 24) knn_thread_launch<24>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    else knn_thread_launch<32>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
     return 0;
 }
 
@@ -416,12 +372,13 @@ extern "C" int ms_knn_tie_queries(const void *ws, size_t ws_bytes, int64_t m, in
 // 3x3 cells.  pairs (max_pairs,2) receives (i<j) index pairs in no particular order; *npairs their total
 // count (may exceed max_pairs); *min_above = smallest distance > dthreshold seen among the scanned
 // candidates (the reference's move radius, utils.py:129; +inf if none).
-__global__ void __launch_bounds__(128) k_overlap(const float4 *__restrict__ sorted, int64_t m, Grid g, const int32_t *__restrict__ start,
+__global__ void __launch_bounds__(128) k_overlap(const float4 *__restrict__ sorted, int64_t m, const Grid *__restrict__ gp, const int32_t *__restrict__ start,
                                                  double thr, int32_t *pairs, unsigned long long max_pairs,
                                                  unsigned long long *npairs, unsigned long long *min_above_bits) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const Grid g = *gp;
     double mine = 1e300;
-    if (p < m) {
+    if (p < m && g.ok) {
         const float4 q = __ldg(sorted + p);
         const int qi = __float_as_int(q.w);
         int cx, cy; cell_of(g, q.x, q.y, cx, cy);
@@ -447,100 +404,57 @@ __global__ void __launch_bounds__(128) k_overlap(const float4 *__restrict__ sort
     for (int o = 16; o > 0; o >>= 1) mine = fmin(mine, __shfl_xor_sync(0xffffffffu, mine, o));
     if ((threadIdx.x & 31) == 0 && mine < 1e300) atomicMin(min_above_bits, (unsigned long long)__double_as_longlong(mine));   // positive doubles order as integers
 }
+__global__ void k_overlap_init(unsigned long long *res) { res[0] = 0ull; res[1] = 0x7ff0000000000000ull; }
 
 extern "C" size_t ms_overlap_workspace_bytes(int64_t n) { return ms_knn_workspace_bytes(n, 19); }
 
-// box4 (host, may be NULL) = xy extent to lay the cell list over {xmin, ymin, xmax, ymax}: with it nothing is read
-// back before the launch (points outside are clamped into the border cells, which costs speed, not pairs);
+// box4 (host, may be NULL = measure the extent on the device) = xy extent to lay the cell list over
+// {xmin, ymin, xmax, ymax} (points outside are clamped into the border cells, which costs speed, not pairs);
 // result_dev (device, 2 x u64) receives {pair count, bits of the smallest distance above the threshold}.
 static int overlap_launch(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs, int64_t max_pairs,
-                          unsigned long long *result_dev, void *ws, size_t ws_bytes, cudaStream_t s);
+                          unsigned long long *result_dev, void *ws, size_t ws_bytes, cudaStream_t s, unsigned long long **res_out) {
+    MS_REQUIRE(points && m > 0 && dthreshold >= 0.0 && max_pairs >= 0 && (pairs || max_pairs == 0), "ms_overlapping_pairs: bad arguments");
+    MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_overlapping_pairs: too many points");
+    MS_REQUIRE(ws_bytes >= ms_overlap_workspace_bytes(m), "ms_overlapping_pairs: workspace too small");
+    CellList cl;
+    if (build_cell_list(points, m, NULL, box4, 2.0, dthreshold, ws, ws_bytes, s, cl)) return 2;
+    unsigned long long *res = result_dev ? result_dev : (unsigned long long*)(cl.bb + 8);   // [0] = pair count, [1] = min distance bits
+    MS_K("overlap_init", s); k_overlap_init<<<1, 1, 0, s>>>(res);
+    MS_K("overlap", s); k_overlap<<<ms_blocks(m, 128), 128, 0, s>>>(cl.sorted, m, cl.grid, cl.start, dthreshold, pairs, (unsigned long long)max_pairs, res, res + 1);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    if (res_out) *res_out = res;
+    return 0;
+}
 
 extern "C" int ms_overlapping_pairs_async(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs,
                                           int64_t max_pairs, unsigned long long *result_dev, void *ws, size_t ws_bytes, void *stream) {
     MS_REQUIRE(result_dev != NULL, "ms_overlapping_pairs_async: result_dev is required");
-    return overlap_launch(points, m, dthreshold, box4, pairs, max_pairs, result_dev, ws, ws_bytes, (cudaStream_t)stream);
+    return overlap_launch(points, m, dthreshold, box4, pairs, max_pairs, result_dev, ws, ws_bytes, (cudaStream_t)stream, NULL);
 }
 
 extern "C" int ms_overlapping_pairs(const float *points, int64_t m, double dthreshold, int32_t *pairs, int64_t max_pairs,
                                     int64_t *npairs_out, double *min_above_out, void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(npairs_out != NULL, "ms_overlapping_pairs: npairs is required");
-    const int rc = overlap_launch(points, m, dthreshold, NULL, pairs, max_pairs, NULL, ws, ws_bytes, s);
+    unsigned long long *res = NULL;
+    const int rc = overlap_launch(points, m, dthreshold, NULL, pairs, max_pairs, NULL, ws, ws_bytes, s, &res);
     if (rc) return rc;
-    MsArena A(ws, ws_bytes);
-    const int64_t ncell_max = m + 2048;
-    A.take<int32_t>(m); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<int32_t>(ncell_max); A.take<float4>(m);
-    A.take<char>(ms_scan_ws_bytes(ncell_max));
-    unsigned *bb = (unsigned*)A.take<unsigned>(64);
     unsigned long long h2[2];
-    MS_CUDA(cudaMemcpyAsync(h2, (unsigned long long*)(bb + 8), sizeof(h2), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaMemcpyAsync(h2, res, sizeof(h2), cudaMemcpyDeviceToHost, s));
     MS_CUDA(cudaStreamSynchronize(s));
     *npairs_out = (int64_t)h2[0];
     if (min_above_out) memcpy(min_above_out, &h2[1], 8);
     return 0;
 }
 
-static int overlap_launch(const float *points, int64_t m, double dthreshold, const float *box4, int32_t *pairs, int64_t max_pairs,
-                          unsigned long long *result_dev, void *ws, size_t ws_bytes, cudaStream_t s) {
-    MS_REQUIRE(points && m > 0 && dthreshold >= 0.0 && max_pairs >= 0 && (pairs || max_pairs == 0), "ms_overlapping_pairs: bad arguments");
-    MS_REQUIRE(m < ((int64_t)1 << 31) - 4096, "ms_overlapping_pairs: too many points");
-    MS_REQUIRE(ws_bytes >= ms_overlap_workspace_bytes(m), "ms_overlapping_pairs: workspace too small");
-    const int64_t ncell_max = m + 2048;
-    MsArena A(ws, ws_bytes);
-    int32_t *cell = A.take<int32_t>(m);
-    int32_t *cnt = A.take<int32_t>(ncell_max), *start = A.take<int32_t>(ncell_max), *cursor = A.take<int32_t>(ncell_max);
-    float4 *sorted = A.take<float4>(m);
-    void *scan_ws = A.take<char>(ms_scan_ws_bytes(ncell_max));
-    unsigned *bb = (unsigned*)A.take<unsigned>(64);
-    unsigned long long *res = result_dev ? result_dev : (unsigned long long*)(bb + 8);   // [0] = pair count, [1] = min distance bits
-    static const unsigned init[4] = { 0xffffffffu, 0xffffffffu, 0u, 0u };
-    static const unsigned long long rinit[2] = { 0ull, 0x7ff0000000000000ull };
-    MS_CUDA(cudaMemcpyAsync(res, rinit, sizeof(rinit), cudaMemcpyHostToDevice, s));
-    float lo[2], hi[2];
-    if (box4) { lo[0] = box4[0]; lo[1] = box4[1]; hi[0] = box4[2]; hi[1] = box4[3]; }
-    else {
-        MS_CUDA(cudaMemcpyAsync(bb, init, sizeof(init), cudaMemcpyHostToDevice, s));
-        MS_K("bbox", s); k_bbox<<<ms_sm_count() * 4, 256, 0, s>>>(points, m, bb);
-        unsigned hb[4];
-        MS_CUDA(cudaMemcpyAsync(hb, bb, sizeof(hb), cudaMemcpyDeviceToHost, s));
-        MS_CUDA(cudaStreamSynchronize(s));
-        for (int d = 0; d < 2; d++) {
-            unsigned u = hb[d]; unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&lo[d], &v, 4);
-            u = hb[2 + d]; v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; memcpy(&hi[d], &v, 4);
-        }
-    }
-    double wx = (double)hi[0] - lo[0], wy = (double)hi[1] - lo[1];
-    MS_REQUIRE(wx == wx && wy == wy && wx < 1e30 && wy < 1e30, "ms_overlapping_pairs: non-finite coordinates");
-    if (!(wx > 0.0)) wx = 1e-6; if (!(wy > 0.0)) wy = 1e-6;
-    double h = sqrt(wx * wy * 2.0 / (double)m);
-    if (h < dthreshold) h = dthreshold;
-    Grid g;
-    for (;;) {
-        const double nxd = floor(wx / h) + 1.0, nyd = floor(wy / h) + 1.0;
-        if (nxd * nyd <= (double)(ncell_max - 1)) { g.nx = (int)nxd; g.ny = (int)nyd; break; }
-        h *= 1.5;
-    }
-    g.lox = lo[0]; g.loy = lo[1]; g.h = h; g.inv_h = 1.0 / h;
-    const int64_t ncell = (int64_t)g.nx * g.ny;
-    MS_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (ncell + 1), s));
-    MS_K("cell_count", s); k_cell_count<<<ms_blocks(m, 256), 256, 0, s>>>(points, m, g, cell, cnt);
-    if (ms_exclusive_scan_i32(cnt, start, ncell, scan_ws, s)) return 2;
-    MS_K("cell_scatter", s); k_cell_scatter<<<ms_blocks(m, 256), 256, 0, s>>>(points, m, cell, start, cursor, sorted);
-    MS_K("overlap", s); k_overlap<<<ms_blocks(m, 128), 128, 0, s>>>(sorted, m, g, start, dthreshold, pairs, (unsigned long long)max_pairs, res, res + 1);
-    MS_K(NULL, s);
-    MS_LAUNCH_CHECK();
-    return 0;
-}
-
 // ------------------------------------------------------------------ stage 3: PCA normals
 // One thread per point: centroid and covariance in neighbour order, cyclic Jacobi (CGAL's internal
 // 3x3 solver when CGAL_EIGEN3_ENABLED is off, setup.py:217), smallest-eigenvalue eigenvector.
-__global__ void __launch_bounds__(128) k_pca(const float *__restrict__ pts, int64_t m, const int32_t *__restrict__ nbr, int k1,
-                                             double *__restrict__ normals) {
+__global__ void __launch_bounds__(128) k_pca(const float *__restrict__ pts, int64_t m_cap, const int64_t *__restrict__ info,
+                                             const int32_t *__restrict__ nbr, int k1, double *__restrict__ normals) {
     const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= m) return;
+    if (q >= ms_count(info, m_cap)) return;
     double c0 = 0.0, c1 = 0.0, c2 = 0.0; int cnt = 0;
     for (int j = 0; j < k1; j++) {
         const int i = __ldg(nbr + q * k1 + j); if (i < 0) continue;
@@ -593,10 +507,10 @@ __global__ void __launch_bounds__(128) k_pca(const float *__restrict__ pts, int6
     normals[3*q] = n0; normals[3*q+1] = n1; normals[3*q+2] = n2;
 }
 
-extern "C" int ms_pca_normals(const float *points_all, int64_t m, const int32_t *nbr, int k1,
+extern "C" int ms_pca_normals(const float *points_all, int64_t m_cap, const int64_t *info, const int32_t *nbr, int k1,
                               double *normals, void *stream) {
-    MS_REQUIRE(m > 0 && k1 >= 1, "ms_pca_normals: bad arguments");
-    MS_K("pca", (cudaStream_t)stream); k_pca<<<ms_blocks(m, 128), 128, 0, (cudaStream_t)stream>>>(points_all, m, nbr, k1, normals);
+    MS_REQUIRE(m_cap > 0 && k1 >= 1, "ms_pca_normals: bad arguments");
+    MS_K("pca", (cudaStream_t)stream); k_pca<<<ms_blocks(m_cap, 128), 128, 0, (cudaStream_t)stream>>>(points_all, m_cap, info, nbr, k1, normals);
     MS_K(NULL, (cudaStream_t)stream);
     MS_LAUNCH_CHECK();
     return 0;

@@ -48,16 +48,16 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
     cap = int(L.ms_pointset_capacity(V, 1))
     pts_all = torch.empty((cap, 3), dtype=torch.float32, device=dev)
     gsrc = torch.empty(cap, dtype=torch.int32, device=dev)
-    m_out = C.c_int64(0)
+    info = torch.empty(_lib.INFO_WORDS, dtype=torch.int64, device=dev)
     ws = _lib.workspace(L.ms_ghosts_workspace_bytes(V), dev)
     box = _lib.box6(np.array([b0[0], b0[1], -1.0, b1[0], b1[1], 1.0], np.float32))
     _lib.check(L.ms_ghosts(pd.data_ptr(), V, 1, box, float(blayer), pts_all.data_ptr(), gsrc.data_ptr(),
-                           C.byref(m_out), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
-    m = int(m_out.value)
+                           info.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
+    m = int(info[_lib.INFO_M].item())          # the producer is not the per-frame path: it may wait for the count
     k1 = min(int(knbrs) + 1, 32, m)
     nbr = torch.empty((m, k1), dtype=torch.int32, device=dev)
     ws = _lib.workspace(L.ms_knn_workspace_bytes(m, k1), dev)
-    _lib.check(L.ms_knn(pts_all.data_ptr(), m, k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    _lib.check(L.ms_knn(pts_all.data_ptr(), m, info.data_ptr(), k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
     fcap = 2 * m + 64
     dfaces = torch.empty((fcap, 3), dtype=torch.int32, device=dev)
     doffs = torch.empty((fcap, 3, 2), dtype=torch.int8, device=dev)

@@ -18,12 +18,46 @@ from .trimesh import TriMesh
 LOGGER = logging.getLogger(__name__)
 
 
+class PointNormalsInfo(dict):
+    """info of point_normals_device: `m` (points incl. ghost images), `n_unoriented`, `knn_ties`, `mst_rounds`.  The
+    numbers live in an 8 x int64 status block on the device (include/memsurfer_b200.h, MS_INFO_*) whose download
+    was queued behind the kernels; the first look at any key waits for it -- the chain itself never does."""
+
+    def __init__(self, pending):
+        super().__init__()
+        self._pending = pending
+
+    def _resolve(self):
+        if self._pending is not None:
+            h = self._pending.result()
+            self._pending = None
+            dict.update(self, m=int(h[_lib.INFO_M]), n_unoriented=int(h[_lib.INFO_UNORIENTED]),
+                        knn_ties=int(h[_lib.INFO_KNN_TIES]), mst_rounds=int(h[_lib.INFO_MST_ROUNDS]))
+            if int(h[_lib.INFO_ERROR]) != 0:
+                raise _lib.MemSurferCudaError('point normals: non-finite point coordinates')
+        return self
+
+    def __getitem__(self, k):
+        return dict.__getitem__(self._resolve(), k)
+
+    def get(self, k, default=None):
+        return dict.get(self._resolve(), k, default)
+
+    def __contains__(self, k):
+        return dict.__contains__(self._resolve(), k)
+
+    def __repr__(self):
+        return dict.__repr__(self._resolve())
+
+
 def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1, keep=None):
     """Device pipeline of Membrane.compute_pnormals (membrane.py:124-157).
 
     points_dev: (n,3) float32 CUDA tensor.  Returns (pnormals f32 (n,3), pnormals f64 (n,3), info)
-    with info = dict(m=#points incl. ghosts, n_unoriented=...).  If `keep` is a dict the
-    intermediate device buffers (points_all, nbr, normals_all) are stored in it for tests.
+    with info = PointNormalsInfo(m=#points incl. ghosts, n_unoriented=..., ...).  Nothing is waited for: the
+    five C-ABI calls are queued back to back on the current stream (the number of ghost images stays on the
+    device; buffers are sized by ms_pointset_capacity).  If `keep` is a dict the intermediate device buffers
+    (points_all, ghost_src, nbr, normals_all, normals_pca) are stored in it for tests (this does synchronise).
     """
     _lib.require_cuda()
     L = _lib.lib()
@@ -32,62 +66,66 @@ def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1
     n = int(points_dev.shape[0])
     k1 = int(knbrs) + 1
     cap = int(L.ms_pointset_capacity(n, int(bool(periodic))))
-    import ctypes as C
     pts_all = torch.empty((cap, 3), dtype=torch.float32, device=dev)
     gsrc = torch.empty(cap, dtype=torch.int32, device=dev)
-    m_out = C.c_int64(0)
-    ws = _lib.workspace(L.ms_ghosts_workspace_bytes(n), dev)
+    info = torch.empty(_lib.INFO_WORDS, dtype=torch.int64, device=dev)
+    ws = _lib.workspace(max(L.ms_ghosts_workspace_bytes(n), L.ms_knn_workspace_bytes(cap, k1), L.ms_orient_workspace_bytes(cap, k1)), dev)
     box = _lib.box6(np.asarray(bbox, np.float32).reshape(-1)) if periodic else None
     _lib.check(L.ms_ghosts(points_dev.data_ptr(), n, int(bool(periodic)), box, float(blayer) if periodic else 0.0,
-                           pts_all.data_ptr(), gsrc.data_ptr(), C.byref(m_out), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
-    m = int(m_out.value)
-    nbr = torch.empty((m, k1), dtype=torch.int32, device=dev)
-    ws = _lib.workspace(max(L.ms_knn_workspace_bytes(m, k1), L.ms_orient_workspace_bytes(m, k1)), dev)
-    _lib.check(L.ms_knn(pts_all.data_ptr(), m, k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
-    nrm = torch.empty((m, 3), dtype=torch.float64, device=dev)
-    _lib.check(L.ms_pca_normals(pts_all.data_ptr(), m, nbr.data_ptr(), k1, nrm.data_ptr(), st), 'ms_pca_normals')
+                           pts_all.data_ptr(), gsrc.data_ptr(), info.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_ghosts')
+    nbr = torch.empty((cap, k1), dtype=torch.int32, device=dev)
+    _lib.check(L.ms_knn(pts_all.data_ptr(), cap, info.data_ptr(), k1, nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    nrm = torch.empty((cap, 3), dtype=torch.float64, device=dev)
+    _lib.check(L.ms_pca_normals(pts_all.data_ptr(), cap, info.data_ptr(), nbr.data_ptr(), k1, nrm.data_ptr(), st), 'ms_pca_normals')
     if keep is not None:
         keep['normals_pca'] = nrm.clone()
-    bad = C.c_int64(0)
-    _lib.check(L.ms_orient_normals(pts_all.data_ptr(), m, nbr.data_ptr(), k1, nrm.data_ptr(), C.byref(bad),
+    _lib.check(L.ms_orient_normals(pts_all.data_ptr(), cap, info.data_ptr(), nbr.data_ptr(), k1, nrm.data_ptr(),
                                    ws.data_ptr(), ws.numel(), st), 'ms_orient_normals')
     o32 = torch.empty((n, 3), dtype=torch.float32, device=dev)
     o64 = torch.empty((n, 3), dtype=torch.float64, device=dev)
     _lib.check(L.ms_finish_pnormals(nrm.data_ptr(), n, int(ndir_hint), o32.data_ptr(), o64.data_ptr(),
                                     ws.data_ptr(), ws.numel(), st), 'ms_finish_pnormals')
+    pinfo = PointNormalsInfo(_lib.d2h_async(info))
     if keep is not None:
-        keep.update(points_all=pts_all[:m], ghost_src=gsrc[:m], nbr=nbr, normals_all=nrm)
-    return o32, o64, dict(m=m, n_unoriented=int(bad.value))
+        m = pinfo['m']
+        keep.update(points_all=pts_all[:m], ghost_src=gsrc[:m], nbr=nbr[:m], normals_all=nrm[:m], normals_pca=keep['normals_pca'][:m])
+    return o32, o64, pinfo
+
+
+def _info_block(m, dev):
+    return torch.tensor([int(m)] + [0] * (_lib.INFO_WORDS - 1), dtype=torch.int64, device=dev)
 
 
 def knn_device(points_dev, k1):
     """(m,k1) int32 neighbour lists of an (m,3) float32 CUDA tensor through ms_knn, plus the number of queries
     that met an exact distance tie (diagnostic).  Stage 2 of point_normals_device on its own."""
-    import ctypes as C
     L = _lib.lib()
     dev = points_dev.device
     st = _lib.stream_ptr(dev)
     m = int(points_dev.shape[0])
     nbr = torch.empty((m, int(k1)), dtype=torch.int32, device=dev)
+    info = _info_block(m, dev)
     ws = _lib.workspace(L.ms_knn_workspace_bytes(m, int(k1)), dev)
-    _lib.check(L.ms_knn(points_dev.data_ptr(), m, int(k1), nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
-    ties = C.c_int64(0)
-    _lib.check(L.ms_knn_tie_queries(ws.data_ptr(), ws.numel(), m, int(k1), C.byref(ties), st), 'ms_knn_tie_queries')
-    return nbr, int(ties.value)
+    _lib.check(L.ms_knn(points_dev.data_ptr(), m, info.data_ptr(), int(k1), nbr.data_ptr(), ws.data_ptr(), ws.numel(), st), 'ms_knn')
+    return nbr, int(info[_lib.INFO_KNN_TIES].item())
 
 
-def orient_normals_device(points_dev, nbr_dev, normals_dev):
+def orient_normals_device(points_dev, nbr_dev, normals_dev, phase_times=None):
     """MST orientation (stage 4) of given (m,3) float64 normals in place; returns the number of points that are
-    not connected to the source."""
+    not connected to the source.  phase_times: a list that receives the microseconds of every phase of the kernel."""
     import ctypes as C
     L = _lib.lib()
     dev = points_dev.device
     m, k1 = int(nbr_dev.shape[0]), int(nbr_dev.shape[1])
+    info = _info_block(m, dev)
     ws = _lib.workspace(L.ms_orient_workspace_bytes(m, k1), dev)
-    bad = C.c_int64(0)
-    _lib.check(L.ms_orient_normals(points_dev.data_ptr(), m, nbr_dev.data_ptr(), k1, normals_dev.data_ptr(), C.byref(bad),
+    _lib.check(L.ms_orient_normals(points_dev.data_ptr(), m, info.data_ptr(), nbr_dev.data_ptr(), k1, normals_dev.data_ptr(),
                                    ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)), 'ms_orient_normals')
-    return int(bad.value)
+    if phase_times is not None:
+        buf, n = (C.c_double * 64)(), C.c_int(0)
+        _lib.check(L.ms_orient_phase_times(ws.data_ptr(), ws.numel(), m, k1, buf, 64, C.byref(n), _lib.stream_ptr(dev)), 'ms_orient_phase_times')
+        phase_times.extend(buf[i] * 1e-3 for i in range(n.value))
+    return int(info[_lib.INFO_UNORIENTED].item())
 
 
 class Membrane(object):
@@ -130,7 +168,10 @@ class Membrane(object):
             self.labels = None
 
         self.device = torch.device(kwargs.get('device', 'cuda:0'))
-        self.points = _lib.pinned_copy(self.points, np.float32)
+        # float32 copy as membrane.py:79, made in page-locked memory so that the upload is a DMA.  An input that
+        # already is float32 and page-locked (`memsurfer_b200.pinned`) is used where it is: it is never written
+        # to (fit_points_to_box_xy copies first if it has to move a point).
+        self.points, self._points_shared = _lib.staged(self.points, np.float32)
         self.bbox = self.bbox.astype(np.float32)
         # the reference copies the points into its PointSet HERE (membrane.py:81), i.e. before any
         # later fit_points_to_box_xy(): normals are computed on these coordinates.  The PointSet copy
@@ -141,7 +182,8 @@ class Membrane(object):
             self._stream = _lib.next_stream(self.device)
             self._upload_and_check(kwargs.get('check_overlaps', True))
 
-        self.pnormals = None
+        self._pnormals = None            # float32 numpy once fetched
+        self._pnormals_pending = None    # its download in flight (_lib.Pending)
         self._pnormals_f64 = None
         self._pnormals_f64_dev = None
         self.spoints = None
@@ -179,6 +221,30 @@ class Membrane(object):
         return mesh
 
     @property
+    def pnormals(self):
+        """(npoints,3) float32 point normals, None before compute_pnormals (memsurfer/membrane.py:62,141).  The
+        kernels and the download are only QUEUED by Membrane.compute(); the first look at the array waits."""
+        if self._pnormals is None and self._pnormals_pending is not None:
+            self._pnormals = self._pnormals_pending.result()
+            self._pnormals_pending = None
+            self._after_pnormals()
+        return self._pnormals
+
+    @pnormals.setter
+    def pnormals(self, value):
+        self._pnormals, self._pnormals_pending = value, None
+
+    def _after_pnormals(self):
+        info = self.info.get('pnormals')
+        if info is not None and info['n_unoriented'] > 0:
+            # the reference silently returns a permuted array here (PointSet.cpp:176-193)
+            LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
+                           "Some normals may be incorrectly oriented!")
+        self.check_overlaps()
+        if self._pnormals.shape != (self.npoints, 3):
+            raise ValueError(f'PointSet computed incorrect normals (got {self._pnormals.size} values')
+
+    @property
     def pnormals_f64(self):
         """fp64 twin of `pnormals` (not part of the reference API; fetched from the device on first use)."""
         if self._pnormals_f64 is None and self._pnormals_f64_dev is not None:
@@ -194,6 +260,11 @@ class Membrane(object):
         if self._pset_event is not None:
             self._pset_event.synchronize()         # the PointSet upload reads self.points
         boxw = self.bbox[1, :] - self.bbox[0, :]
+        xy = self.points[:, :2]
+        if not ((xy < self.bbox[0, :2]).any() or (xy > self.bbox[1, :2]).any()):
+            return 0
+        if self._points_shared:            # the caller's own page-locked array: leave it as it is
+            self.points, self._points_shared = self.points.copy(), False
         for d in range(2):
             lo = self.points[:, d] < self.bbox[0, d]
             self.points[lo, d] += boxw[d]
@@ -204,33 +275,34 @@ class Membrane(object):
 
     # ---------------------------------------------------------------------- point normals (GPU)
     @_lib.home_stream
-    def compute_pnormals(self, knbrs=18, ndir_hint=+1):
-        """(npoints,3) float32 normals by (k+1)-NN PCA + MST orientation (membrane.py:124-157)."""
-        if self.pnormals is not None:
-            return self.pnormals
+    def _queue_pnormals(self, knbrs=18, ndir_hint=+1):
+        """Queue ghosts -> k-NN -> PCA -> MST orientation -> float32 hand-off and the download of the result on
+        this membrane's stream; returns at once."""
+        if self._pnormals is not None or self._pnormals_pending is not None:
+            return
         _lib.require_cuda()
-        pts = self._pset_dev
-        o32, o64, info = point_normals_device(pts, self.bbox, self.periodic,
+        o32, o64, info = point_normals_device(self._pset_dev, self.bbox, self.periodic,
                                               getattr(self, 'blayer', 0.2), knbrs, ndir_hint)
         self.info['pnormals'] = info
-        if info['n_unoriented'] > 0:
-            # the reference silently returns a permuted array here (PointSet.cpp:176-193)
-            LOGGER.warning(f"PointSet::need_normals failed for {info['n_unoriented']} points: "
-                           "Some normals may be incorrectly oriented!")
-        self.pnormals = _lib.d2h(o32)
-        self.check_overlaps()
+        self._pnormals_pending = _lib.d2h_async(o32)
         self._pnormals_f64_dev, self._pnormals_f64 = o64, None      # fp64 twin stays in HBM until asked for
-        if self.pnormals.shape != (self.npoints, 3):
-            raise ValueError(f'PointSet computed incorrect normals (got {self.pnormals.size} values')
-        return self.pnormals
+
+    def compute_pnormals(self, knbrs=18, ndir_hint=+1, wait=True):
+        """(npoints,3) float32 normals by (k+1)-NN PCA + MST orientation (membrane.py:124-157).  wait=False (not in
+        the reference) only queues the kernels and the download and returns None; `self.pnormals` waits when read."""
+        self._queue_pnormals(knbrs, ndir_hint)
+        return self.pnormals if wait else None
 
     # ---------------------------------------------------------------------- surface producer (host)
     def compute_approx_surface(self, exactness_level=10):
         """Reference: screened Poisson reconstruction via pypoisson (membrane.py:160-183), a host
         producer that is unavailable in this image.  Kept as an explicit no-op stage: the point
         normals it would consume are computed, the smooth surface falls back to the points."""
-        self.compute_pnormals()
-        self.surf_poisson = None
+        self._queue_pnormals()
+        if self.surf_poisson is None:
+            LOGGER.warning('compute_approx_surface: screened Poisson reconstruction (pypoisson) is a HOST producer that is '
+                           'not available here; assign a TriMesh to Membrane.surf_poisson (or use set_membrane_surface) '
+                           'to get a smoothed surface -- otherwise memb_smooth is built on the raw points')
 
     @_lib.home_stream
     def set_membrane_surface(self, spoints, ppoints, planar_bbox):
@@ -242,11 +314,22 @@ class Membrane(object):
 
     @_lib.home_stream
     def compute_membrane_surface(self):
-        """Stand-in for membrane.py:186-234 without Poisson/CGAL: spoints = points, ppoints = their
-        (x,y); planar bbox = the periodic box.  Everything after that follows the reference."""
-        self.spoints = self.points.copy()
-        self.ppoints = self.points[:, :2].copy()
-        self._planar_bbox = (self.bbox[0, :2].copy(), self.bbox[1, :2].copy())
+        """memsurfer/membrane.py:186-234.  With a smoothing surface in `self.surf_poisson` (a TriMesh: the output of a
+        Poisson reconstruction, assigned by the caller -- pypoisson itself is a host producer that is not in this
+        image) the reference flow runs as written: parameterize it, project the points on it and on its plane
+        (closest-point kernel), planar bbox = the parameterisation's.  Without one the points are their own
+        smooth surface: spoints = points, ppoints = their (x, y), planar bbox = the periodic box (logged)."""
+        if self.surf_poisson is not None:
+            self.surf_poisson.parameterize()
+            self.spoints, self.ppoints = self.surf_poisson.project_on_surface_and_plane(self.points)
+            bb0, bb1 = self.surf_poisson.parameterization_bbox()
+            self._planar_bbox = (np.asarray(bb0, np.float32), np.asarray(bb1, np.float32))
+        else:
+            LOGGER.warning('compute_membrane_surface: no smoothing surface (Membrane.surf_poisson is None): '
+                           'memb_smooth is built on the raw points and equals memb_exact')
+            self.spoints = self.points.copy()
+            self.ppoints = self.points[:, :2].copy()
+            self._planar_bbox = (self.bbox[0, :2].copy(), self.bbox[1, :2].copy())
         # membrane.py:199-200 -- separate coincident projections before triangulating
         from .utils import test_overlapping_points
         test_overlapping_points(self.spoints, fix=True, device=self.device)
@@ -377,7 +460,7 @@ class Membrane(object):
         knbrs = 18
         m = Membrane(positions, labels=labels, periodic=periodic, bbox=bbox)
         m.fit_points_to_box_xy()
-        m.compute_pnormals(knbrs)
+        m._queue_pnormals(knbrs)            # compute_pnormals without waiting for the result (pnormals is lazy)
         m.compute_approx_surface()
         m.compute_membrane_surface()
         return m

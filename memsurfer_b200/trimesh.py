@@ -57,7 +57,7 @@ class TriMesh(object):
         vertices = np.asarray(vertices)
         if vertices.ndim != 2 or vertices.shape[1] not in [2, 3]:
             raise ValueError(f'TriMesh needs 2D or 3D vertices: got {vertices.shape}')
-        self.vertices = _lib.pinned_copy(vertices, np.float32)
+        self.vertices, _ = _lib.staged(vertices, np.float32)       # page-locked float32 inputs are used where they are
 
         if 'faces' in kwargs and kwargs['faces'] is not None:
             faces = np.asarray(kwargs['faces'])
@@ -118,11 +118,11 @@ class TriMesh(object):
 
     def set_periodic_triangulation(self, faces, periodic_faces, trimmed_faces, duplicated_vidxs, duplicated_verts):
         """Inject the arrays `_fetch_faces` (trimesh.py:421-436) would fetch from the C++ object."""
-        self.faces = _lib.pinned_copy(np.asarray(faces).reshape(-1, 3), np.uint32)
+        self.faces, _ = _lib.staged(np.asarray(faces).reshape(-1, 3), np.uint32)
         self._periodic_faces = np.ascontiguousarray(periodic_faces, dtype=np.uint32).reshape(-1, 3)
-        self._trimmed_faces = _lib.pinned_copy(np.asarray(trimmed_faces).reshape(-1, 3), np.uint32)
+        self._trimmed_faces, _ = _lib.staged(np.asarray(trimmed_faces).reshape(-1, 3), np.uint32)
         self._duplicated_vidxs = np.ascontiguousarray(duplicated_vidxs, dtype=np.uint32)
-        self._duplicated_verts = _lib.pinned_copy(np.asarray(duplicated_verts).reshape(-1, self.vertices.shape[1]), np.float32)
+        self._duplicated_verts, _ = _lib.staged(np.asarray(duplicated_verts).reshape(-1, self.vertices.shape[1]), np.float32)
         self._invalidate()
 
     def _retrim(self):
