@@ -7,20 +7,25 @@ One step = one frame: for each of the 2 leaflets of a s
 undulating bilayer (BASELINE.json configs[2]: 1M lipids, ~500k points per leaflet)
 compute_pnormals(k=18), compute_properties (vertex normals, point areas, mean + Gaussian
 curvature) and compute_densities(types=[2], sigmas=[10,20,30,40], get_nlipdis=True) for 'all' and
-each of the 3 lipid types.  The host mesh producer (Delaunay stand-in) runs once in set-up and is
-not part of the timed region (it stays on the host by design).
+each of the 3 lipid types.  The mesh producer (periodic Delaunay + trim) runs once in set-up and is
+not part of the timed region; it is reported beside it (`mesh_producer`).
 
  * `value`: frames/s with the inputs resident in HBM (C-ABI calls on device pointers).
- * `e2e`:   the same frame through the drop-in Membrane/TriMesh API from HOST arrays: host->device
-            copies of points/mesh/ids and device->host copies of every result inside the timing.
- * `roofline`: the dominant kernel (KDE pair-sum) against the fp64-FMA peak measured in the same
-            process by a DFMA probe; `roofline_geometry`: the fused mesh-properties kernel against
-            the measured HBM copy bandwidth (MEASURED_PEAKS.json).
+ * `e2e`:   the same frame through the drop-in Membrane/TriMesh API from page-locked HOST arrays:
+            host->device copies of points/mesh/labels and device->host copies of every result inside
+            the timing.
+ * `roofline`: the dominant kernel (KDE pair-sum) against the fp64 issue peak measured in the same
+            process by a DFMA probe; `roofline_geometry` (mesh properties), `roofline_knn` and
+            `roofline_orient` against the measured HBM copy bandwidth (MEASURED_PEAKS.json).
+ * `parity`: max errors of this run's own outputs against the CPU oracle (outside the timed region).
  * `cpu_baseline`: the reference's own C++ (oracle/_ref, single-threaded as shipped) for vertex
             normals, point areas and KDE, the fp64 restatement for the CGAL/VTK parts, timed on
             this box's host cores on a bounded sample (see `sample`).
+ * `allpairs`: the same frame with the reference's literal all-pairs KDE sum (like-for-like with the CPU arm).
+ * `trajectory`: BASELINE configs[3] (100k-lipid, 8-type frames sharded over the ranks; strong scaling).
 N > 1: every rank runs the same pipeline on its own frame (weak scaling, frames sharded across
-GPUs); the only collective is the all_gather of the per-frame summary records.
+GPUs); the only collective is the all_gather of the per-frame summary records.  Ranks pin
+themselves to their own host cores before any thread pool starts.
 """
 import argparse
 import json
@@ -30,8 +35,6 @@ import sys
 import threading
 import time
 
-import numpy as np
-
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -39,21 +42,13 @@ if ROOT not in sys.path:
 SIGMAS = [10.0, 20.0, 30.0, 40.0]
 FRACTIONS = [0.4, 0.3, 0.3]
 METRIC = "membrane_frames_per_sec"
-# fp64 FLOP per evaluated 2-D periodic pair / algorithmic bytes per vertex
+# fp64 FLOP per evaluated 2-D periodic pair / algorithmic bytes per unit
 FLOP_PER_PAIR_2D = 32.0
-FP64_INSTR_PER_PAIR = {"kde_pairs": 14, "kde_cells": 10, "kde_groups": 10}
+FP64_INSTR_PER_PAIR = {"kde_pairs": 14, "kde_groups": 10}
 GEOM_BYTES_PER_VERTEX = 84.0
-
-
-def _load_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures."""
-    try:
-        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-    except Exception:
-        return {}
-
-
-TRAFFIC = _load_traffic()
+KNN_BYTES_PER_POINT = (36.0, 112.0)             # without / with the neighbour indices written out
+ORIENT_BYTES_PER_POINT = lambda k1: 4.0 * k1 + 24.0 + 24.0      # neighbour row + normal in + normal out
+MESH_KERNELS = ("face_records", "edge_mean", "vertex_gather", "pad_verts", "corner_terms", "vertex_gather8")
 
 
 def parse_args():
@@ -68,28 +63,89 @@ def parse_args():
                          "0 = all pairs, the reference's literal sum)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the all-pairs, trajectory, type-3 and producer side measurements")
+    ap.add_argument("--trajectory-frames", type=int, default=512, help="total frames of the configs[3] measurement (all ranks)")
+    ap.add_argument("--no-pin", action="store_true", help="do not bind the rank to its own host cores")
     return ap.parse_args()
 
 
+# ---------------------------------------------------------------------------------------------- host placement
+def pin_rank(local_rank, local_world):
+    """Bind this process to its own slice of the host cores (before numpy/torch start thread pools).  Returns
+    (cores, numa node of the first core)."""
+    try:
+        avail = sorted(os.sched_getaffinity(0))
+        per = max(1, len(avail) // max(1, local_world))
+        mine = avail[local_rank * per:(local_rank + 1) * per] or avail
+        os.sched_setaffinity(0, mine)
+    except Exception:
+        return None, None
+    node = None
+    try:
+        base = "/sys/devices/system/node"
+        for d in sorted(os.listdir(base)):
+            if not d.startswith("node"):
+                continue
+            cpus = set()
+            for part in open(os.path.join(base, d, "cpulist")).read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+            if mine[0] in cpus:
+                node = int(d[4:])
+                break
+    except Exception:
+        pass
+    return mine, node
+
+
 # ---------------------------------------------------------------------------------------------- inputs
-def make_frame_inputs(lipids, frame):
-    """Two leaflets of frame `frame` + their host-produced periodic meshes."""
-    from memsurfer_b200 import synth, TriMesh
-    leaflets = []
-    for li, z0 in enumerate((20.0, -20.0)):
-        pts, labels, bbox = synth.make_leaflet(lipids // 2, seed=1234 + li, z0=z0, ntypes=3, fractions=FRACTIONS,
-                                               phase_shift=0.05 * frame)
+def make_leaflet_inputs(npoints, seed, z0, ntypes, fractions, phase_shift, device):
+    """One leaflet + its periodic mesh in the reference layout.  device=None: host producer (scipy stand-in for
+    CGAL); else the GPU periodic Delaunay (TriMesh.compute_delaunay) -- either way outside the timed frame."""
+    import numpy as np
+    from memsurfer_b200 import synth
+    pts, labels, bbox = synth.make_leaflet(npoints, seed=seed, z0=z0, ntypes=ntypes, fractions=fractions, phase_shift=phase_shift)
+    lo, hi = pts.min(axis=0), pts.max(axis=0)
+    if device is None:
         dfaces, doffs = synth.periodic_delaunay(pts[:, :2], bbox[0], bbox[1])
-        tri = synth.trim_periodic(pts, dfaces, doffs, pts.min(axis=0), pts.max(axis=0))
-        leaflets.append(dict(points=pts, labels=labels, bbox=bbox, tri=tri, lo=pts.min(axis=0), hi=pts.max(axis=0)))
-    return leaflets
+        tri = synth.trim_periodic(pts, dfaces, doffs, lo, hi)
+    else:
+        from memsurfer_b200 import TriMesh
+        planar = TriMesh(pts[:, :2], periodic=True, label="memb_planar", device=device)
+        planar.set_bbox(bbox[0, :2], bbox[1, :2])
+        planar.compute_delaunay()
+        m3 = TriMesh(pts, periodic=True, label="memb_smooth", device=device)
+        m3.set_bbox(lo, hi)                                   # the producer's bbox (spoints min/max, membrane.py:214-217)
+        m3.copy_triangulation(planar)
+        tri = dict(faces=m3.faces, periodic_faces=m3._periodic_faces, trimmed_faces=m3._trimmed_faces,
+                   duplicated_vidxs=m3._duplicated_vidxs, duplicated_verts=m3._duplicated_verts)
+    return dict(points=pts, labels=labels, bbox=bbox, tri=tri, lo=lo, hi=hi)
+
+
+def make_frame_inputs(lipids, frame, device=None, ntypes=3, fractions=FRACTIONS):
+    """Two leaflets of frame `frame` + their periodic meshes."""
+    return [make_leaflet_inputs(lipids // 2, 1234 + li, z0, ntypes, fractions, 0.05 * frame, device)
+            for li, z0 in enumerate((20.0, -20.0))]
+
+
+def pin_inputs(lf):
+    """The frame's input arrays in page-locked host memory (the e2e arm uploads from there by DMA)."""
+    import numpy as np
+    from memsurfer_b200 import pinned
+    out = dict(lf)
+    out["points"] = pinned(lf["points"], np.float32)
+    t = lf["tri"]
+    out["tri"] = dict(faces=pinned(t["faces"], np.uint32), periodic_faces=t["periodic_faces"],
+                      trimmed_faces=pinned(t["trimmed_faces"], np.uint32), duplicated_vidxs=t["duplicated_vidxs"],
+                      duplicated_verts=pinned(t["duplicated_verts"], np.float32))
+    return out
 
 
 def new_mesh(lf, device):
     from memsurfer_b200 import TriMesh
     t = lf["tri"]
     mesh = TriMesh(lf["points"], periodic=True, label="memb_smooth", device=device)
-    mesh.set_bbox(lf["lo"], lf["hi"])          # the producer's bbox (spoints min/max, membrane.py:214-217)
+    mesh.set_bbox(lf["lo"], lf["hi"])
     mesh.set_periodic_triangulation(t["faces"], t["periodic_faces"], t["trimmed_faces"],
                                     t["duplicated_vidxs"], t["duplicated_verts"])
     return mesh
@@ -118,6 +174,7 @@ class ClockSampler(object):
             self.lines.append(ln.strip())
 
     def stop(self):
+        import numpy as np
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -143,13 +200,15 @@ class ClockSampler(object):
 
 
 # ---------------------------------------------------------------------------------------------- CPU baseline
-def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False):
-    """Reference CPU path on a bounded sample of the frame workload -> (frames/s, details)."""
+def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False, keep=None):
+    """Reference CPU path on a bounded sample of the frame workload -> (frames/s, details).  keep: dict that
+    receives the oracle's full-size outputs (for the parity key)."""
+    import numpy as np
     from oracle import oracle as O
     import ctypes
     try:
         gomp = ctypes.CDLL("libgomp.so.1")
-        ncores = os.cpu_count() or 1
+        ncores = len(os.sched_getaffinity(0)) or 1
         gomp.omp_set_num_threads(ncores if all_threads else 1)
     except OSError:
         ncores = 1
@@ -159,7 +218,7 @@ def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False):
     faces = np.ascontiguousarray(np.concatenate([tri["faces"], tri["trimmed_faces"]]), np.uint32)
     R = O.ref()
     t = {}
-    t0 = time.perf_counter(); O.point_normals(pts, bbox, 0.2, 18, +1); t["pnormals_port"] = time.perf_counter() - t0
+    t0 = time.perf_counter(); pn = O.point_normals(pts, bbox, 0.2, 18, +1); t["pnormals_port"] = time.perf_counter() - t0
     if R is not None:
         t0 = time.perf_counter(); O.ref_need_normals(verts, faces); O.ref_need_pointareas(verts, faces)
         t["normals_areas_reference"] = time.perf_counter() - t0
@@ -168,7 +227,9 @@ def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False):
         t["normals_areas_port"] = time.perf_counter() - t0
     bb = np.concatenate([pts.min(0), pts.max(0)]).astype(np.float32)
     xw, yw = float(np.float32(0.5) * (bb[3] - bb[0])), float(np.float32(0.5) * (bb[4] - bb[1]))
-    t0 = time.perf_counter(); O.curvatures(verts, faces, (xw, yw)); t["curvatures_port"] = time.perf_counter() - t0
+    t0 = time.perf_counter(); H, K = O.curvatures(verts, faces, (xw, yw)); t["curvatures_port"] = time.perf_counter() - t0
+    if keep is not None:
+        keep.update(pnormals=pn, H=H[:V], K=K[:V])
     # KDE: the reference evaluates all V x n_ids pairs; sample = a compact patch of the same leaflet
     ns = int(min(kde_sample_verts, V))
     side = int(round(np.sqrt(V)))
@@ -187,11 +248,14 @@ def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False):
     pairs_per_s = ns * ns / t["kde_sample"]
     nl = [int((labels == l).sum()) for l in np.unique(labels)]
     pairs_leaflet = len(SIGMAS) * (V * V + sum(V * n for n in nl))
-    t_leaflet = t["pnormals_port"] + t.get("normals_areas_reference", t.get("normals_areas_port", 0.0)) \
-        + t["curvatures_port"] + pairs_leaflet / pairs_per_s
+    t_nokde = t["pnormals_port"] + t.get("normals_areas_reference", t.get("normals_areas_port", 0.0)) + t["curvatures_port"]
+    t_leaflet = t_nokde + pairs_leaflet / pairs_per_s
     fps = 1.0 / (2.0 * t_leaflet)
     detail = {"seconds": {k: round(v, 4) for k, v in t.items()}, "kde_pairs_per_s": pairs_per_s,
-              "kde_pairs_per_leaflet": pairs_leaflet, "extrapolated_frame_seconds": 2.0 * t_leaflet}
+              "kde_pairs_per_leaflet": pairs_leaflet, "extrapolated_frame_seconds": 2.0 * t_leaflet,
+              "measured_non_kde_seconds_per_frame": 2.0 * t_nokde,
+              "note": "the KDE term (99.9 % of the frame) is EXTRAPOLATED linearly in pairs from the patch; the survey host "
+                      "measured 5.3e7 pairs/s/core for the same code (BASELINE.md section 2) -- different CPU"}
     sample = (f"one leaflet (V={V}): point normals [fp64 port of CGAL pca+mst], vertex normals + point areas "
               f"[{'reference C++' if R is not None else 'port'}], curvatures [fp64 port of vtkCurvatures] at full size; "
               f"KDE [{kind}] on a {ns}-vertex patch, type 2, sigma 20, all pairs ({ns * ns:.3g} pairs), extrapolated "
@@ -201,6 +265,7 @@ def cpu_reference_baseline(lf, kde_sample_verts=16384, all_threads=False):
 
 # ---------------------------------------------------------------------------------------------- reference arm
 def run_reference_arm(args, rank):
+    import numpy as np
     if rank != 0:
         return
     leaflets = make_frame_inputs(args.lipids, 0)[:1]
@@ -212,10 +277,13 @@ def run_reference_arm(args, rank):
             vals.append(fps)
     v = float(np.mean(vals))
     V = leaflets[0]["points"].shape[0]
+    cfg = workload_config(args, V)
+    cfg["kde"] = "all pairs (the reference's literal sum), EXTRAPOLATED from a 12 288-vertex patch"
+    cfg["mesh_producer"] = "host (scipy Delaunay stand-in for CGAL), untimed"
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (reference) / f64 (port)", "data": "synthetic",
-            "config": workload_config(args, V),
+            "config": cfg,
             "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample,
                              "detail": detail},
             "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -230,7 +298,7 @@ def workload_config(args, V):
             "kde": "all pairs" if args.kde_cutoff <= 0 else f"cut-off {args.kde_cutoff} sigma (cell list)",
             "l2": "flushed between steps (512 MiB device write)",
             "parallelism": f"frames sharded over {args.gpus} GPU(s), 1 frame per rank per step",
-            "mesh_producer": "host (scipy Delaunay stand-in for CGAL), untimed"}
+            "mesh_producer": "GPU periodic Delaunay + trim (TriMesh.compute_delaunay), untimed"}
 
 
 # ---------------------------------------------------------------------------------------------- our arm
@@ -239,10 +307,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
     if args.impl == "reference":
         run_reference_arm(args, rank)
         return
+    cores, numa = (None, None) if args.no_pin else pin_rank(local_rank, local_world)
 
+    import numpy as np
     import torch
     import torch.distributed as dist
     from memsurfer_b200 import _lib, Membrane, TriMesh
@@ -254,6 +325,7 @@ def main():
         dist.init_process_group("nccl", device_id=device)
     L = _lib.lib()
     Membrane.KDE_CUTOFF_SIGMAS = args.kde_cutoff
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
 
     def barrier():
         torch.cuda.synchronize()
@@ -261,19 +333,46 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def gather_floats(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device=device)
+        if world == 1:
+            return [float(x)]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
+
     # frame `rank` of the trajectory: every rank owns one frame per step (weak scaling)
-    leaflets = make_frame_inputs(args.lipids, rank)
+    t_setup = time.perf_counter()
+    leaflets = [pin_inputs(lf) for lf in make_frame_inputs(args.lipids, rank, device=device)]
+    t_setup = time.perf_counter() - t_setup
     V = leaflets[0]["points"].shape[0]
     frames = [LeafletFrame(lf["points"], lf["labels"], lf["bbox"], new_mesh(lf, device), device=device) for lf in leaflets]
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
 
-    def step_device():
+    def step_local(cutoff=None):
         recs = []
         for fr in frames:
-            fr.run(SIGMAS, 18, args.kde_cutoff)
+            fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
             recs.append(fr.summary())
-        rec = torch.stack(recs)
+        return torch.stack(recs)
+
+    def step_device():
+        rec = step_local()
         return gather_summaries(rec) if world > 1 else rec.unsqueeze(0)
+
+    def timed_local(fn, nwarm, nsteps):
+        """This rank only (no collective inside): side measurements of rank 0."""
+        for _ in range(nwarm):
+            fn()
+        total_ms = 0.0
+        for _ in range(nsteps):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            total_ms += e0.elapsed_time(e1)
+        return total_ms
 
     def timed(fn, nwarm, nsteps, profile=False):
         for _ in range(nwarm):
@@ -294,10 +393,8 @@ def main():
         prof = _lib.profile_report() if profile else {}
         L.ms_profile_enable(0)
         barrier()
-        t = torch.tensor([total_ms], dtype=torch.float64, device=device)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), launches, prof
+        per_rank = gather_floats(total_ms)
+        return max(per_rank), launches, prof, per_rank
 
     clocks = ClockSampler(local_rank)
     if rank == 0:
@@ -315,30 +412,32 @@ def main():
             break
         step_device()
         torch.cuda.synchronize()
-    total_ms, launches, _ = timed(step_device, args.warmup, args.steps, profile=False)
+    total_ms, launches, _, per_rank_ms = timed(step_device, args.warmup, args.steps, profile=False)
     clk = clocks.stop() if rank == 0 else None
     ms_per_step = total_ms / args.steps
     value = world * 1e3 / ms_per_step
-    # second, shorter pass with an event around every kernel launch: the per-kernel times behind `roofline`
+    # second, shorter pass with an event around every kernel launch: the per-kernel times behind the rooflines
     psteps = max(1, min(args.steps, 5))
-    ptotal_ms, _, prof = timed(step_device, 1, psteps, profile=True)
+    ptotal_ms, _, prof, _ = timed(step_device, 1, psteps, profile=True)
+    pinfo = [dict(m=fr.info['m'], cands=fr.info['knn_candidates'], rounds=fr.info['mst_rounds']) for fr in frames]
 
-    # ---- end to end through the drop-in API, from host arrays
-    e2e = None
+    # ---- end to end through the drop-in API, from page-locked host arrays
+    e2e, per_rank_e2e = None, None
     if not args.no_e2e:
         bytes_io = {"h2d": 0, "d2h": 0}
 
         def step_e2e():
             # one frame in the order of the reference's own driver (examples/ex_3lipid.py:165-175): build BOTH
-            # membranes from host arrays (Membrane.compute: point normals + surface; the surface is the host
-            # producer's output, injected), then properties and compute_densities([top, bottom], ...) for 'all'
-            # and every lipid type; finally EVERY result is read back as numpy (downloads inside the timing)
+            # membranes from host arrays (Membrane.compute: point normals + surface; the surface is the producer's
+            # output, injected), then properties and compute_densities([top, bottom], ...) for 'all' and every
+            # lipid type; finally EVERY result is read back as numpy (downloads inside the timing)
             h2d = d2h = 0
             ms = []
             for lf in leaflets:
                 m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=device)
-                pn = m.compute_pnormals(18)
-                h2d += m._pset_nbytes; d2h += pn.nbytes
+                m.compute_pnormals(18, wait=False)              # queued, like Membrane.compute() does
+                m.fit_points_to_box_xy()                        # membrane.py:305 (nothing to move here; the check is host work)
+                h2d += m._pset_nbytes
                 m.memb_smooth = new_mesh(lf, device)
                 ms.append(m)
             for m, lf in zip(ms, leaflets):
@@ -350,6 +449,7 @@ def main():
             recs = []
             for m in ms:
                 mesh = m.memb_smooth
+                d2h += m.pnormals.nbytes
                 d2h += sum(mesh.attributes[k].nbytes for k in ('pnormal', 'parea', 'mean_curv', 'gaus_curv'))
                 d2h += sum(v.nbytes for v in m.attributes.values())
                 recs.append([float(mesh.attributes['parea'].sum()), float(mesh.attributes['mean_curv'].mean())])
@@ -357,11 +457,20 @@ def main():
             return recs
 
         esteps = max(1, min(args.steps, 10))
-        e2e_ms, _, _ = timed(step_e2e, 2, esteps)
+        e2e_ms, _, _, per_rank_e2e = timed(step_e2e, 2, esteps)
         e2e_ms /= esteps
+        per_rank_e2e = [x / esteps for x in per_rank_e2e]
         e2e = {"value": world * 1e3 / e2e_ms, "unit": "frames/s", "ms_per_step": e2e_ms,
                "h2d_bytes_per_step": bytes_io["h2d"], "d2h_bytes_per_step": bytes_io["d2h"],
-               "api": "memsurfer_b200.Membrane / TriMesh (host numpy in, numpy out)"}
+               "api": "memsurfer_b200.Membrane / TriMesh (page-locked host numpy in, numpy out)"}
+
+    # ---- side measurements (every rank takes part in the trajectory; the rest is rank 0 only)
+    extras = {}
+    if not args.no_extras:
+        extras["trajectory"] = measure_trajectory(args, rank, world, device, barrier, gather_floats)
+    rank_cores = gather_floats(-1 if cores is None else cores[0])
+    rank_ncores = gather_floats(0 if cores is None else len(cores))
+    rank_numa = gather_floats(-1 if numa is None else numa)
 
     if rank != 0:
         if world > 1:
@@ -370,7 +479,7 @@ def main():
 
     # ---- rooflines (rank 0): DFMA probe for the fp64 peak, measured HBM peak from MEASURED_PEAKS.json
     import ctypes
-    probe = torch.empty(148 * 8 * 256, dtype=torch.float64, device=device)
+    probe = torch.empty(sms * 8 * 256, dtype=torch.float64, device=device)
     flop = ctypes.c_double(0)
     st = _lib.stream_ptr(device)
     best = 0.0
@@ -384,23 +493,28 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     pairs_allpairs_equiv = sum(fr.pairs_per_run(SIGMAS) for fr in frames)
     pairs_step = sum(fr.evaluated_pairs(SIGMAS, cutoff_sigmas=args.kde_cutoff) for fr in frames)
-    kname = max(("kde_groups", "kde_cells", "kde_pairs"), key=lambda k: prof.get(k, {"ms": 0.0})["ms"])
+    kname = max(("kde_groups", "kde_pairs"), key=lambda k: prof.get(k, {"ms": 0.0})["ms"])
     kp = prof.get(kname, {"launches": 0, "ms": 0.0})
     roof = None
     if kp["launches"]:
-        # fp64-pipe instructions per pair, counted in the SASS of the 2-D kernels (cuobjdump):
-        # k_kde_pairs periodic 7 DADD + 4 DFMA + 2 DSETP + 1 DMUL = 14; k_kde_cells / k_kde_groups 5 DADD + 4 DFMA + 1 DMUL = 10
+        # fp64-pipe instructions per pair, counted in the SASS of the 2-D kernels (profiles/*sass*):
+        # k_kde_pairs periodic 7 DADD + 4 DFMA + 2 DSETP + 1 DMUL = 14; k_kde_groups 5 DADD + 4 DFMA + 1 DMUL = 10
         instr = FP64_INSTR_PER_PAIR[kname]
         pairs_per_launch = pairs_step * psteps / kp["launches"]
         avg_ms = kp["ms"] / kp["launches"]
         pps = pairs_per_launch / (avg_ms * 1e-3)
         ach = pps * instr * 2.0 / 1e12
         roof = {"kernel": "k_" + kname, "bound": "fp64_fma", "achieved": ach, "peak": best, "unit": "TFLOP/s",
-                "frac": ach / best if best > 0 else None, "traffic": TRAFFIC.get(kname),
+                "frac": ach / best if best > 0 else None, "traffic": traffic.get(kname),
                 "definition": "evaluated pairs/s x fp64-pipe instructions per pair x 2 (every DADD/DMUL/DSETP/DFMA holds one "
                               "FMA slot of the fp64 pipe) / DFMA-probe peak",
                 "peak_source": "ms_dfma_probe in this process (no fp64 figure in MEASURED_PEAKS.json)",
@@ -409,30 +523,80 @@ def main():
                 "allpairs_equivalent_pairs_per_s": pairs_allpairs_equiv * psteps / (kp["ms"] * 1e-3),
                 "tflops_at_32_flop_per_pair_convention": pps * FLOP_PER_PAIR_2D / 1e12,
                 "share_of_step": kp["ms"] / ptotal_ms}
-    mesh_kernels = ("face_records", "edge_mean", "vertex_gather")
-    mp_ms = sum(prof.get(k, {"ms": 0.0})["ms"] for k in mesh_kernels)
-    mp_n = prof.get("vertex_gather", {"launches": 0})["launches"]
+    mp_ms = sum(prof.get(k, {"ms": 0.0})["ms"] for k in MESH_KERNELS)
+    mp_n = max([prof.get(k, {"launches": 0})["launches"] for k in MESH_KERNELS] + [0])
     roof_g = None
     if mp_n:
         avg_ms = mp_ms / mp_n
         ach = V * GEOM_BYTES_PER_VERTEX / (avg_ms * 1e-3) / 1e9
-        roof_g = {"kernel": "ms_mesh_properties = k_face_records + k_edge_mean + k_vertex_gather", "bound": "hbm",
+        roof_g = {"kernel": "ms_mesh_properties = " + " + ".join("k_" + k for k in MESH_KERNELS if k in prof), "bound": "hbm",
                   "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                  "traffic": TRAFFIC.get("mesh_properties"), "peak_source": hbm_src,
+                  "traffic": traffic.get("mesh_properties"), "peak_source": hbm_src,
                   "bytes_per_vertex": GEOM_BYTES_PER_VERTEX, "avg_ms_per_mesh": avg_ms, "meshes": mp_n,
                   "share_of_step": mp_ms / ptotal_ms,
-                  "note": "algorithmic bytes per SURVEY 8(d); the three passes are bound by fp64 sqrt/div/atan2 "
-                          "latency and L2 gathers, not by HBM (DESIGN.md 4.2)"}
+                  "note": "algorithmic bytes per SURVEY 8(d); the passes are bound by the fp64 pipe (sqrt/div/atan2, "
+                          "~1 250 fp64 instructions per face) and L2 gathers, not by HBM (DESIGN.md 4.2)"}
+
+    def hbm_record(names, units, bytes_per_unit, what, extra=None):
+        ms_ = sum(prof.get(k, {"ms": 0.0})["ms"] for k in names)
+        n_ = max([prof.get(k, {"launches": 0})["launches"] for k in names] + [0])
+        if not n_:
+            return None
+        calls = n_ if len(names) == 1 else prof.get(names[-1], {"launches": n_})["launches"]
+        avg = ms_ / calls
+        ach = units * bytes_per_unit / (avg * 1e-3) / 1e9
+        r = {"kernel": " + ".join("k_" + k for k in names if k in prof), "bound": "hbm", "achieved": ach, "peak": hbm_peak,
+             "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": hbm_src, "bytes_per_unit": bytes_per_unit,
+             "units_per_call": units, "avg_ms_per_call": avg, "calls": calls, "share_of_step": ms_ / ptotal_ms, "what": what}
+        r.update(extra or {})
+        return r
+
+    m_pts = float(np.mean([p["m"] for p in pinfo]))
+    knn_names = ("bbox", "make_grid", "cell_count", "cell_scatter", "knn")
+    knn_ms = sum(prof.get(k, {"ms": 0.0})["ms"] for k in knn_names)
+    roof_knn = hbm_record(knn_names, m_pts, KNN_BYTES_PER_POINT[1],
+                          "exact 19-NN of the points incl. ghost images through a uniform cell list (neighbour indices written out)",
+                          {"achieved_at_36_bytes_per_point": m_pts * KNN_BYTES_PER_POINT[0] / (knn_ms / max(1, len(frames) * psteps) * 1e-3) / 1e9 if knn_ms else None,
+                           "candidate_distances_per_s": sum(p["cands"] for p in pinfo) * psteps / (prof.get("knn", {"ms": 0.0})["ms"] * 1e-3) if prof.get("knn") else None,
+                           "candidates_per_query": float(np.mean([p["cands"] / p["m"] for p in pinfo])),
+                           "note": "latency / L2-bound in practice (SURVEY 8(d)): report both GB/s and candidate distances/s"})
+    roof_or = hbm_record(("orient",), m_pts, ORIENT_BYTES_PER_POINT(19),
+                         "MST orientation: ONE cooperative kernel per leaflet (Boruvka rounds decided on the device)",
+                         {"boruvka_rounds": [p["rounds"] for p in pinfo],
+                          "graph_edges_per_s": None if not prof.get("orient") else 9.7 * m_pts * len(frames) * psteps / (prof["orient"]["ms"] * 1e-3)})
+
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, V),
             "vertices_per_sec": value * 2 * V, "gpu_launches": launches, "clocks": clk, "e2e": e2e,
-            "roofline": roof, "roofline_geometry": roof_g,
+            "roofline": roof, "roofline_geometry": roof_g, "roofline_knn": roof_knn, "roofline_orient": roof_or,
+            "per_rank": {"ms_per_step": [x / args.steps for x in per_rank_ms], "e2e_ms_per_step": per_rank_e2e,
+                         "first_core": [int(x) for x in rank_cores], "cores": [int(x) for x in rank_ncores],
+                         "numa_node": [int(x) for x in rank_numa]},
+            "setup_seconds": round(t_setup, 2),
             "kernel_ms_per_step": {k: round(v["ms"] / psteps, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}}
-    if not args.no_e2e:
-        # the mesh producer is NOT part of a frame; reported beside it: periodic Delaunay + trim of
-        # one leaflet's planar points on the device, host arrays in, host arrays out
-        from memsurfer_b200 import TriMesh
+    line.update(extras)
+
+    if not args.no_extras:
+        # like-for-like with the CPU arm: the reference's literal all-pairs sum on the same frame
+        try:
+            ap_ms = timed_local(lambda: step_local(0.0), 1, 1)
+            line["allpairs"] = {"ms_per_step": ap_ms, "frames_per_s": 1e3 / ap_ms, "kde": "all pairs (--kde-cutoff 0), 1 step, this rank",
+                                "pairs_per_step": pairs_allpairs_equiv}
+        except Exception as e:
+            line["allpairs"] = {"error": repr(e)}
+        # type-3 (3-D Gaussian) fields: same frame, same cut-off
+        try:
+            fr = frames[0]
+            def t3():
+                fr.run_densities(SIGMAS, types=(3,), cutoff_sigmas=args.kde_cutoff)
+            t3_ms = timed_local(t3, 1, 3)
+            for k in [k for k in fr.densities if 'type3' in k]:
+                del fr.densities[k]
+            line["kde_type3"] = {"ms_per_leaflet": t3_ms / 3, "what": "16 type-3 fields of one leaflet (4 sigmas x (all + 3 types)), device-resident"}
+        except Exception as e:
+            line["kde_type3"] = {"error": repr(e)}
+        # the mesh producer is NOT part of a frame; reported beside it
         lf = leaflets[0]
         try:
             t_prod = []
@@ -444,17 +608,109 @@ def main():
                 pm.compute_delaunay()
                 t_prod.append((time.perf_counter() - t0) * 1e3)
             line["mesh_producer"] = {"ms_per_leaflet": min(t_prod[1:]), "faces": int(pm.faces.shape[0] + pm._trimmed_faces.shape[0]),
-                                     "what": "TriMesh.compute_delaunay: ms_ghosts + ms_knn + ms_delaunay_periodic + ms_delaunay_split, "
-                                             "duplicated-vertex bookkeeping on the host; not included in value / e2e"}
+                                     "what": "TriMesh.compute_delaunay: ms_ghosts + ms_knn + ms_delaunay_periodic + trim; not included in value / e2e"}
         except Exception as e:            # a side measurement must never cost the bench line
             line["mesh_producer"] = {"error": repr(e)}
+
+    # ---- parity of this run's own outputs against the oracle (outside every timed region)
+    keep = {}
     if world == 1 and not args.no_cpu_baseline:
-        fps, kind, cores, sample, detail = cpu_reference_baseline(leaflets[0])
-        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample,
+        fps, kind, ncpu, sample, detail = cpu_reference_baseline(leaflets[0], keep=keep)
+        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": ncpu, "kind": kind, "sample": sample,
                                 "detail": detail}
+    try:
+        line["parity"] = parity_record(frames[0], leaflets[0], step_local, keep)
+    except Exception as e:
+        line["parity"] = {"error": repr(e)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def parity_record(fr, lf, step_device, keep):
+    """Max errors of the frame bench.py just timed (leaflet 0) against the CPU oracle."""
+    import numpy as np
+    import torch
+    from oracle import oracle as O
+    step_device()
+    torch.cuda.synchronize()
+    pts, labels, tri = lf["points"], lf["labels"], lf["tri"]
+    V = pts.shape[0]
+    verts = np.ascontiguousarray(np.concatenate([pts, tri["duplicated_verts"]]), np.float32)
+    faces = np.ascontiguousarray(np.concatenate([tri["faces"], tri["trimmed_faces"]]), np.uint32)
+    out = {"against": "oracle/ms_oracle.c (fp64 restatement), leaflet 0 of the timed frame; bars: 1e-9 relative / 1e-12 absolute"}
+    out["vertex_normals_max_abs"] = float(np.abs(fr.vn64.cpu().numpy() - O.mesh_normals(verts, faces)[:V]).max())
+    out["point_areas_max_abs"] = float(np.abs(fr.pa64.cpu().numpy() - O.pointareas(verts, faces)[:V]).max())
+    if "H" in keep:
+        H, K = keep["H"], keep["K"]
+    else:
+        H, K = O.curvatures(verts, faces, fr.half_box)
+        H, K = H[:V], K[:V]
+
+    def rel(a, b):
+        return float((np.abs(a - b) / np.maximum(np.abs(b), 1e-3 * np.abs(b).max())).max())
+    out["mean_curv_max_rel"] = rel(fr.H.cpu().numpy(), H)
+    out["gaus_curv_max_rel"] = rel(fr.K.cpu().numpy(), K)
+    if "pnormals" in keep:
+        out["point_normals_max_abs"] = float(np.abs(fr.pnormals64.cpu().numpy() - keep["pnormals"]).max())
+    tg = np.arange(0, V, max(1, V // 256))[:256]
+    bb = fr.bboxl
+    worst = 0.0
+    for s, l in ((10.0, 'all'), (40.0, 1)):
+        ids = np.zeros(0, np.int32) if l == 'all' else np.where(labels == l)[0].astype(np.int32)
+        got = fr.densities['density_type2_{}_k{:.1f}'.format(l, s)][0].cpu().numpy()
+        raw = O.kde_raw_targets(pts, ids, tg, 2, s, bb)
+        ratio = got[tg] / raw
+        worst = max(worst, float(np.abs(ratio / np.median(ratio) - 1).max()))
+        out['density_{}_k{:.0f}_sum_minus_count'.format(l, s)] = float(got.sum() - (ids.shape[0] or V))
+    out["density_max_rel_dev_256_targets"] = worst
+    return out
+
+
+def measure_trajectory(args, rank, world, device, barrier, gather_floats):
+    """BASELINE configs[3]: frames of a 100k-lipid, 8-type bilayer sharded over the ranks (frame f -> rank f mod W,
+    strong scaling: the total number of frames is fixed).  Device-resident inputs; every frame = 2 leaflets through
+    LeafletFrame.run + one summary record; the records of all frames are exchanged in ONE all_gather at the end."""
+    import numpy as np
+    import torch
+    from memsurfer_b200 import _lib
+    from memsurfer_b200.frame import LeafletFrame, gather_summaries, shard_frames
+    try:
+        mine = shard_frames(args.trajectory_frames, rank, world)
+        ndistinct = min(len(mine), 8)                       # distinct frames kept resident; the loop cycles through them
+        sets = []
+        for f in mine[:ndistinct]:
+            lfs = make_frame_inputs(100000, f, device=device, ntypes=8, fractions=None)
+            sets.append([LeafletFrame(lf["points"], lf["labels"], lf["bbox"], new_mesh(lf, device), device=device) for lf in lfs])
+        Vt = sets[0][0].nv
+
+        def run_all():
+            recs = []
+            for i in range(len(mine)):
+                for fr in sets[i % ndistinct]:
+                    fr.run(SIGMAS, 18, args.kde_cutoff)
+                    recs.append(fr.summary())
+            rec = torch.stack(recs)
+            return gather_summaries(rec) if world > 1 else rec
+
+        for fr in sets[0]:
+            fr.run(SIGMAS, 18, args.kde_cutoff)             # warm-up (workspaces, function attributes)
+        barrier()
+        L = _lib.lib()
+        L.ms_launch_count(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); run_all(); e1.record()
+        torch.cuda.synchronize()
+        launches = int(L.ms_launch_count(1))
+        per_rank = gather_floats(e0.elapsed_time(e1))
+        ms = max(per_rank)
+        return {"config": f"configs[3]: {args.trajectory_frames} frames x 100k lipids (2 x {Vt} points), 8 types, sigmas {SIGMAS}, "
+                          f"frame f -> rank f mod {world}; {ndistinct} distinct frames resident per rank, cycled",
+                "frames": args.trajectory_frames, "frames_per_s": args.trajectory_frames / (ms * 1e-3), "scaling": "strong",
+                "ms_total": ms, "ms_per_frame_per_rank": ms / max(1, len(mine)), "per_rank_ms": per_rank,
+                "launches_per_frame": launches / max(1, len(mine)), "collective": "one all_gather of the summary records at the end"}
+    except Exception as e:
+        return {"error": repr(e)}
 
 
 if __name__ == "__main__":

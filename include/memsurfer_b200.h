@@ -43,8 +43,14 @@ const char *ms_last_error(void);
 #define MS_INFO_KNN_TIES    2   /* diagnostic: k-NN queries redone in exact (distance, index) order  */
 #define MS_INFO_MST_ROUNDS  3   /* diagnostic: Boruvka rounds                                         */
 #define MS_INFO_ERROR       4   /* bit flags, 0 = ok                                                  */
+#define MS_INFO_KNN_CANDS   5   /* diagnostic: candidate distances the k-NN evaluated                */
 #define MS_INFO_WORDS       8
 #define MS_ERR_NONFINITE    1   /* non-finite coordinates: every neighbour list is -1                */
+
+/* Replaces the host scan of Membrane.fit_points_to_box_xy (membrane.py:100-121): *count_dev (device int64) = number
+ * of x / y coordinates outside [box0, box1] (box6 on the host), i.e. how many coordinates the wrap would move.  The
+ * usual answer is 0, and then the host never has to walk the points.                                            */
+int ms_points_outside_box(const float *points, int64_t n, const float *box6, int64_t *count_dev, void *stream);
 
 /* Upper bound of points incl. ghost images (each point gets <= 3 images). */
 int64_t ms_pointset_capacity(int64_t n, int periodic);

@@ -24,6 +24,7 @@ _vp, _i64, _i32, _f32, _f64, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.
 _SIGNATURES = {
     "ms_version": (C.c_int, []),
     "ms_last_error": (C.c_char_p, []),
+    "ms_points_outside_box": (C.c_int, [_vp, _i64, C.POINTER(_f32), _vp, _vp]),
     "ms_pointset_capacity": (_i64, [_i64, _i32]),
     "ms_ghosts_workspace_bytes": (_sz, [_i64]),
     "ms_ghosts": (C.c_int, [_vp, _i64, _i32, C.POINTER(_f32), _f32, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -76,7 +77,7 @@ _SIGNATURES = {
 }
 EXPORTS = tuple(_SIGNATURES.keys())
 # layout of the device status block of the point-normal chain (include/memsurfer_b200.h)
-INFO_M, INFO_UNORIENTED, INFO_KNN_TIES, INFO_MST_ROUNDS, INFO_ERROR, INFO_WORDS = 0, 1, 2, 3, 4, 8
+INFO_M, INFO_UNORIENTED, INFO_KNN_TIES, INFO_MST_ROUNDS, INFO_ERROR, INFO_KNN_CANDS, INFO_WORDS = 0, 1, 2, 3, 4, 5, 8
 
 
 def lib():

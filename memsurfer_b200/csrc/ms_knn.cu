@@ -56,6 +56,29 @@ __global__ void __launch_bounds__(256) k_copy_points(const float *__restrict__ p
 }
 
 extern "C" int64_t ms_pointset_capacity(int64_t n, int periodic) { return periodic ? 4 * n : n; }
+
+// number of x / y coordinates outside the box: what Membrane.fit_points_to_box_xy (membrane.py:100-121) would move
+__global__ void __launch_bounds__(256) k_count_outside(const float *__restrict__ pts, int64_t n, float b0x, float b0y, float b1x, float b1y,
+                                                       unsigned long long *count) {
+    unsigned c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float x = pts[3*i], y = pts[3*i+1];
+        c += (x < b0x) + (x > b1x) + (y < b0y) + (y > b1y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, (unsigned long long)c);
+}
+extern "C" int ms_points_outside_box(const float *points, int64_t n, const float *box6, int64_t *count_dev, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(points && n > 0 && box6 && count_dev, "ms_points_outside_box: bad arguments");
+    MS_CUDA(cudaMemsetAsync(count_dev, 0, sizeof(int64_t), s));
+    MS_K("count_outside", s);
+    k_count_outside<<<ms_sm_count() * 4, 256, 0, s>>>(points, n, box6[0], box6[1], box6[3], box6[4], (unsigned long long*)count_dev);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
 extern "C" size_t ms_ghosts_workspace_bytes(int64_t n) {
     return 2 * ms_align((size_t)(n + 1) * sizeof(int32_t)) + ms_scan_ws_bytes(n) + 1024;
 }
@@ -63,7 +86,7 @@ extern "C" size_t ms_ghosts_workspace_bytes(int64_t n) {
 // info[MS_INFO_M] = n + total ghosts (or n); the other diagnostic slots are cleared
 __global__ void k_ghost_total(const int32_t *__restrict__ off_n, int64_t n, int64_t *info) {
     info[MS_INFO_M] = n + (off_n ? (int64_t)*off_n : 0);
-    info[MS_INFO_UNORIENTED] = 0; info[MS_INFO_KNN_TIES] = 0; info[MS_INFO_MST_ROUNDS] = 0; info[MS_INFO_ERROR] = 0;
+    info[MS_INFO_UNORIENTED] = 0; info[MS_INFO_KNN_TIES] = 0; info[MS_INFO_MST_ROUNDS] = 0; info[MS_INFO_ERROR] = 0; info[MS_INFO_KNN_CANDS] = 0;
 }
 
 extern "C" int ms_ghosts(const float *points, int64_t n, int periodic, const float *box6, float blayer,
@@ -228,9 +251,10 @@ __device__ __forceinline__ void knn_scan_fast(const float4 *__restrict__ sorted,
 
 // ring-by-ring search around cell (cx,cy) until the K-th distance lies inside the explored square
 template <int K, bool FAST>
-__device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, const Grid &g, const int32_t *__restrict__ start,
+__device__ __forceinline__ unsigned knn_search(const float4 *__restrict__ sorted, const Grid &g, const int32_t *__restrict__ start,
                                            int cx, int cy, double qx, double qy, double qz, double (&bd)[K], int (&bi)[K], bool &tie) {
     const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
+    unsigned ncand = 0;
     for (int r = 0; ; r++) {
         for (int yy = cy - r; yy <= cy + r; yy++) {
             if (yy < 0 || yy >= g.ny) continue;
@@ -242,6 +266,7 @@ __device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, co
                 x0 = max(x0, 0); x1 = min(x1, g.nx - 1);
                 if (x0 > x1) continue;
                 const int pb = __ldg(start + yy * g.nx + x0), pe = __ldg(start + yy * g.nx + x1 + 1);
+                ncand += (unsigned)(pe - pb);
                 if (FAST) knn_scan_fast<K>(sorted, pb, pe, qx, qy, qz, bd, bi, tie);
                 else      knn_scan<K>(sorted, pb, pe, qx, qy, qz, bd, bi);
             }
@@ -255,6 +280,7 @@ __device__ __forceinline__ void knn_search(const float4 *__restrict__ sorted, co
         const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
         if (bm > 0.0 && bd[K - 1] < DBL_MAX && sqrt(bd[K - 1]) < bm * (1.0 - 1e-9)) break;
     }
+    return ncand;
 }
 
 template <int K>
@@ -272,21 +298,28 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
 #pragma unroll
     for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
     int qi = -1;
+    unsigned ncand = 0;
     if (q < m && g.ok) {
         const float4 me = sorted[q];
         qi = __float_as_int(me.w);
         const double qx = me.x, qy = me.y, qz = me.z;
         int cx, cy; cell_of(g, me.x, me.y, cx, cy);
         bool tie = false;
-        knn_search<K, true>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
+        ncand = knn_search<K, true>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
 #pragma unroll
         for (int j = 1; j < K; j++) tie |= (bd[j] == bd[j - 1]) && bd[j] < DBL_MAX;      // ties inside the kept list
         if (tie) {             // rare: repeat with the exact (distance, index) order
             if (info_out) atomicAdd((unsigned long long*)(info_out + MS_INFO_KNN_TIES), 1ull);
 #pragma unroll
             for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
-            knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
+            ncand += knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
         }
+    }
+    if (info_out) {             // diagnostic: candidate distances evaluated (one atomic per warp)
+        unsigned long long c = ncand;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd((unsigned long long*)(info_out + MS_INFO_KNN_CANDS), c);
     }
     if (q < m && !g.ok) qi = __float_as_int(sorted[q].w);      // non-finite input: the row is all -1
     sm_q[threadIdx.x] = qi;

@@ -32,7 +32,8 @@ class PointNormalsInfo(dict):
             h = self._pending.result()
             self._pending = None
             dict.update(self, m=int(h[_lib.INFO_M]), n_unoriented=int(h[_lib.INFO_UNORIENTED]),
-                        knn_ties=int(h[_lib.INFO_KNN_TIES]), mst_rounds=int(h[_lib.INFO_MST_ROUNDS]))
+                        knn_ties=int(h[_lib.INFO_KNN_TIES]), mst_rounds=int(h[_lib.INFO_MST_ROUNDS]),
+                        knn_candidates=int(h[_lib.INFO_KNN_CANDS]))
             if int(h[_lib.INFO_ERROR]) != 0:
                 raise _lib.MemSurferCudaError('point normals: non-finite point coordinates')
         return self
@@ -177,6 +178,7 @@ class Membrane(object):
         # later fit_points_to_box_xy(): normals are computed on these coordinates.  The PointSet copy
         # lives in HBM: the upload starts now and self.points is not touched before it has landed.
         self._pset_dev, self._pset_event, self._stream, self._overlap = None, None, None, None
+        self._outside, self._points_at_upload = None, True      # self.points still equals what was uploaded
         self._pset_nbytes = self.points.nbytes
         if torch.cuda.is_available():
             self._stream = _lib.next_stream(self.device)
@@ -201,6 +203,18 @@ class Membrane(object):
         self._pset_dev = _lib.h2d(self.points, self.device)
         self._pset_event = torch.cuda.Event()
         self._pset_event.record(torch.cuda.current_stream(self.device))
+        # fit_points_to_box_xy (membrane.py:100-121) walks the points four times on the host; the device counts the
+        # coordinates outside the box right behind the upload, and the host only walks them if there are any
+        self._outside = None
+        if self.periodic:
+            cnt = torch.empty(1, dtype=torch.int64, device=self.device)
+            _lib.check(_lib.lib().ms_points_outside_box(self._pset_dev.data_ptr(), self.npoints, _lib.box6(self.bbox.reshape(-1)),
+                                                        cnt.data_ptr(), _lib.stream_ptr(self.device)), 'ms_points_outside_box')
+            self._outside = _lib.d2h_async(cnt)
+            # the count stands for self.points only while nobody writes to the array: hand out a read-only view
+            # (fit_points_to_box_xy swaps in a writable copy when it has to move a point)
+            self.points = self.points.view()
+            self.points.flags.writeable = False
         # membrane.py:84 -- warn about coincident input points (grid-based on the GPU instead of pdist).  The
         # search is only queued here (cell list over the given box, no read-back); the verdict is fetched at
         # the first point where this membrane synchronises anyway (compute_pnormals) or by check_overlaps().
@@ -257,13 +271,13 @@ class Membrane(object):
     def fit_points_to_box_xy(self):
         """Wrap x,y into the box (membrane.py:100-121); returns the number of adjusted coordinates."""
         nadjusted = 0
-        if self._pset_event is not None:
-            self._pset_event.synchronize()         # the PointSet upload reads self.points
         boxw = self.bbox[1, :] - self.bbox[0, :]
-        xy = self.points[:, :2]
-        if not ((xy < self.bbox[0, :2]).any() or (xy > self.bbox[1, :2]).any()):
-            return 0
-        if self._points_shared:            # the caller's own page-locked array: leave it as it is
+        outside = getattr(self, '_outside', None)
+        if outside is not None and self._points_at_upload:
+            if int(outside.result()[0]) == 0:      # counted on the device right behind the upload
+                return 0
+        self._points_at_upload = False
+        if self._points_shared or not self.points.flags.writeable:      # the caller's own array / the read-only view
             self.points, self._points_shared = self.points.copy(), False
         for d in range(2):
             lo = self.points[:, d] < self.bbox[0, d]
