@@ -161,6 +161,18 @@ int ms_kde_select(const double *raw, int64_t nv, int nlabels, const uint8_t *sel
                   int get_counts, double *density_f64, float *density_f32,
                   void *ws, size_t ws_bytes, void *stream);
 
+/* Any number of fields of one call in two launches (instead of ms_kde_select's two per field).  raw = nrows rows of nv
+ * raw sums (e.g. the (nsigma, nlabels, nv) block of ms_kde_labels_multi: nrows = nsigma * nlabels).
+ * ms_kde_label_totals: partials (ms_kde_label_totals_bytes(nrows) bytes) = fixed-order partial sums of every row.
+ * ms_kde_fields: field f = the union of the labels in masks[f] (bit l = label l) of the sigma whose first row is
+ * row0[f], normalised like TriMesh::kde (TriMesh_kde.cpp:504-524) with n_selected[f] source vertices; row0, masks,
+ * n_selected are HOST arrays of nfields (<= 64) entries; outputs (nfields, nv), either may be NULL.                */
+size_t ms_kde_label_totals_bytes(int64_t nrows);
+int ms_kde_label_totals(const double *raw, int64_t nrows, int64_t nv, double *partials, void *stream);
+int ms_kde_fields(const double *raw, const double *partials, int64_t nv, int nlabels, int nfields,
+                  const int32_t *row0, const uint64_t *masks, const double *n_selected, int get_counts,
+                  double *out_f64, float *out_f32, void *stream);
+
 /* Several sigmas in one call: raw (nsigma, nlabels, nv) = the ms_kde_labels result of every sigma (host array
  * `sigmas`).  With a cut-off whose window plan fits every sigma the vertices are binned ONCE (on the grid of the
  * smallest sigma) and only re-staged per sigma; otherwise a loop over ms_kde_labels.  This is the loop

@@ -1137,6 +1137,84 @@ extern "C" int ms_kde_select(const double *raw, int64_t nv, int nlabels, const u
     return 0;
 }
 
+// ------------------------------------------------------------------ all fields of a call in two launches
+// Membrane.compute_densities (membrane.py:289-297) asks for one field per (sigma, label set); each is
+//   density = sum_{l in set} raw[sigma][l] / nv          (TriMesh_kde.cpp:504-512)
+//   get_counts: density *= n_selected / sum_j density    (TriMesh_kde.cpp:515-524)
+// The sum over all vertices only depends on the per-(sigma, label) totals of raw: ms_kde_label_totals reduces every
+// row of raw once (fixed order: KDE_TOT_BLOCKS partial sums per row), ms_kde_fields then writes ANY number of
+// fields in one launch -- instead of two launches per field.
+#define KDE_TOT_BLOCKS 256
+#define KDE_MAX_FIELDS 64
+__global__ void __launch_bounds__(RED_T) k_kde_label_totals(const double *__restrict__ raw, int64_t nv, double *__restrict__ partials) {
+    __shared__ double sm[RED_T];
+    const double *__restrict__ x = raw + (size_t)blockIdx.y * nv;
+    double s = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * RED_T + threadIdx.x; i < nv; i += (int64_t)KDE_TOT_BLOCKS * RED_T) s += x[i];
+    sm[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) partials[(size_t)blockIdx.y * KDE_TOT_BLOCKS + blockIdx.x] = sm[0];
+}
+struct KdeFieldSet { int row0[KDE_MAX_FIELDS]; unsigned long long mask[KDE_MAX_FIELDS]; double nsel[KDE_MAX_FIELDS]; };
+#define FIELD_PER_T 4
+__global__ void __launch_bounds__(RED_T) k_kde_fields(const double *__restrict__ raw, const double *__restrict__ partials, int64_t nv, int nlabels,
+                                                      KdeFieldSet F, int get_counts, double *__restrict__ o64, float *__restrict__ o32) {
+    __shared__ double sm[RED_T];
+    const int f = blockIdx.y;
+    const int row0 = F.row0[f];
+    const unsigned long long mask = F.mask[f];
+    const double inv_nv = 1.0 / (double)nv;
+    double scale = 1.0;
+    if (get_counts) {             // sum_j density_j = (sum of the selected rows' totals) / nv, re-reduced in a fixed order by every block
+        double t = 0.0;
+        for (int l = 0; l < nlabels; l++) if ((mask >> l) & 1ull) t += partials[(size_t)(row0 + l) * KDE_TOT_BLOCKS + threadIdx.x];
+        sm[threadIdx.x] = t;
+        __syncthreads();
+        for (int o = RED_T / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+        scale = F.nsel[f] / (sm[0] * inv_nv);
+    }
+#pragma unroll
+    for (int k = 0; k < FIELD_PER_T; k++) {
+        const int64_t j = ((int64_t)blockIdx.x * FIELD_PER_T + k) * RED_T + threadIdx.x;
+        if (j >= nv) break;
+        double d = 0.0;
+        for (int l = 0; l < nlabels; l++) if ((mask >> l) & 1ull) d += raw[(size_t)(row0 + l) * nv + j];
+        d *= inv_nv;
+        if (get_counts) d *= scale;
+        if (o64) o64[(size_t)f * nv + j] = d;
+        if (o32) o32[(size_t)f * nv + j] = (float)d;
+    }
+}
+
+extern "C" size_t ms_kde_label_totals_bytes(int64_t nrows) { return (size_t)(nrows < 1 ? 1 : nrows) * KDE_TOT_BLOCKS * sizeof(double); }
+extern "C" int ms_kde_label_totals(const double *raw, int64_t nrows, int64_t nv, double *partials, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(raw && partials && nrows >= 1 && nrows <= 65535 && nv > 0, "ms_kde_label_totals: bad arguments");
+    MS_K("kde_label_totals", s); k_kde_label_totals<<<dim3(KDE_TOT_BLOCKS, (unsigned)nrows), RED_T, 0, s>>>(raw, nv, partials);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int ms_kde_fields(const double *raw, const double *partials, int64_t nv, int nlabels, int nfields,
+                             const int32_t *row0, const uint64_t *masks, const double *n_selected, int get_counts,
+                             double *out_f64, float *out_f32, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(raw && partials && row0 && masks && n_selected && nv > 0 && nlabels >= 1 && nlabels <= KDE_MAX_LABELS,
+               "ms_kde_fields: bad arguments");
+    MS_REQUIRE(nfields >= 1 && nfields <= KDE_MAX_FIELDS, "ms_kde_fields: 1 <= nfields <= %d", KDE_MAX_FIELDS);
+    KdeFieldSet F;
+    for (int f = 0; f < nfields; f++) {
+        MS_REQUIRE(row0[f] >= 0 && masks[f] != 0ull && n_selected[f] > 0.0, "ms_kde_fields: field %d selects no source label", f);
+        F.row0[f] = row0[f]; F.mask[f] = masks[f]; F.nsel[f] = n_selected[f];
+    }
+    MS_K("kde_fields", s);
+    k_kde_fields<<<dim3((unsigned)ms_blocks(nv, RED_T * FIELD_PER_T), (unsigned)nfields), RED_T, 0, s>>>(raw, partials, nv, nlabels, F, get_counts, out_f64, out_f32);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, const int32_t *labels, int nlabels,
                                       int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                                       double *pairs, void *ws, size_t ws_bytes, void *stream) {

@@ -77,6 +77,7 @@ class LeafletFrame(object):
         self.kde_raw = torch.empty((nl, nv), dtype=torch.float64, device=dev)
         self.sum_ws = _lib.workspace(L.ms_field_summary_workspace_bytes(24), dev)
         self.densities = {}
+        self._field_blocks = {}
         self.pnormals32 = self.pnormals64 = None
         self.info = {}
 
@@ -140,32 +141,52 @@ class LeafletFrame(object):
                            'ms_kde_labels_multi')
                 for i, s in enumerate(sigmas):
                     raws[(t, float(s))] = self.kde_raw_multi[i * nl * self.nv:(i + 1) * nl * self.nv]
+        import ctypes as C
         for t in types:
-            for s in sigmas:
-                if not fused:
+            if not fused:
+                for s in sigmas:
                     self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, 'all', s), t, s, get_nlipids, None, cutoff_sigmas)
                     for l, ids in self.label_ids.items():
                         self.run_density('density_type{0}_{1}_k{2:.1f}'.format(t, l, s), t, s, get_nlipids, ids, cutoff_sigmas)
-                    continue
-                nl = int(self.label_values.shape[0])
-                raw = raws.get((t, float(s)))
-                if raw is None:
-                    raw = self.kde_raw
+                continue
+            nl = int(self.label_values.shape[0])
+            if (t, float(sigmas[0])) in raws:
+                raw_all = self.kde_raw_multi                     # (nsigma, nl, nv) from the shared binning
+            else:                                                # one ms_kde_labels pass per sigma into the same layout
+                need = len(sigmas) * nl * self.nv
+                if getattr(self, 'kde_raw_multi', None) is None or self.kde_raw_multi.numel() < need:
+                    self.kde_raw_multi = torch.empty(need, dtype=torch.float64, device=self.device)
+                raw_all = self.kde_raw_multi
+                for i, s in enumerate(sigmas):
                     _lib.check(L.ms_kde_labels(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(), nl, int(t),
                                                int(self.periodic), self._box(cutoff_sigmas), float(s), float(cutoff_sigmas),
-                                               self.kde_raw.data_ptr(), self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
+                                               raw_all.data_ptr() + 8 * i * nl * self.nv, self.kde_ws.data_ptr(), self.kde_ws.numel(), st),
                                'ms_kde_labels')
+            # every field of this type in two launches: per-row totals, then all normalised fields
+            nrows = len(sigmas) * nl
+            tot_words = int(L.ms_kde_label_totals_bytes(nrows)) // 8
+            if getattr(self, 'kde_totals', None) is None or self.kde_totals.numel() < tot_words:
+                self.kde_totals = torch.empty(tot_words, dtype=torch.float64, device=self.device)
+            _lib.check(L.ms_kde_label_totals(raw_all.data_ptr(), nrows, self.nv, self.kde_totals.data_ptr(), st), 'ms_kde_label_totals')
+            names, row0, masks, nsels = [], [], [], []
+            for i, s in enumerate(sigmas):
                 for li, l in enumerate(['all'] + [v.item() for v in self.label_values]):
-                    name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)
-                    out = self.densities.get(name)
-                    if out is None:
-                        out = self.densities[name] = (torch.empty(self.nv, dtype=torch.float64, device=self.device),
-                                                      torch.empty(self.nv, dtype=torch.float32, device=self.device))
-                    sel = np.ones(nl, np.uint8) if li == 0 else np.eye(nl, dtype=np.uint8)[li - 1]
-                    nsel = float(self.nv if li == 0 else self.label_counts[li - 1])
-                    _lib.check(L.ms_kde_select(raw.data_ptr(), self.nv, nl, sel.tobytes(), nsel, int(bool(get_nlipids)),
-                                               out[0].data_ptr(), out[1].data_ptr(), self.kde_sel_ws.data_ptr(),
-                                               self.kde_sel_ws.numel(), st), 'ms_kde_select')
+                    names.append('density_type{0}_{1}_k{2:.1f}'.format(t, l, s))
+                    row0.append(i * nl)
+                    masks.append((1 << nl) - 1 if li == 0 else 1 << (li - 1))
+                    nsels.append(float(self.label_counts.sum() if li == 0 else self.label_counts[li - 1]))
+            for b in range(0, len(names), 64):
+                nb_ = min(64, len(names) - b)
+                blk = self._field_blocks.get((t, b))
+                if blk is None or blk[0].shape[0] != nb_:
+                    blk = self._field_blocks[(t, b)] = (torch.empty((nb_, self.nv), dtype=torch.float64, device=self.device),
+                                                        torch.empty((nb_, self.nv), dtype=torch.float32, device=self.device))
+                _lib.check(L.ms_kde_fields(raw_all.data_ptr(), self.kde_totals.data_ptr(), self.nv, nl, nb_,
+                                           (C.c_int32 * nb_)(*row0[b:b + nb_]), (C.c_uint64 * nb_)(*masks[b:b + nb_]),
+                                           (C.c_double * nb_)(*nsels[b:b + nb_]), int(bool(get_nlipids)),
+                                           blk[0].data_ptr(), blk[1].data_ptr(), st), 'ms_kde_fields')
+                for k in range(nb_):
+                    self.densities[names[b + k]] = (blk[0][k], blk[1][k])
 
     def run(self, sigmas, knbrs=18, cutoff_sigmas=0.0, fused=True):
         self.run_pnormals(knbrs)

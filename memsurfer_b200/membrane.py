@@ -458,15 +458,48 @@ class Membrane(object):
             a.properties['thickness'] = a.memb_smooth.compute_distance_to_surface(b.memb_smooth)
             b.properties['thickness'] = b.memb_smooth.compute_distance_to_surface(a.memb_smooth)
 
+    def _fused_select(self, labels):
+        """Label indices (into the distinct label values) selected by `labels`, or None when the label-fused KDE
+        does not apply (no point labels, or too many distinct ones)."""
+        if self.labels is None:
+            return None
+        values, inverse = self._label_table()
+        if values.shape[0] > self.MAX_FUSED_LABELS:
+            return None
+        select = np.arange(values.shape[0]) if len(labels) == 0 else np.where(np.isin(values, labels))[0]
+        if select.shape[0] == 0:           # absent label: empty id list = all vertices (membrane.py:273-274)
+            select = np.arange(values.shape[0])
+        return select
+
+    @_lib.home_stream
+    def _compute_densities_fused(self, t, sigmas, names, get_nlipdis, labels):
+        """All sigmas of one (type, label set) through one multi-field launch; False if the fused path does not apply."""
+        if t not in (2, 3) or self.memb_smooth is None:
+            return False
+        select = self._fused_select(labels)
+        if select is None:
+            return False
+        mesh = self._adopt(self.memb_smooth)
+        if mesh._label_index is None:
+            mesh.set_vertex_labels(self._label_table()[1], self._label_values.shape[0], self._label_counts)
+        vals = mesh.compute_density_labels_multi(t, sigmas, names, get_nlipdis, select, self.KDE_CUTOFF_SIGMAS)
+        for n_, v in zip(names, vals):
+            self.attributes.adopt(n_, v)
+        return True
+
     @staticmethod
     def compute_densities(membranes, types, sigmas, get_nlipdis, l):
         labels = [] if l == 'all' else [l]
         for m in membranes:            # label-fused path: all sigmas of a type on one binning of the vertices
             m._prefetch_densities(types, sigmas)
         for t in types:
-            for s in sigmas:
-                name = 'density_type{0}_{1}_k{2:.1f}'.format(t, l, s)
-                for m in membranes:
+            names = ['density_type{0}_{1}_k{2:.1f}'.format(t, l, s) for s in sigmas]
+            for m in membranes:
+                if len(labels) > 0 and m.labels is None:
+                    raise ValueError('Cannot compute density of selected labels, because point labels are not available')
+                if m._compute_densities_fused(t, sigmas, names, get_nlipdis, labels):
+                    continue
+                for s, name in zip(sigmas, names):       # the reference's loop (membrane.py:289-297)
                     m.compute_density(t, s, name, get_nlipdis, labels)
 
     @staticmethod

@@ -555,15 +555,35 @@ class TriMesh(object):
 
     KDE_RAW_CACHE_BYTES = 4 << 30      # raw per-label pair sums kept per mesh (oldest (type, sigma, cut-off) evicted first)
 
-    def _kde_raw_store(self, key, raw):
+    def _kde_raw_store(self, keys, block):
+        """Cache the raw per-label sums of one ms_kde_labels(_multi) call: block (nsigma, nlabels, nv); keys[i] = the
+        (type, sigma, cut-off) of sigma i.  Every key maps to (block holder, i); the holder also keeps the per-row
+        totals once they are needed.  Oldest blocks are evicted first when the cache outgrows its byte budget."""
         cache = self._dev.setdefault('kde_raw', {})
-        cache[key] = raw
-        total = sum(v.numel() * 8 for v in cache.values())
-        for k in list(cache.keys()):
-            if total <= self.KDE_RAW_CACHE_BYTES or k == key:
+        holder = {'raw': block, 'totals': None}
+        for i, k in enumerate(keys):
+            cache[k] = (holder, i)
+        seen, total = [], 0
+        for k, (h, _) in cache.items():
+            if not any(h is x for x in seen):
+                seen.append(h); total += h['raw'].numel() * 8
+        for h in seen:
+            if total <= self.KDE_RAW_CACHE_BYTES or h is holder:
                 continue
-            total -= cache[k].numel() * 8
-            del cache[k]
+            total -= h['raw'].numel() * 8
+            for k in [k for k, (hh, _) in cache.items() if hh is h]:
+                del cache[k]
+
+    def _kde_totals(self, holder):
+        """(nsigma * nlabels, 256) partial sums of every row of the block (one launch, cached with the block)."""
+        if holder['totals'] is None:
+            L = _lib.lib()
+            raw = holder['raw']
+            nrows, nv = raw.shape[0] * raw.shape[1], raw.shape[2]
+            tot = torch.empty(int(L.ms_kde_label_totals_bytes(nrows)) // 8, dtype=torch.float64, device=self.device)
+            _lib.check(L.ms_kde_label_totals(raw.data_ptr(), nrows, nv, tot.data_ptr(), _lib.stream_ptr(self.device)), 'ms_kde_label_totals')
+            holder['totals'] = tot
+        return holder['totals']
 
     def clear_density_cache(self):
         """Drop the raw per-label pair sums kept for later compute_density_labels calls (device memory)."""
@@ -592,19 +612,20 @@ class TriMesh(object):
         cache = d.setdefault('kde_raw', {})
         key = (int(type), float(sigma), float(cutoff_sigmas))
         if key in cache:
-            return cache[key]
+            h, i = cache[key]
+            return h['raw'][i]
         kverts = self._kde_verts_device()
         nv = kverts.shape[0]
         if 'labels' not in d:
             d['labels'] = _lib.h2d(self._label_index, dev)
-        raw = torch.empty((self._nlabels, nv), dtype=torch.float64, device=dev)
+        raw = torch.empty((1, self._nlabels, nv), dtype=torch.float64, device=dev)
         ws = self._workspace('kde_ws', L.ms_kde_labels_workspace_bytes(nv, self._nlabels))
         _lib.check(L.ms_kde_labels(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
                                    int(bool(self.periodic)), self._kde_box(cutoff_sigmas), float(sigma),
                                    float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
                                    _lib.stream_ptr(dev)), 'ms_kde_labels')
-        self._kde_raw_store(key, raw)
-        return raw
+        self._kde_raw_store([key], raw)
+        return raw[0]
 
     @_lib.home_stream
     def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0):
@@ -629,8 +650,7 @@ class TriMesh(object):
                                          int(bool(self.periodic)), self._kde_box(cutoff_sigmas), sg, len(todo),
                                          float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
                                          _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
-        for i, s_ in enumerate(todo):
-            self._kde_raw_store((int(type), s_, float(cutoff_sigmas)), raw[i])
+        self._kde_raw_store([(int(type), s_, float(cutoff_sigmas)) for s_ in todo], raw)
 
     @_lib.home_stream
     def density_select_device(self, raw, select, get_nlipids):
@@ -648,6 +668,41 @@ class TriMesh(object):
                                    o64.data_ptr(), o32.data_ptr(), ws.data_ptr(), ws.numel(),
                                    _lib.stream_ptr(dev)), 'ms_kde_select')
         return o64, o32
+
+    @_lib.home_stream
+    def compute_density_labels_multi(self, type, sigmas, names, get_nlipids, select, cutoff_sigmas=0.0):
+        """compute_density_labels for several sigmas of one label set at once: the fields that are not cached yet are
+        normalised and written by ONE ms_kde_fields launch per block of raw sums (all sigmas of a prefetch share one).
+        Returns the stored values (downloads possibly still in flight) in the order of `names`."""
+        if type not in (2, 3):
+            return [self.compute_density_labels(type, s_, n_, get_nlipids, select, cutoff_sigmas, lazy=True) for s_, n_ in zip(sigmas, names)]
+        L = _lib.lib()
+        dev = self.device
+        sel = np.zeros(self._nlabels, bool)
+        sel[np.asarray(select, dtype=np.int64)] = True
+        mask = int(sum(1 << int(l) for l in np.flatnonzero(sel)))
+        nsel = float(self._label_counts[sel].sum())
+        todo = [(float(s_), n_) for s_, n_ in zip(sigmas, names) if n_ not in self._fields]
+        by_block = {}
+        for s_, n_ in todo:
+            self.density_labels_device(type, s_, cutoff_sigmas)             # makes sure the raw sums exist
+            h, i = self._dev['kde_raw'][(int(type), s_, float(cutoff_sigmas))]
+            by_block.setdefault(id(h), (h, []))[1].append((i, n_))
+        for h, items in by_block.values():
+            raw = h['raw']
+            nv, nf = raw.shape[2], len(items)
+            tot = self._kde_totals(h)
+            row0 = (_lib.C.c_int32 * nf)(*[i * self._nlabels for i, _ in items])
+            masks = (_lib.C.c_uint64 * nf)(*([mask] * nf))
+            nsels = (_lib.C.c_double * nf)(*([nsel] * nf))
+            o64 = torch.empty((nf, nv), dtype=torch.float64, device=dev)
+            o32 = torch.empty((nf, nv), dtype=torch.float32, device=dev)
+            _lib.check(L.ms_kde_fields(raw.data_ptr(), tot.data_ptr(), nv, self._nlabels, nf, row0, masks, nsels,
+                                       int(bool(get_nlipids)), o64.data_ptr(), o32.data_ptr(), _lib.stream_ptr(dev)), 'ms_kde_fields')
+            for k, (_, n_) in enumerate(items):
+                self._fields.park(n_, o32[k])
+                self.attributes_f64.park(n_, o64[k])
+        return [self._fields.raw(n_) for n_ in names]
 
     @_lib.home_stream
     def compute_density_labels(self, type, sigma, name, get_nlipids, select, cutoff_sigmas=0.0, lazy=False):
