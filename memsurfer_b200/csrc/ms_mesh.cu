@@ -1,5 +1,5 @@
-// ms_mesh.cu -- TriMesh geometry on B200: vertex->face CSR build and ONE fused per-vertex
-// gather kernel for vertex normals, mixed Voronoi areas, mean and Gaussian curvature.
+// ms_mesh.cu -- TriMesh geometry on B200: vertex->face CSR build, a corner-parallel pass for the atan2 terms and an
+// eight-lanes-per-vertex ordered gather for vertex normals, mixed Voronoi areas, mean and Gaussian curvature.
 //
 // Replaces (LLNL/MemSurfer): TriMesh::need_normals memsurfer/src/TriMesh.cpp:99-133,
 // TriMesh::need_pointareas TriMesh.cpp:140-190, their periodic wrappers TriMesh.hpp:346-407,
@@ -14,7 +14,6 @@
 // produced (the reference computes and then drops them, TriMesh.hpp:368-369, trimesh.py:310-311).
 #include "ms_common.cuh"
 
-#define MESH_T 128
 
 // ------------------------------------------------------------------ topology
 __global__ void __launch_bounds__(256) k_face_degree(const float *__restrict__ verts, const uint32_t *__restrict__ faces,
@@ -86,11 +85,19 @@ extern "C" int ms_mesh_topology(const float *verts_all, int64_t nv_all, int64_t 
     return 0;
 }
 
-// ------------------------------------------------------------------ properties: face pass, edge pass, vertex gather
+// ------------------------------------------------------------------ properties: corner pass + vertex gather
+// Data flow (algorithmic bytes: 84 B/vertex): vertices are padded ONCE to float4 (one LDG.128 per
+// gather); the only per-face state that goes through memory is what is expensive to recompute -- the atan2
+// results: the three corner angle terms of the Gaussian curvature and the (up to three) dihedral edge terms of
+// the mean curvature, 48 bytes per face.  Everything else (face normal, corner weights, mixed Voronoi corner
+// areas, triangle area: cross products, a square root and a division) is recomputed per (vertex, incident face)
+// from the L2-resident float4 vertices -- the 128-byte face records of the first version cost 11x the
+// algorithmic DRAM traffic.
 struct D3 { double x, y, z; };
-__device__ __forceinline__ D3 ldv(const float *__restrict__ verts, uint32_t i) {
-    const float *p = verts + 3 * (size_t)i;
-    D3 r; r.x = (double)__ldg(p); r.y = (double)__ldg(p + 1); r.z = (double)__ldg(p + 2); return r;
+// random gathers go straight to L2 (ld.cg): through L1 they were measured 2.8x slower in the orientation kernel
+__device__ __forceinline__ D3 ldv4(const float4 *__restrict__ v4, uint32_t i) {
+    const float4 p = __ldcg(v4 + i);
+    D3 r; r.x = (double)p.x; r.y = (double)p.y; r.z = (double)p.z; return r;
 }
 __device__ __forceinline__ D3 sub(const D3 &a, const D3 &b) { D3 r; r.x = a.x - b.x; r.y = a.y - b.y; r.z = a.z - b.z; return r; }
 __device__ __forceinline__ double dot(const D3 &a, const D3 &b) { return a.x*b.x + a.y*b.y + a.z*b.z; }
@@ -109,109 +116,64 @@ __device__ __forceinline__ double angle_between(const D3 &u, const D3 &v) {
     return atan2(sqrt(dot(c, c)), dot(u, v));
 }
 
-// Everything that depends on one face only, computed ONCE per face (the reference's face loops,
-// TriMesh.cpp:108-128 and :149-189, and the per-triangle part of vtkCurvatures): 16 doubles = one
-// 128-byte line per face.
-struct __align__(16) FaceRec {
-    double fn[3];      // a x b (unnormalised face normal of need_normals; 0 for a degenerate face)
-    double w[3];       // weight of fn at corner 0,1,2: 1/(|a|^2|c|^2), 1/(|b|^2|a|^2), 1/(|c|^2|b|^2) (0 if degenerate)
-    double ca[3];      // mixed Voronoi corner areas (need_pointareas)
-    double al[3];      // pi - interior angle subtracted from K at corner 0,1,2 (vtkCurvatures Gauss)
-    double area;       // triangle area as vtkTriangle::TriangleArea forms it
-    double nn[3];      // unit normal in the face's own vertex order (vtkTriangle::ComputeNormal)
-};
-
-__global__ void __launch_bounds__(128) k_face_records(const float *__restrict__ verts, const uint32_t *__restrict__ faces,
-                                                      int64_t nf, FaceRec *__restrict__ rec) {
-    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= nf) return;
-    const double PI = 3.14159265358979323846;
-    const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
-    const D3 p[3] = { ldv(verts, t[0]), ldv(verts, t[1]), ldv(verts, t[2]) };
-    FaceRec r;
-    {   // ---- vertex normal contribution (TriMesh.cpp:110-127)
-        const D3 a = sub(p[0], p[1]), bb = sub(p[1], p[2]), c = sub(p[2], p[0]);
-        const double l2a = dot(a, a), l2b = dot(bb, bb), l2c = dot(c, c);
-        r.fn[0] = r.fn[1] = r.fn[2] = 0.0; r.w[0] = r.w[1] = r.w[2] = 0.0;
-        if (l2a != 0.0 && l2b != 0.0 && l2c != 0.0) {
-            const D3 fn = cross(a, bb);
-            r.fn[0] = fn.x; r.fn[1] = fn.y; r.fn[2] = fn.z;
-            r.w[0] = 1.0 / (l2a * l2c); r.w[1] = 1.0 / (l2b * l2a); r.w[2] = 1.0 / (l2c * l2b);
-        }
-    }
-    {   // ---- mixed Voronoi corner areas (TriMesh.cpp:152-188)
-        const D3 ed[3] = { sub(p[2], p[1]), sub(p[0], p[2]), sub(p[1], p[0]) };
-        const D3 cr = cross(ed[0], ed[1]);
-        const double area = 0.5 * sqrt(dot(cr, cr));
-        const double l2[3] = { dot(ed[0], ed[0]), dot(ed[1], ed[1]), dot(ed[2], ed[2]) };
-        const double ew[3] = { l2[0] * (l2[1] + l2[2] - l2[0]), l2[1] * (l2[2] + l2[0] - l2[1]), l2[2] * (l2[0] + l2[1] - l2[2]) };
-        double *ca = r.ca;
-        if (ew[0] <= 0.0) {
-            ca[1] = -0.25 * l2[2] * area / dot(ed[0], ed[2]);
-            ca[2] = -0.25 * l2[1] * area / dot(ed[0], ed[1]);
-            ca[0] = area - ca[1] - ca[2];
-        } else if (ew[1] <= 0.0) {
-            ca[2] = -0.25 * l2[0] * area / dot(ed[1], ed[0]);
-            ca[0] = -0.25 * l2[2] * area / dot(ed[1], ed[2]);
-            ca[1] = area - ca[2] - ca[0];
-        } else if (ew[2] <= 0.0) {
-            ca[0] = -0.25 * l2[1] * area / dot(ed[2], ed[1]);
-            ca[1] = -0.25 * l2[0] * area / dot(ed[2], ed[0]);
-            ca[2] = area - ca[0] - ca[1];
-        } else {
-            const double ewscale = 0.5 * area / (ew[0] + ew[1] + ew[2]);
-            ca[0] = ewscale * (ew[1] + ew[2]); ca[1] = ewscale * (ew[2] + ew[0]); ca[2] = ewscale * (ew[0] + ew[1]);
-        }
-    }
-    {   // ---- Gaussian curvature terms and the face's own unit normal (vtkCurvatures)
-        const D3 g0 = sub(p[1], p[0]), g1 = sub(p[2], p[1]), g2 = sub(p[0], p[2]);
-        r.al[0] = PI - angle_between(g2, g0); r.al[1] = PI - angle_between(g0, g1); r.al[2] = PI - angle_between(g1, g2);
-        const D3 dn = tri_dir(p[0], p[1], p[2]);
-        r.area = 0.5 * sqrt(dot(dn, dn));
-        const D3 nn = unit_or_same(dn);
-        r.nn[0] = nn.x; r.nn[1] = nn.y; r.nn[2] = nn.z;
-    }
-    rec[g] = r;
+__global__ void __launch_bounds__(256) k_pad_verts(const float *__restrict__ verts, int64_t n, float4 *__restrict__ v4) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v4[i] = make_float4(verts[3*i], verts[3*i+1], verts[3*i+2], 0.f);
 }
 
-// Mean curvature, edge pass (vtkCurvatures::GetMeanCurvature): one thread per HALF-EDGE (g, ed) of a kept
-// face g.  If exactly one other kept face n shares the edge and n > g, Hf = 3 * len * dihedral / (A_g + A_n)
-// is stored in He[3g+ed] and hflag[3g+ed] is set; both end points pick it up in the gather.  The
-// neighbour search walks the incident list of an end point that is an original vertex (every face
-// on the edge is in that list); edges between two duplicated vertices feed dropped rows only.
-__global__ void __launch_bounds__(128) k_edge_mean(const float *__restrict__ verts, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
-                                                   const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
-                                                   const uint8_t *__restrict__ keep, const FaceRec *__restrict__ rec,
-                                                   double *__restrict__ He, uint8_t *__restrict__ hflag) {
+// One thread per CORNER / half-edge (g, i) -- 3F threads, at most two atan2 each:
+//  * al[3g+i] = pi - angle at corner i (the term vtkCurvatures::GetGaussCurvature subtracts at that vertex);
+//  * He[3g+i] = mean-curvature term of the edge (t[i], t[i+1]) of a kept face g (vtkCurvatures::GetMeanCurvature):
+//    if exactly one other kept face n shares the edge and n > g, Hf = 3 * len * dihedral / (A_g + A_n) and
+//    hflag[3g+i] = 1; both end points pick it up in the gather.  The neighbour search walks the incident list of
+//    an end point that is an original vertex (every face on the edge is in that list); edges between two
+//    duplicated vertices feed dropped rows only.  The neighbour's unit normal and area are recomputed from its
+//    own three vertices (same operations as for g: the result does not depend on who computes it).
+__global__ void __launch_bounds__(128) k_corner_terms(const float4 *__restrict__ v4, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
+                                                      const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
+                                                      const uint8_t *__restrict__ keep, int want_mean,
+                                                      double *__restrict__ al, double *__restrict__ He, uint8_t *__restrict__ hflag) {
     const int64_t he = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (he >= 3 * nf) return;
+    const double PI = 3.14159265358979323846;
     const int64_t g = he / 3;
     const int ed = (int)(he - 3 * g);
+    const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
+    const D3 p[3] = { ldv4(v4, t[0]), ldv4(v4, t[1]), ldv4(v4, t[2]) };
+    {   // corner angle: corner 0 -> (g2, g0), 1 -> (g0, g1), 2 -> (g1, g2) with g_k = p[k+1] - p[k]
+        const D3 u = ed == 0 ? sub(p[0], p[2]) : (ed == 1 ? sub(p[1], p[0]) : sub(p[2], p[1]));
+        const D3 v = ed == 0 ? sub(p[1], p[0]) : (ed == 1 ? sub(p[2], p[1]) : sub(p[0], p[2]));
+        al[he] = PI - angle_between(u, v);
+    }
     uint8_t flag = 0;
-    if (__ldg(keep + g)) {
-        const uint32_t t[3] = { __ldg(faces + 3*g), __ldg(faces + 3*g + 1), __ldg(faces + 3*g + 2) };
+    if (want_mean && __ldg(keep + g)) {
+        // (no dynamic indexing: p[] and t[] stay in registers)
         const uint32_t vl = ed == 0 ? t[0] : (ed == 1 ? t[1] : t[2]);
         const uint32_t vr = ed == 0 ? t[1] : (ed == 1 ? t[2] : t[0]);
-        const uint32_t vo = ed == 0 ? t[2] : (ed == 1 ? t[0] : t[1]);
         uint32_t a = vl, u = vr;                       // walk a's list, look for u
         if ((int64_t)a >= nv) { a = vr; u = vl; }
         if ((int64_t)a < nv) {
             const int b = __ldg(off + a), e = __ldg(off + a + 1);
             int cnt = 0, nb = -1;
             for (int j = b; j < e; j++) {
-                const int h = __ldg(adj + j) >> 2;
+                const int packed = __ldg(adj + j);
+                const int h = packed >> 2, c = packed & 3;            // a sits at corner c of face h
                 if (h == (int)g || !__ldg(keep + h)) continue;
                 const uint32_t *th = faces + 3 * (size_t)h;
-                if (__ldg(th) == u || __ldg(th + 1) == u || __ldg(th + 2) == u) { nb = h; cnt++; }
+                if (__ldg(th + (c == 2 ? 0 : c + 1)) == u || __ldg(th + (c == 0 ? 2 : c - 1)) == u) { nb = h; cnt++; }
             }
             if (cnt == 1 && nb > (int)g) {
-                const D3 ore = ldv(verts, vl), end = ldv(verts, vr), oth = ldv(verts, vo);
+                const D3 ore = ed == 0 ? p[0] : (ed == 1 ? p[1] : p[2]);
+                const D3 end = ed == 0 ? p[1] : (ed == 1 ? p[2] : p[0]);
+                const D3 oth = ed == 0 ? p[2] : (ed == 1 ? p[0] : p[1]);
                 const D3 d0 = tri_dir(ore, end, oth);
                 const D3 nfu = unit_or_same(d0);
                 const double Af0 = 0.5 * sqrt(dot(d0, d0));
-                const FaceRec *rn = rec + nb;
-                D3 nn; nn.x = rn->nn[0]; nn.y = rn->nn[1]; nn.z = rn->nn[2];
-                const double Af = Af0 + rn->area;
+                const uint32_t *tn = faces + 3 * (size_t)nb;
+                const D3 q0 = ldv4(v4, __ldg(tn)), q1 = ldv4(v4, __ldg(tn + 1)), q2 = ldv4(v4, __ldg(tn + 2));
+                const D3 dn = tri_dir(q0, q1, q2);
+                const D3 nn = unit_or_same(dn);
+                const double Af = Af0 + 0.5 * sqrt(dot(dn, dn));
                 D3 ev = sub(end, ore);
                 const double len = sqrt(dot(ev, ev));
                 if (len != 0.0) { ev.x /= len; ev.y /= len; ev.z /= len; }
@@ -227,51 +189,124 @@ __global__ void __launch_bounds__(128) k_edge_mean(const float *__restrict__ ver
     hflag[he] = flag;
 }
 
-// One thread per ORIGINAL vertex: walk the incident (face, corner) list in ascending order -- the order
-// in which the reference's sequential face loop adds to this vertex -- and sum the per-face records.
-__global__ void __launch_bounds__(MESH_T) k_vertex_gather(
-        int64_t nv, const int32_t *__restrict__ off, const int32_t *__restrict__ adj, const uint8_t *__restrict__ keep,
-        const FaceRec *__restrict__ rec, const double *__restrict__ He, const uint8_t *__restrict__ hflag,
+// Vertex gather.  A block owns VG_V consecutive ORIGINAL vertices, i.e. one contiguous range of the CSR incidence
+// array.  Phase 1: one thread per incident (face, corner) ENTRY recomputes what that corner contributes (dense: every
+// lane has an entry, whatever the vertex degrees) and leaves eight doubles in shared memory.  Phase 2: thread
+// (vertex i, quantity q) adds up quantity q over the entries of vertex i in ascending order -- the order in which the
+// reference's sequential face loop adds to that vertex, so the sums are bit-equal to the sequential oracle.
+#define VG_T 128
+#define VG_V 16           // vertices per block (x VG_Q quantities = VG_T summing threads)
+#define VG_Q 8            // doubles per entry: pn.x, pn.y, pn.z, corner area, triangle area, angle term, H term 0, H term 1
+__global__ void __launch_bounds__(VG_T) k_vertex_gather8(
+        const float4 *__restrict__ v4, const uint32_t *__restrict__ faces, int64_t nv,
+        const int32_t *__restrict__ off, const int32_t *__restrict__ adj, const uint8_t *__restrict__ keep,
+        const double *__restrict__ al, const double *__restrict__ He, const uint8_t *__restrict__ hflag,
         double *__restrict__ vn64, float *__restrict__ vn32, double *__restrict__ pa64, float *__restrict__ pa32,
         double *__restrict__ Hout, double *__restrict__ Kout) {
-    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= nv) return;
+    __shared__ double sm[VG_T][VG_Q + 1];                 // +1: the summing threads read a column, 9 doubles apart
+    __shared__ int sm_h[VG_T];
+    __shared__ int sm_off[VG_V + 1];
     const double PI = 3.14159265358979323846;
-    double pnx = 0.0, pny = 0.0, pnz = 0.0;
-    double parea = 0.0, Hsum = 0.0, Ksum = 2.0 * PI, dA = 0.0;
+    const int tid = threadIdx.x;
+    const int64_t v0 = (int64_t)blockIdx.x * VG_V;
+    const int nvb = (int)min((int64_t)VG_V, nv - v0);
+    if (tid <= VG_V) sm_off[tid] = __ldg(off + v0 + min(tid, nvb));
+    __syncthreads();
+    const int eb = sm_off[0], ee = sm_off[VG_V];
+    const int vi = tid / VG_Q, q = tid % VG_Q;            // phase 2 role: vertex vi of the block, quantity q
+    const int my_b = sm_off[vi], my_e = sm_off[vi + 1];
+    // running sum: q = 0..2 normal, 3 point area, 4 dA, 5 K (starts at 2 pi, terms are subtracted), 6 H, 7 number of H terms
+    double acc = q == 5 ? 2.0 * PI : 0.0;
     int hcnt = 0;
-    const int b = __ldg(off + v), e = __ldg(off + v + 1);
-    for (int j = b; j < e; j++) {
-        const int packed = __ldg(adj + j);
-        const int g = packed >> 2, ci = packed & 3;
-        const FaceRec *r = rec + g;
-        const double w = r->w[ci];
-        pnx += r->fn[0] * w; pny += r->fn[1] * w; pnz += r->fn[2] * w;
-        parea += r->ca[ci];
-        if (!__ldg(keep + g)) continue;
-        // edges of g that touch v, in ascending edge index: {ci, (ci+2)%3} sorted
-        const int e0 = ci == 0 ? 0 : ci - 1, e1 = ci == 0 ? 2 : ci;
-        if (__ldg(hflag + 3*(size_t)g + e0)) { Hsum += He[3*(size_t)g + e0]; hcnt++; }
-        if (__ldg(hflag + 3*(size_t)g + e1)) { Hsum += He[3*(size_t)g + e1]; hcnt++; }
-        dA += r->area;
-        Ksum -= r->al[ci];
+    for (int r0 = eb; r0 < ee; r0 += VG_T) {
+        const int j = r0 + tid;
+        double c[VG_Q] = { 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0 };
+        int myh = 0;
+        if (j < ee) {
+            const int packed = __ldg(adj + j);
+            const int g = packed >> 2, ci = packed & 3;
+            const uint32_t t[3] = { __ldcg(faces + 3*(size_t)g), __ldcg(faces + 3*(size_t)g + 1), __ldcg(faces + 3*(size_t)g + 2) };
+            const D3 p[3] = { ldv4(v4, t[0]), ldv4(v4, t[1]), ldv4(v4, t[2]) };
+            {   // ---- vertex normal contribution (TriMesh.cpp:110-127): fn = a x b, weight 1 / (|e|^2 |e'|^2) of the corner's edges
+                const D3 a = sub(p[0], p[1]), bb = sub(p[1], p[2]), cc = sub(p[2], p[0]);
+                const double l2a = dot(a, a), l2b = dot(bb, bb), l2c = dot(cc, cc);
+                if (l2a != 0.0 && l2b != 0.0 && l2c != 0.0) {
+                    const D3 fn = cross(a, bb);
+                    const double w = ci == 0 ? 1.0 / (l2a * l2c) : (ci == 1 ? 1.0 / (l2b * l2a) : 1.0 / (l2c * l2b));
+                    c[0] = fn.x * w; c[1] = fn.y * w; c[2] = fn.z * w;
+                }
+            }
+            {   // ---- mixed Voronoi corner area (TriMesh.cpp:152-188)
+                const D3 ed[3] = { sub(p[2], p[1]), sub(p[0], p[2]), sub(p[1], p[0]) };
+                const D3 cr = cross(ed[0], ed[1]);
+                const double area = 0.5 * sqrt(dot(cr, cr));
+                const double l2[3] = { dot(ed[0], ed[0]), dot(ed[1], ed[1]), dot(ed[2], ed[2]) };
+                const double ew[3] = { l2[0] * (l2[1] + l2[2] - l2[0]), l2[1] * (l2[2] + l2[0] - l2[1]), l2[2] * (l2[0] + l2[1] - l2[2]) };
+                double ca[3];
+                if (ew[0] <= 0.0) {
+                    ca[1] = -0.25 * l2[2] * area / dot(ed[0], ed[2]);
+                    ca[2] = -0.25 * l2[1] * area / dot(ed[0], ed[1]);
+                    ca[0] = area - ca[1] - ca[2];
+                } else if (ew[1] <= 0.0) {
+                    ca[2] = -0.25 * l2[0] * area / dot(ed[1], ed[0]);
+                    ca[0] = -0.25 * l2[2] * area / dot(ed[1], ed[2]);
+                    ca[1] = area - ca[2] - ca[0];
+                } else if (ew[2] <= 0.0) {
+                    ca[0] = -0.25 * l2[1] * area / dot(ed[2], ed[1]);
+                    ca[1] = -0.25 * l2[0] * area / dot(ed[2], ed[0]);
+                    ca[2] = area - ca[0] - ca[1];
+                } else {
+                    const double ewscale = 0.5 * area / (ew[0] + ew[1] + ew[2]);
+                    ca[0] = ewscale * (ew[1] + ew[2]); ca[1] = ewscale * (ew[2] + ew[0]); ca[2] = ewscale * (ew[0] + ew[1]);
+                }
+                c[3] = ci == 0 ? ca[0] : (ci == 1 ? ca[1] : ca[2]);
+            }
+            if (__ldcg(keep + g)) {   // ---- curvature terms of kept faces (vtkCurvatures)
+                const D3 dn = tri_dir(p[0], p[1], p[2]);
+                c[4] = 0.5 * sqrt(dot(dn, dn));
+                c[5] = __ldcg(al + 3*(size_t)g + ci);
+                // edges of g that touch this vertex, in ascending edge index: {ci, (ci+2)%3} sorted
+                const int e0 = ci == 0 ? 0 : ci - 1, e1 = ci == 0 ? 2 : ci;
+                if (__ldcg(hflag + 3*(size_t)g + e0)) { c[6] = __ldcg(He + 3*(size_t)g + e0); myh++; }
+                if (__ldcg(hflag + 3*(size_t)g + e1)) { c[7] = __ldcg(He + 3*(size_t)g + e1); myh++; }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < VG_Q; k++) sm[tid][k] = c[k];
+        sm_h[tid] = myh;
+        __syncthreads();
+        const int jb = max(my_b, r0) - r0, je = min(my_e, r0 + VG_T) - r0;      // this vertex's entries inside the round
+        if (q <= 4) { for (int i = jb; i < je; i++) acc += sm[i][q]; }
+        else if (q == 5) { for (int i = jb; i < je; i++) acc -= sm[i][5]; }
+        else if (q == 6) { for (int i = jb; i < je; i++) { acc += sm[i][6]; acc += sm[i][7]; } }
+        else { for (int i = jb; i < je; i++) hcnt += sm_h[i]; }
+        __syncthreads();
     }
+    // hand the sums of a vertex (8 consecutive lanes) to its first lane
+    const int base = (tid & 31) / VG_Q * VG_Q;
+    double r[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) r[k] = __shfl_sync(0xffffffffu, acc, base + k);
+    hcnt = __shfl_sync(0xffffffffu, hcnt, base + 7);
+    const int64_t v = v0 + vi;
+    if (vi >= nvb || q != 0) return;
+    double pnx = r[0], pny = r[1], pnz = r[2];
     {
         const double l = sqrt(pnx*pnx + pny*pny + pnz*pnz);
         if (l <= 0.0) { pnx = 1.0; pny = 0.0; pnz = 0.0; }
-        else { const double q = 1.0 / l; pnx *= q; pny *= q; pnz *= q; }
+        else { const double qq = 1.0 / l; pnx *= qq; pny *= qq; pnz *= qq; }
     }
     if (vn64) { vn64[3*v] = pnx; vn64[3*v+1] = pny; vn64[3*v+2] = pnz; }
     if (vn32) { vn32[3*v] = (float)pnx; vn32[3*v+1] = (float)pny; vn32[3*v+2] = (float)pnz; }
-    if (pa64) pa64[v] = parea;
-    if (pa32) pa32[v] = (float)parea;
-    if (Hout) Hout[v] = hcnt > 0 ? 0.5 * Hsum / (double)hcnt : 0.0;
-    if (Kout) Kout[v] = dA > 0.0 ? 3.0 * Ksum / dA : 0.0;
+    if (pa64) pa64[v] = r[3];
+    if (pa32) pa32[v] = (float)r[3];
+    if (Hout) Hout[v] = hcnt > 0 ? 0.5 * r[6] / (double)hcnt : 0.0;
+    if (Kout) Kout[v] = r[4] > 0.0 ? 3.0 * r[5] / r[4] : 0.0;
 }
 
 extern "C" size_t ms_mesh_properties_workspace_bytes(int64_t nv, int64_t nf) {
-    (void)nv;
-    return ms_align((size_t)(nf + 1) * sizeof(FaceRec)) + ms_align((size_t)(3 * nf + 1) * sizeof(double)) + ms_align((size_t)3 * nf + 1) + 1024;
+    // float4 vertices for up to 3 nf + nv rows are never needed: nv_all <= nv + 3 nf (every duplicated vertex is used by a face)
+    return ms_align((size_t)(nv + 3 * nf + 1) * sizeof(float4)) + 2 * ms_align((size_t)(3 * nf + 1) * sizeof(double)) + ms_align((size_t)3 * nf + 1) + 1024;
 }
 
 extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_t nv,
@@ -283,23 +318,23 @@ extern "C" int ms_mesh_properties(const float *verts_all, int64_t nv_all, int64_
                                   void *ws, size_t ws_bytes, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(nv >= 0 && nv <= nv_all && nf >= 0, "ms_mesh_properties: bad sizes");
+    MS_REQUIRE(nv_all <= nv + 3 * nf, "ms_mesh_properties: %lld vertices beyond the first %lld, but %lld faces can reference %lld at most",
+               (long long)(nv_all - nv), (long long)nv, (long long)nf, (long long)(3 * nf));
     MS_REQUIRE(csr_off && csr_adj && keep, "ms_mesh_properties: topology missing (call ms_mesh_topology first)");
     MS_REQUIRE(ws_bytes >= ms_mesh_properties_workspace_bytes(nv, nf), "ms_mesh_properties: workspace too small");
     if (nv == 0) return 0;
     MsArena A(ws, ws_bytes);
-    FaceRec *rec = A.take<FaceRec>(nf + 1);
-    double *He = A.take<double>(3 * nf + 1);
+    float4 *v4 = A.take<float4>(nv + 3 * nf + 1);
+    double *al = A.take<double>(3 * nf + 1), *He = A.take<double>(3 * nf + 1);
     uint8_t *hflag = A.take<uint8_t>(3 * nf + 1);
-    const bool want_curv = mean_curv != NULL || gaus_curv != NULL;
+    MS_K("pad_verts", s); k_pad_verts<<<ms_blocks(nv_all, 256), 256, 0, s>>>(verts_all, nv_all, v4);
     if (nf > 0) {
-        MS_K("face_records", s); k_face_records<<<ms_blocks(nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, rec);
-        if (mean_curv) { MS_K("edge_mean", s); k_edge_mean<<<ms_blocks(3 * nf, 128), 128, 0, s>>>(verts_all, faces_all, nf, nv, csr_off, csr_adj, keep, rec, He, hflag); }
-        else MS_CUDA(cudaMemsetAsync(hflag, 0, (size_t)nf * 3, s));
+        MS_K("corner_terms", s);
+        k_corner_terms<<<ms_blocks(3 * nf, 128), 128, 0, s>>>(v4, faces_all, nf, nv, csr_off, csr_adj, keep, mean_curv != NULL, al, He, hflag);
     }
-    (void)want_curv;
-    MS_K("vertex_gather", s);
-    k_vertex_gather<<<ms_blocks(nv, MESH_T), MESH_T, 0, s>>>(nv, csr_off, csr_adj, keep, rec, He, hflag,
-                                                             vnormals_f64, vnormals_f32, pareas_f64, pareas_f32, mean_curv, gaus_curv);
+    MS_K("vertex_gather8", s);
+    k_vertex_gather8<<<ms_blocks(nv, VG_V), VG_T, 0, s>>>(v4, faces_all, nv, csr_off, csr_adj, keep, al, He, hflag,
+                                                                     vnormals_f64, vnormals_f32, pareas_f64, pareas_f32, mean_curv, gaus_curv);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
     return 0;
