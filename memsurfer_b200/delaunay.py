@@ -21,6 +21,23 @@ class IncompleteCells(RuntimeError):
     box) or exactly cocircular points.  Callers fall back to the host triangulation."""
 
 
+def wrap_into_box(xy, b0, b1, out=None):
+    """TriMesh::wrap_vertices (memsurfer/src/TriMesh.cpp:462-491, called at TriMesh_cgal.cpp:191): x, y folded into
+    [box0, box1) by at most one period, float32 arithmetic.  Returns an (n, 3) float32 array with z = 0."""
+    xy = np.asarray(xy)[:, :2]
+    b0, b1 = np.asarray(b0, np.float32)[:2], np.asarray(b1, np.float32)[:2]
+    w = (b1 - b0).astype(np.float32)
+    pts = _lib.pinned_empty((xy.shape[0], 3), np.float32) if out is None else out
+    pts[:, :2] = xy
+    for d in range(2):
+        lo = pts[:, d] < b0[d]
+        pts[lo, d] += w[d]
+        hi = pts[:, d] >= b1[d]
+        pts[hi, d] -= w[d]
+    pts[:, 2] = 0.0
+    return pts
+
+
 def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0.2, split=False):
     """xy (V,2) planar points, box0/box1 the periodic box.  Returns (dfaces (F,3) int64, doffs (F,3,2) int8);
     faces are counter-clockwise and ordered by their smallest vertex id.  split=True: returns instead
@@ -34,15 +51,7 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
     b0 = np.asarray(box0, np.float32)[:2]
     b1 = np.asarray(box1, np.float32)[:2]
     w = (b1 - b0).astype(np.float32)
-    pts = _lib.pinned_empty((V, 3), np.float32)
-    # TriMesh::wrap_vertices (TriMesh_cgal.cpp:191): into [box0, box1)
-    pts[:, :2] = xy
-    for d in range(2):
-        lo = pts[:, d] < b0[d]
-        pts[lo, d] += w[d]
-        hi = pts[:, d] >= b1[d]
-        pts[hi, d] -= w[d]
-    pts[:, 2] = 0.0
+    pts = wrap_into_box(xy, b0, b1)
     st = _lib.stream_ptr(dev)
     pd = _lib.h2d(pts, dev)
     cap = int(L.ms_pointset_capacity(V, 1))

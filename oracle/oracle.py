@@ -78,6 +78,12 @@ def ref():
         if hasattr(R, "msref_need_neighbors"):
             R.msref_need_neighbors.restype = C.c_int64
             R.msref_need_neighbors.argtypes = [_f32p, C.c_int, _u32p, C.c_int, _i32p, C.c_int64]
+        if hasattr(R, "msref_trim_periodic"):
+            _i8p = np.ctypeslib.ndpointer(np.int8, flags="C_CONTIGUOUS")
+            _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+            R.msref_trim_periodic.argtypes = [_f32p, C.c_int, C.c_int, _f32p, C.c_int, _i32p, _i8p, C.c_int,
+                                              _i32p, _i32p, _i32p, _i32p, _f32p, _i64p]
+            R.msref_wrap_vertices.argtypes = [_f32p, C.c_int, C.c_int, _f32p, C.c_int, C.c_int, _f32p]
         _REF = R
     return _REF
 
@@ -293,4 +299,37 @@ def ref_kde_geodesic(verts, faces, ids, sigma, get_counts, bbox=None):
     rc = R.msref_kde_geodesic(verts, verts.shape[0], faces, faces.shape[0], int(bool(get_counts)), float(sigma),
                               int(bbox is not None), bb, 6, ids, ids.shape[0], out)
     assert rc == 0
+    return out
+
+
+def ref_trim_periodic(verts, dfaces, doffs, bbox0, bbox1):
+    """The COMPILED reference's TriMesh::trim_periodicDelaunay (TriMesh.cpp:493-575) on a given periodic Delaunay
+    (mDelaunayFaces set through the opened class, oracle/ref_shim.cpp): dict with the five arrays of
+    trimesh.py:421-436 in the reference's dtypes."""
+    R = ref()
+    v = _f32(verts)
+    nv, dim = v.shape
+    bb = np.ascontiguousarray(np.concatenate([np.asarray(bbox0, np.float32)[:dim], np.asarray(bbox1, np.float32)[:dim]]), np.float32)
+    df = np.ascontiguousarray(dfaces, np.int32).reshape(-1, 3)
+    do = np.ascontiguousarray(doffs, np.int8).reshape(-1, 3, 2)
+    nf = df.shape[0]
+    faces, pf, tf = (np.zeros((nf, 3), np.int32) for _ in range(3))
+    dids = np.zeros(3 * nf, np.int32)
+    dverts = np.zeros((3 * nf, dim), np.float32)
+    counts = np.zeros(3, np.int64)
+    rc = R.msref_trim_periodic(v, nv, dim, bb, bb.shape[0], df, do, nf, faces, pf, tf, dids, dverts, counts)
+    assert rc == 0, rc
+    n0, n1, n2 = (int(x) for x in counts)
+    return dict(faces=faces[:n0].astype(np.uint32), periodic_faces=pf[:n1].astype(np.uint32), trimmed_faces=tf[:n1].astype(np.uint32),
+                duplicated_vidxs=dids[:n2].astype(np.uint32), duplicated_verts=dverts[:n2].copy())
+
+
+def ref_wrap_vertices(verts, bbox0, bbox1, wrap_dim=2):
+    """The compiled reference's TriMesh::wrap_vertices (TriMesh.cpp:462-491)."""
+    R = ref()
+    v = _f32(verts)
+    nv, dim = v.shape
+    bb = np.ascontiguousarray(np.concatenate([np.asarray(bbox0, np.float32)[:dim], np.asarray(bbox1, np.float32)[:dim]]), np.float32)
+    out = np.zeros_like(v)
+    assert R.msref_wrap_vertices(v, nv, dim, bb, bb.shape[0], int(wrap_dim), out) == 0
     return out

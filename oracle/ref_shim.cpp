@@ -9,7 +9,14 @@
 //   need_normals(bool)             memsurfer/src/TriMesh.hpp:346
 //   need_pointareas(bool)          memsurfer/src/TriMesh.hpp:379
 //   kde(name,type,get_counts,...)  memsurfer/src/TriMesh_kde.cpp:443
+// trim_periodicDelaunay (TriMesh.hpp:214) and its input mDelaunayFaces (TriMesh.hpp:104) are private and are only fed by
+// the CGAL path, which cannot compile here: open the class for this driver.  The standard
+// headers were already included by ref_stub.h, so the macro only touches the reference's own headers.
+#define private public
+#define protected public
 #include "TriMesh.hpp"
+#undef private
+#undef protected
 #include "DensityKernels.hpp"
 #include "DistanceKernels.hpp"
 #include <cstring>
@@ -95,6 +102,49 @@ int msref_kde(const float *verts, int nv, int type, int get_counts, float sigma,
                             r = &m.kde("d", type, get_counts != 0, gk, dk, vids, false); }
         }
         std::memcpy(out_density, r->data(), sizeof(float)*r->size());
+        return 0;
+    } catch (const std::exception &e) { std::cerr << e.what(); return 1; }
+}
+
+// TriMesh::trim_periodicDelaunay (TriMesh.cpp:493-575) on a given periodic Delaunay: dfaces (nf,3) original vertex ids,
+// doffs (nf,3,2) periodic offsets in {-1,0,1}; the mesh's own bbox (n = 4 for 2-D, 6 for 3-D vertices).  Outputs sized
+// for the worst case by the caller: faces / pfaces / tfaces (nf,3), dup_ids (3 nf), dup_verts (3 nf, dim).
+// counts = {#faces, #periodic faces (= #trimmed faces), #duplicated vertices}.
+int msref_trim_periodic(const float *verts, int nv, int dim, const float *bbox, int nbbox,
+                        const int32_t *dfaces, const int8_t *doffs, int nf,
+                        int32_t *faces, int32_t *pfaces, int32_t *tfaces, int32_t *dup_ids, float *dup_verts, long long *counts) {
+    try {
+        TriMesh m(const_cast<float*>(verts), nv, dim);
+        m.set_periodic();
+        m.set_bbox(const_cast<float*>(bbox), nbbox);
+        m.mDelaunayFaces.resize(nf);
+        for (int f = 0; f < nf; f++) {
+            m.mDelaunayFaces[f].resize(3);
+            for (int d = 0; d < 3; d++)
+                m.mDelaunayFaces[f][d] = PeriodicVertex((TypeIndex)dfaces[3*f+d], doffs[6*f+2*d], doffs[6*f+2*d+1]);
+        }
+        m.trim_periodicDelaunay(false);
+        const std::vector<TypeIndexI> a = m.get_faces(), b = m.periodic_faces(false), c = m.trimmed_faces(false), d = m.duplicate_ids();
+        const std::vector<TypeFunction> e = m.duplicated_vertices(false);
+        std::memcpy(faces, a.data(), sizeof(int32_t) * a.size());
+        std::memcpy(pfaces, b.data(), sizeof(int32_t) * b.size());
+        std::memcpy(tfaces, c.data(), sizeof(int32_t) * c.size());
+        std::memcpy(dup_ids, d.data(), sizeof(int32_t) * d.size());
+        std::memcpy(dup_verts, e.data(), sizeof(float) * e.size());
+        counts[0] = (long long)a.size() / 3; counts[1] = (long long)b.size() / 3; counts[2] = (long long)d.size();
+        return (b.size() == c.size() && e.size() == d.size() * (size_t)dim) ? 0 : 2;
+    } catch (const std::exception &e) { std::cerr << e.what(); return 1; }
+}
+
+// TriMesh::wrap_vertices (TriMesh.cpp:462-491): x,y (dim = 2) folded into [box0, box1), in place on a copy.
+int msref_wrap_vertices(const float *verts, int nv, int dim, const float *bbox, int nbbox, int wrap_dim, float *out) {
+    try {
+        TriMesh m(const_cast<float*>(verts), nv, dim);
+        m.set_periodic();
+        m.set_bbox(const_cast<float*>(bbox), nbbox);
+        m.wrap_vertices((uint8_t)wrap_dim);
+        const std::vector<TypeFunction> v = m.get_vertices();
+        std::memcpy(out, v.data(), sizeof(float) * v.size());
         return 0;
     } catch (const std::exception &e) { std::cerr << e.what(); return 1; }
 }
