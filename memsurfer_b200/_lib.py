@@ -134,7 +134,7 @@ def pinned_empty(shape, dtype):
 
 
 _copy_pool = None
-COPY_THREADS = int(os.environ.get("MS_COPY_THREADS", "4"))
+COPY_THREADS = 4             # host threads that share one large staging copy
 COPY_MIN_BYTES = 1 << 20
 
 

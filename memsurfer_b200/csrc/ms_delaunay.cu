@@ -17,26 +17,103 @@
 // (rare: very uneven density); a cell that cannot be closed inside the ghost layer is counted in
 // *n_incomplete (the caller falls back to its host producer).
 //
-// Arithmetic: fp64 on float32 inputs, compiled without FMA contraction.  The Delaunay triangulation is
-// unique unless four points are cocircular; inputs that close to degenerate (|incircle| below fp64 rounding)
-// may come out with a different diagonal than an exact-predicate code would choose.
+// Arithmetic: fp64 on float32 inputs, compiled without FMA contraction.  Whether a bisector cuts off a cell vertex is
+// the in-circle predicate of four points; when the fp64 value of that test is within 1e-10 of zero (relative to its
+// terms) it is re-evaluated in double-double arithmetic on the exact coordinate differences (~104 bits: exact for
+// float32 inputs whose differences carry <= 26 bits, which includes every lattice) and an exact ZERO -- four or more
+// cocircular points -- is decided by the symbolic perturbation CGAL's Delaunay_triangulation_2 uses
+// (side_of_oriented_circle with `perturb`: points ordered lexicographically, the largest one is pushed off the
+// circle first [recalled, CGAL 4.13; CGAL itself is not in the tree]).  The answer is a function of the four points
+// only, so the four cells that share a degenerate Voronoi vertex agree and the stars always glue to a triangulation.
 #include "ms_common.cuh"
+
+// ---- double-double helpers (explicit fma(): this file is built --fmad=false, which only stops contraction)
+struct dd { double hi, lo; };
+__device__ __forceinline__ dd dd_two_sum(double a, double b) { const double s = a + b, bb = s - a; dd r; r.hi = s; r.lo = (a - (s - bb)) + (b - bb); return r; }
+__device__ __forceinline__ dd dd_two_prod(double a, double b) { dd r; r.hi = a * b; r.lo = fma(a, b, -r.hi); return r; }
+__device__ __forceinline__ dd dd_add(dd a, dd b) {
+    dd s = dd_two_sum(a.hi, b.hi); const dd t = dd_two_sum(a.lo, b.lo);
+    s.lo += t.hi; s = dd_two_sum(s.hi, s.lo); s.lo += t.lo; return dd_two_sum(s.hi, s.lo);
+}
+__device__ __forceinline__ dd dd_neg(dd a) { a.hi = -a.hi; a.lo = -a.lo; return a; }
+__device__ __forceinline__ dd dd_mul(dd a, dd b) {
+    dd p = dd_two_prod(a.hi, b.hi);
+    p.lo += a.hi * b.lo + a.lo * b.hi;
+    return dd_two_sum(p.hi, p.lo);
+}
+__device__ __forceinline__ int dd_sign(dd a) { return a.hi > 0.0 ? 1 : (a.hi < 0.0 ? -1 : (a.lo > 0.0 ? 1 : (a.lo < 0.0 ? -1 : 0))); }
+// sign of the orientation of (a, b, c): > 0 counter-clockwise
+__device__ __forceinline__ int dl_orient(double ax, double ay, double bx, double by, double cx, double cy) {
+    const double ux = bx - ax, uy = by - ay, vx = cx - ax, vy = cy - ay;     // exact (float32-valued inputs)
+    return dd_sign(dd_add(dd_two_prod(ux, vy), dd_neg(dd_two_prod(uy, vx))));
+}
+// sign of the in-circle determinant: > 0 iff d lies inside the circle through a, b, c (counter-clockwise)
+__device__ __forceinline__ int dl_incircle(double ax, double ay, double bx, double by, double cx, double cy, double dx, double dy) {
+    const double x0 = ax - dx, y0 = ay - dy, x1 = bx - dx, y1 = by - dy, x2 = cx - dx, y2 = cy - dy;   // exact
+    const dd l0 = dd_add(dd_two_prod(x0, x0), dd_two_prod(y0, y0));
+    const dd l1 = dd_add(dd_two_prod(x1, x1), dd_two_prod(y1, y1));
+    const dd l2 = dd_add(dd_two_prod(x2, x2), dd_two_prod(y2, y2));
+    const dd m0 = dd_add(dd_two_prod(x1, y2), dd_neg(dd_two_prod(y1, x2)));
+    const dd m1 = dd_add(dd_two_prod(x2, y0), dd_neg(dd_two_prod(y2, x0)));
+    const dd m2 = dd_add(dd_two_prod(x0, y1), dd_neg(dd_two_prod(y0, x1)));
+    return dd_sign(dd_add(dd_add(dd_mul(l0, m0), dd_mul(l1, m1)), dd_mul(l2, m2)));
+}
+// lexicographic (x, y, index) order of two points
+__device__ __forceinline__ bool dl_lex_less(const float *__restrict__ pts, int64_t i, int64_t j) {
+    const float xi = pts[3*i], xj = pts[3*j];
+    if (xi != xj) return xi < xj;
+    const float yi = pts[3*i + 1], yj = pts[3*j + 1];
+    if (yi != yj) return yi < yj;
+    return i < j;
+}
+// is q inside the circle through (p0, p1, p2), counter-clockwise and not collinear -- ties decided by perturbation
+__device__ __forceinline__ bool dl_inside_sos(const float *__restrict__ pts, int64_t p0, int64_t p1, int64_t p2, int64_t q) {
+    const double x0 = pts[3*p0], y0 = pts[3*p0+1], x1 = pts[3*p1], y1 = pts[3*p1+1], x2 = pts[3*p2], y2 = pts[3*p2+1], xq = pts[3*q], yq = pts[3*q+1];
+    const int s = dl_incircle(x0, y0, x1, y1, x2, y2, xq, yq);
+    if (s != 0) return s > 0;
+    // cocircular: walk the four points from the lexicographically largest down (CGAL: 2 iterations are enough)
+    int64_t o[4] = { p0, p1, p2, q };
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+#pragma unroll
+        for (int b = 0; b < 3 - a; b++) if (dl_lex_less(pts, o[b + 1], o[b])) { const int64_t t = o[b]; o[b] = o[b + 1]; o[b + 1] = t; }
+    for (int i = 3; i > 0; i--) {
+        const int64_t w = o[i];
+        if (w == q) return false;                                   // ON_NEGATIVE_SIDE: outside
+        int r = 0;
+        if (w == p2) r = dl_orient(x0, y0, x1, y1, xq, yq);
+        else if (w == p1) r = dl_orient(x0, y0, xq, yq, x2, y2);
+        else r = dl_orient(xq, yq, x1, y1, x2, y2);
+        if (r != 0) return r > 0;
+    }
+    return false;
+}
 
 #define DL_MAXV 24          // cell vertices kept per thread (a Voronoi cell has ~6)
 
 struct DlCell { double x[DL_MAXV], y[DL_MAXV]; int g[DL_MAXV]; int n; };
 
-// clip the convex cell (counter-clockwise) with the half-plane {v : v.d <= |d|^2/2}; the new edge gets generator q
-__device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q) {
+// clip the convex cell (counter-clockwise) with the half-plane {v : v.d <= |d|^2/2}; the new edge gets generator q.
+// Cell vertex i is the circumcentre of (p, g[i-1], g[i]) (counter-clockwise): it is cut off iff q lies inside that
+// circle.  The fp64 value decides unless it is within 1e-10 (relative) of zero; then the robust predicate does.
+__device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q, const float *__restrict__ pts, int64_t p) {
     const double h = 0.5 * (dx * dx + dy * dy);
     double s[DL_MAXV];
-    bool any_out = false;
-    for (int i = 0; i < c.n; i++) { s[i] = c.x[i] * dx + c.y[i] * dy - h; any_out |= s[i] > 0.0; }
-    if (!any_out) return true;
+    unsigned outm = 0u;
+    for (int i = 0; i < c.n; i++) {
+        const double tx = c.x[i] * dx, ty = c.y[i] * dy;
+        s[i] = tx + ty - h;
+        bool out = s[i] > 0.0;
+        const int ga = c.g[i == 0 ? c.n - 1 : i - 1], gb = c.g[i];
+        if (ga >= 0 && gb >= 0 && ga != gb && fabs(s[i]) <= 1e-10 * (fabs(tx) + fabs(ty) + h))
+            out = dl_inside_sos(pts, p, ga, gb, q);
+        outm |= (unsigned)out << i;
+    }
+    if (!outm) return true;
     DlCell o; o.n = 0;
     for (int i = 0; i < c.n; i++) {
         const int j = i + 1 == c.n ? 0 : i + 1;
-        const bool in_i = !(s[i] > 0.0), in_j = !(s[j] > 0.0);
+        const bool in_i = !((outm >> i) & 1u), in_j = !((outm >> j) & 1u);
         if (in_i) {
             if (o.n >= DL_MAXV) return false;
             o.x[o.n] = c.x[i]; o.y[o.n] = c.y[i];
@@ -44,7 +121,8 @@ __device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q) 
             o.n++;
         }
         if (in_i != in_j) {
-            const double t = s[i] / (s[i] - s[j]);
+            double t = s[i] / (s[i] - s[j]);                  // a predicate overruled by the robust test leaves t outside [0,1]
+            t = (t >= 0.0 && t <= 1.0) ? t : (in_i ? 1.0 : 0.0);
             if (o.n >= DL_MAXV) return false;
             o.x[o.n] = c.x[i] + t * (c.x[j] - c.x[i]); o.y[o.n] = c.y[i] + t * (c.y[j] - c.y[i]);
             // leaving the half-plane: the next edge runs along the bisector (generator q);
@@ -69,21 +147,23 @@ __device__ __forceinline__ double dl_radius2(const DlCell &c) {
 // thread scans ALL m points for those (order does not matter: the cell is an intersection of half-planes).
 // reach2 = (width of the ghost layer)^2: a cell whose security disc leaves the ghost layer could be cut by a
 // periodic image that was never made -- reported as not closed.
+__device__ __forceinline__ void dl_square(DlCell &c, double R) {
+    c.n = 4;
+    c.x[0] = -R; c.y[0] = -R; c.x[1] = R; c.y[1] = -R; c.x[2] = R; c.y[2] = R; c.x[3] = -R; c.y[3] = R;
+    c.g[0] = c.g[1] = c.g[2] = c.g[3] = -1;
+}
 __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int32_t *__restrict__ nbr, int k1, int64_t p, int64_t m,
                                        double reach2, DlCell &c) {
     const double px = (double)pts[3*p], py = (double)pts[3*p + 1];
     const int32_t *row = nbr + p * k1;
-    // start from a square that contains every bisector of the list: half side = distance to the last neighbour
+    // fast path: start from a square that contains every bisector of the list (half side = distance to the last neighbour)
     double far2 = 0.0;
     {
         const int32_t q = row[k1 - 1];
         const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
         far2 = dx * dx + dy * dy;
     }
-    const double R = sqrt(far2);
-    c.n = 4;
-    c.x[0] = -R; c.y[0] = -R; c.x[1] = R; c.y[1] = -R; c.x[2] = R; c.y[2] = R; c.x[3] = -R; c.y[3] = R;
-    c.g[0] = c.g[1] = c.g[2] = c.g[3] = -1;
+    dl_square(c, sqrt(far2));
     bool complete = false;
     double r2 = 2.0 * far2;
     for (int j = 0; j < k1; j++) {
@@ -91,11 +171,25 @@ __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int3
         if ((int64_t)q == p) continue;
         const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
         if (dx * dx + dy * dy > 4.0 * r2) { complete = true; break; }
-        if (!dl_clip(c, dx, dy, q)) return 0;
+        if (!dl_clip(c, dx, dy, q, pts, p)) return 0;
         r2 = dl_radius2(c);
     }
-    // list exhausted: every point outside it is at least as far as the last neighbour
-    if (!complete && !(far2 > 4.0 * r2)) {
+    bool open = false;
+    for (int i = 0; i < c.n; i++) open |= c.g[i] < 0;
+    // the list ended before the security radius was reached, or part of the starting square is still there (all
+    // listed neighbours on one side: the edge of a cluster, the rim of a void): start again from the largest square a
+    // closable cell fits in (half side = half the ghost layer), clip with the whole list, then scan ALL points for
+    // the cutters beyond it (order does not matter: the cell is an intersection of half-planes)
+    if ((!complete && !(far2 > 4.0 * r2)) || open) {
+        dl_square(c, 0.5001 * sqrt(reach2));
+        r2 = dl_radius2(c);
+        for (int j = 0; j < k1; j++) {
+            const int32_t q = row[j];
+            if ((int64_t)q == p) continue;
+            const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
+            if (!dl_clip(c, dx, dy, q, pts, p)) return 0;
+        }
+        r2 = dl_radius2(c);
         for (int64_t q = 0; q < m; q++) {
             if (q == p) continue;
             const double dx = (double)pts[3*q] - px, dy = (double)pts[3*q + 1] - py;
@@ -106,7 +200,7 @@ __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int3
                 for (int j = 0; j < k1; j++) used |= (int64_t)row[j] == q;
                 if (used) continue;
             }
-            if (!dl_clip(c, dx, dy, (int)q)) return 0;
+            if (!dl_clip(c, dx, dy, (int)q, pts, p)) return 0;
             r2 = dl_radius2(c);
         }
     }

@@ -17,8 +17,12 @@ LOGGER = logging.getLogger(__name__)
 
 
 class IncompleteCells(RuntimeError):
-    """The cell-by-cell construction does not apply: cells not closed inside the ghost layer (too few points for the
-    box) or exactly cocircular points.  Callers fall back to the host triangulation."""
+    """The cell-by-cell construction could not finish: Voronoi cells that do not close inside the ghost layer (too few
+    points for the box; `retry` = a wider ghost layer may help) or stars that do not glue to a triangulation."""
+
+    def __init__(self, msg, retry=False):
+        super().__init__(msg)
+        self.retry = retry
 
 
 def wrap_into_box(xy, b0, b1, out=None):
@@ -77,11 +81,10 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
                                       dfaces.data_ptr(), doffs.data_ptr(), fcap,
                                       C.byref(nf), C.byref(bad), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_periodic')
     if bad.value < 0:
-        raise IncompleteCells('the Voronoi cells do not add up to a triangulation (exactly cocircular points, '
-                              'e.g. an unperturbed lattice)')
+        raise IncompleteCells('the Voronoi cells do not add up to a triangulation of the torus')
     if bad.value > 0:
         raise IncompleteCells(f'{bad.value} Voronoi cells cannot be closed inside the ghost layer '
-                              f'({blayer} box widths): too few points for this box')
+                              f'({blayer} box widths): too few points for this box', retry=blayer < 0.4)
     F = int(nf.value)
     if not split:
         return _lib.d2h(dfaces[:F]).astype(np.int64), _lib.d2h(doffs[:F])

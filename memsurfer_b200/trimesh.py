@@ -11,7 +11,6 @@ Extras that the reference does not have: `attributes_f64` (fp64 twins of the flo
 `to_device()` (pre-stage inputs in HBM) and `*_device` accessors returning torch tensors.
 """
 import logging
-import os
 
 import numpy as np
 import torch
@@ -139,8 +138,22 @@ class TriMesh(object):
         self.set_periodic_triangulation(t['faces'], t['periodic_faces'], t['trimmed_faces'],
                                         t['duplicated_vidxs'], t['duplicated_verts'])
 
+    def set_periodic_delaunay(self, dfaces, doffs):
+        """Inject a periodic Delaunay made by another producer (CGAL in the reference, `synth.periodic_delaunay` in the
+        CPU tests): dfaces (F,3) original vertex ids, doffs (F,3,2) periodic offsets -- the PeriodicVertex triples of
+        TriMesh_cgal.cpp:223-233.  Trimmed with this mesh's bbox like copy_periodicDelaunay (TriMesh.hpp:301-304)."""
+        if not self.periodic:
+            raise ValueError(f'{self.tag()} is not periodic')
+        self._delaunay = (np.asarray(dfaces, np.int64).reshape(-1, 3), np.asarray(doffs, np.int8).reshape(-1, 3, 2))
+        self._retrim()
+
     def compute_delaunay(self):
-        """HOST stand-in for TriMesh::delaunay / periodicDelaunay (CGAL is the reference producer)."""
+        """TriMesh::delaunay / periodicDelaunay (memsurfer/src/TriMesh_cgal.cpp:111-281; CGAL in the reference).  Periodic
+        meshes are triangulated on the GPU (memsurfer_b200.delaunay: ghost images -> k-NN -> one Voronoi cell per point,
+        robust in-circle predicate).  Cells that do not close inside the 0.2-box-width ghost layer (very sparse or
+        very uneven point sets) get one more try with a 0.45-box-width layer; after that IncompleteCells is raised --
+        there is no host triangulation behind this call.  Non-periodic meshes (not on the per-frame path of the
+        reference's drivers, which are periodic) use the planar host producer `synth.planar_delaunay`."""
         if self.faces is not None:
             return
         if not self.periodic:
@@ -149,16 +162,18 @@ class TriMesh(object):
             return
         if self.bbox is None:
             raise ValueError(f'{self.tag()} periodic Delaunay needs a bbox')
+        _lib.require_cuda()
+        from .delaunay import periodic_delaunay_device, IncompleteCells
         self._delaunay = None
-        if torch.cuda.is_available() and os.environ.get('MS_DELAUNAY', 'device') != 'host':
-            from .delaunay import periodic_delaunay_device, IncompleteCells
+        with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
             try:
-                with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
-                    self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device, split=True)
+                self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device, split=True)
             except IncompleteCells as e:
-                LOGGER.warning(f'{self.tag()} {e}: falling back to the host triangulation')
-        if self._delaunay is None:
-            self._delaunay = synth.periodic_delaunay(self.vertices[:, :2], self.bbox[0], self.bbox[1])
+                if not e.retry:
+                    raise
+                LOGGER.info(f'{self.tag()} {e}: once more with a 0.45-box-width ghost layer')
+                self._delaunay = periodic_delaunay_device(self.vertices[:, :2], self.bbox[0], self.bbox[1], self.device, split=True,
+                                                          blayer=0.45, knbrs=31)
         self._retrim()
 
     def copy_triangulation(self, mesh):

@@ -15,7 +15,7 @@ def _periodic_mesh(n=900, seed=3, dim=3):
     pts, _, bbox = synth.make_leaflet(n, seed=seed)
     m = TriMesh(pts[:, :2], periodic=True)
     m.set_bbox(bbox[0, :2], bbox[1, :2])
-    m.compute_delaunay()
+    m.set_periodic_delaunay(*synth.periodic_delaunay(pts[:, :2], bbox[0], bbox[1]))      # host producer: no GPU in these tests
     if dim == 2:
         return m, bbox
     m3 = TriMesh(pts, periodic=True)
