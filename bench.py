@@ -66,6 +66,8 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="skip the all-pairs, trajectory, type-3 and producer side measurements")
     ap.add_argument("--trajectory-frames", type=int, default=512, help="total frames of the configs[3] measurement (all ranks)")
     ap.add_argument("--no-pin", action="store_true", help="do not bind the rank to its own host cores")
+    ap.add_argument("--single-stream", action="store_true", help="device arm: the two leaflets of a frame one after the other "
+                                                                 "(default: each on its own stream)")
     return ap.parse_args()
 
 
@@ -297,7 +299,8 @@ def workload_config(args, V):
                         f"sigmas {SIGMAS}, labels all + {len(FRACTIONS)} types, get_nlipdis",
             "kde": "all pairs" if args.kde_cutoff <= 0 else f"cut-off {args.kde_cutoff} sigma (cell list)",
             "l2": "flushed between steps (512 MiB device write)",
-            "parallelism": f"frames sharded over {args.gpus} GPU(s), 1 frame per rank per step",
+            "parallelism": f"frames sharded over {args.gpus} GPU(s), 1 frame per rank per step; the two leaflets of a frame on "
+                           + ("one stream" if args.single_stream else "two streams"),
             "mesh_producer": "GPU periodic Delaunay + trim (TriMesh.compute_delaunay), untimed"}
 
 
@@ -349,11 +352,27 @@ def main():
     frames = [LeafletFrame(lf["points"], lf["labels"], lf["bbox"], new_mesh(lf, device), device=device) for lf in leaflets]
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
 
+    side_streams = None if args.single_stream else [torch.cuda.Stream(device=device) for _ in frames]
+    use_streams = [True]
+
     def step_local(cutoff=None):
+        # the two leaflets of a frame share nothing (examples/ex_3lipid.py:165-166): with --leaflet-streams each runs on
+        # its own stream (forked from and joined back into the timing stream), else one after the other
         recs = []
-        for fr in frames:
-            fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
-            recs.append(fr.summary())
+        main = torch.cuda.current_stream(device)
+        for i, fr in enumerate(frames):
+            if side_streams is None or not use_streams[0]:
+                fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
+                recs.append(fr.summary())
+                continue
+            side_streams[i].wait_stream(main)
+            with torch.cuda.stream(side_streams[i]):
+                fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
+                recs.append(fr.summary())
+                recs[-1].record_stream(main)
+        if side_streams is not None and use_streams[0]:
+            for st_ in side_streams:
+                main.wait_stream(st_)
         return torch.stack(recs)
 
     def step_device():
@@ -418,7 +437,9 @@ def main():
     value = world * 1e3 / ms_per_step
     # second, shorter pass with an event around every kernel launch: the per-kernel times behind the rooflines
     psteps = max(1, min(args.steps, 5))
+    use_streams[0] = False                      # one stream: the per-kernel events must follow each other
     ptotal_ms, _, prof, _ = timed(step_device, 1, psteps, profile=True)
+    use_streams[0] = True
     pinfo = [dict(m=fr.info['m'], cands=fr.info['knn_candidates'], rounds=fr.info['mst_rounds']) for fr in frames]
 
     # ---- end to end through the drop-in API, from page-locked host arrays
@@ -684,12 +705,27 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
             sets.append([LeafletFrame(lf["points"], lf["labels"], lf["bbox"], new_mesh(lf, device), device=device) for lf in lfs])
         Vt = sets[0][0].nv
 
+        streams = None if args.single_stream else [torch.cuda.Stream(device=device) for _ in range(2)]
+
         def run_all():
             recs = []
+            main = torch.cuda.current_stream(device)
+            if streams is not None:
+                for st_ in streams:
+                    st_.wait_stream(main)
             for i in range(len(mine)):
-                for fr in sets[i % ndistinct]:
-                    fr.run(SIGMAS, 18, args.kde_cutoff)
-                    recs.append(fr.summary())
+                for li, fr in enumerate(sets[i % ndistinct]):       # leaflet li of every frame on stream li
+                    if streams is None:
+                        fr.run(SIGMAS, 18, args.kde_cutoff)
+                        recs.append(fr.summary())
+                    else:
+                        with torch.cuda.stream(streams[li]):
+                            fr.run(SIGMAS, 18, args.kde_cutoff)
+                            recs.append(fr.summary())
+                            recs[-1].record_stream(main)
+            if streams is not None:
+                for st_ in streams:
+                    main.wait_stream(st_)
             rec = torch.stack(recs)
             return gather_summaries(rec) if world > 1 else rec
 
