@@ -279,6 +279,16 @@ size_t ms_delaunay_split_workspace_bytes(int64_t nf);
 int ms_delaunay_split(const int32_t *dfaces, const int8_t *doffs, int64_t nf, uint32_t *full, int32_t *pfaces, int8_t *poffs,
                       int64_t *nfull, void *ws, size_t ws_bytes, void *stream);
 
+/* Second step of TriMesh::trim_periodicDelaunay (TriMesh.cpp:513-560): the crossing faces (pfaces / poffs from
+ * ms_delaunay_split) re-indexed onto duplicated vertices numbered in order of first appearance in the (face, corner)
+ * scan, as the reference's std::find / push_back loop numbers them.  corner_verts (3 nf, dim) f32 = this mesh's coordinates of
+ * the original vertex of every corner, dim 2|3; nv = number of original vertices; box widths of THIS mesh as float32.  tfaces (nf,3) u32, dup_ids (3 nf) u32 = original vertex of every duplicate, dup_verts (3 nf, dim) f32 =
+ * float(double(v) + double(float(off) * boxw)) (TriMesh.cpp:547-549); *ndup (host).  Syncs the stream once.       */
+size_t ms_delaunay_duplicates_workspace_bytes(int64_t nfaces);
+int ms_delaunay_duplicates(const float *corner_verts, int64_t nv, int dim, const int32_t *pfaces, const int8_t *poffs, int64_t nf,
+                           float box_wx, float box_wy, uint32_t *tfaces, uint32_t *dup_ids, float *dup_verts, int64_t *ndup,
+                           void *ws, size_t ws_bytes, void *stream);
+
 /* ---------------------------------------------------------------- geodesic (type 1) KDE
  * ms_geodesics replaces TriMesh::compute_geodesics_fw (memsurfer/src/TriMesh_kde.cpp:196-332): all-pairs
  * shortest paths along the edges of `faces` (for a periodic mesh: its faces followed by its periodic faces,

@@ -67,6 +67,8 @@ _SIGNATURES = {
                                        C.POINTER(_i64), C.POINTER(_i64), _vp, _sz, _vp]),
     "ms_delaunay_split_workspace_bytes": (_sz, [_i64]),
     "ms_delaunay_split": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
+    "ms_delaunay_duplicates_workspace_bytes": (_sz, [_i64]),
+    "ms_delaunay_duplicates": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _i64, _f32, _f32, _vp, _vp, _vp, C.POINTER(_i64), _vp, _sz, _vp]),
     "ms_geodesic_pitch": (_i64, [_i64]),
     "ms_geodesics": (C.c_int, [_vp, _i64, _vp, _i64, _i32, C.POINTER(_f32), _vp, _vp]),
     "ms_kde_geodesic_workspace_bytes": (_sz, [_i64]),

@@ -347,3 +347,99 @@ extern "C" int ms_delaunay_split(const int32_t *dfaces, const int8_t *doffs, int
     *nfull = h;
     return 0;
 }
+
+// ------------------------------------------------------------------ duplicated vertices of the crossing faces
+// Second step of TriMesh::trim_periodicDelaunay (TriMesh.cpp:513-560): every corner of a crossing face that is a periodic
+// image (offset != 0) is re-indexed onto a DUPLICATED vertex; the reference finds or appends (orig, offx, offy) with a
+// linear std::find, so duplicates are numbered in order of FIRST APPEARANCE in the (face, corner) scan.  Here: every
+// image corner inserts its key into an open-addressing hash table with atomicMin on the corner's position (the first
+// appearance wins whatever the thread order), the first appearances are flagged and scanned, and every corner looks
+// its number up.  Coordinates as TriMesh.cpp:547-549: float(double(v) + double(float(off) * boxw)).
+__device__ __forceinline__ unsigned long long dup_key(int v, int ox, int oy) { return (unsigned long long)(unsigned)v * 9ull + (unsigned long long)((ox + 1) * 3 + (oy + 1)); }
+__device__ __forceinline__ uint32_t dup_hash(unsigned long long k) { k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; return (uint32_t)k; }
+#define DUP_EMPTY 0xffffffffffffffffull
+// table slot: key (u64) and the smallest corner position that carries it (u32 in a u64 for atomicMin)
+__global__ void __launch_bounds__(256) k_dup_insert(const int32_t *__restrict__ pf, const int8_t *__restrict__ po, int64_t ncorner,
+                                                    unsigned long long *keys, unsigned long long *firstpos, uint32_t tmask, int32_t *slot_of) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncorner) return;
+    const int ox = po[2*i], oy = po[2*i + 1];
+    if (ox == 0 && oy == 0) { slot_of[i] = -1; return; }
+    const unsigned long long k = dup_key(pf[i], ox, oy);
+    uint32_t h = dup_hash(k) & tmask;
+    for (;;) {
+        const unsigned long long prev = atomicCAS(keys + h, DUP_EMPTY, k);
+        if (prev == DUP_EMPTY || prev == k) break;
+        h = (h + 1) & tmask;
+    }
+    atomicMin(firstpos + h, (unsigned long long)i);
+    slot_of[i] = (int32_t)h;
+}
+__global__ void __launch_bounds__(256) k_dup_flag(int64_t ncorner, const int32_t *__restrict__ slot_of, const unsigned long long *__restrict__ firstpos, int32_t *flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncorner) return;
+    const int s = slot_of[i];
+    flag[i] = s >= 0 && firstpos[s] == (unsigned long long)i;
+}
+__global__ void __launch_bounds__(256) k_dup_emit(const float *__restrict__ cverts, int dim, int64_t nv, const int32_t *__restrict__ pf, const int8_t *__restrict__ po,
+                                                  int64_t ncorner, const int32_t *__restrict__ slot_of, const unsigned long long *__restrict__ firstpos,
+                                                  const int32_t *__restrict__ rank, float bwx, float bwy,
+                                                  uint32_t *__restrict__ tfaces, uint32_t *__restrict__ dup_ids, float *__restrict__ dup_verts) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncorner) return;
+    const int s = slot_of[i];
+    const int v = pf[i];
+    if (s < 0) { tfaces[i] = (uint32_t)v; return; }
+    const int64_t first = (int64_t)firstpos[s];
+    const int d = rank[first];
+    tfaces[i] = (uint32_t)(nv + d);
+    if (first == i) {
+        dup_ids[d] = (uint32_t)v;
+        const int ox = po[2*i], oy = po[2*i + 1];
+        for (int c = 0; c < dim; c++) {
+            float x = cverts[i * dim + c];
+            if (c == 0 && ox != 0) x = (float)((double)x + (double)((float)ox * bwx));
+            if (c == 1 && oy != 0) x = (float)((double)x + (double)((float)oy * bwy));
+            dup_verts[(int64_t)d * dim + c] = x;
+        }
+    }
+}
+static int64_t dup_table_size(int64_t ncorner) { int64_t t = 1024; while (t < 4 * ncorner) t <<= 1; return t; }
+extern "C" size_t ms_delaunay_duplicates_workspace_bytes(int64_t nfaces) {
+    const int64_t nc = 3 * nfaces;
+    return 2 * ms_align((size_t)dup_table_size(nc) * 8) + 3 * ms_align((size_t)(nc + 1) * 4) + ms_scan_ws_bytes(nc) + 1024;
+}
+// corner_verts (3 nf, dim) f32 = this mesh's coordinates of the ORIGINAL vertex of every corner (dim 2 or 3; a few thousand rows:
+// cheaper to gather than to ship the whole vertex array), nv = number of original vertices, pfaces (nf,3) i32 / poffs (nf,3,2) i8 =
+// the crossing faces from ms_delaunay_split, box widths as float32 (bbox1 - bbox0 of THIS mesh); outputs: tfaces (nf,3) u32 (image corners -> nv + duplicate number), dup_ids (3 nf) u32,
+// dup_verts (3 nf, dim) f32; *ndup (host) = number of duplicated vertices.  Syncs the stream once.
+extern "C" int ms_delaunay_duplicates(const float *corner_verts, int64_t nv, int dim, const int32_t *pfaces, const int8_t *poffs, int64_t nf,
+                                      float box_wx, float box_wy, uint32_t *tfaces, uint32_t *dup_ids, float *dup_verts, int64_t *ndup,
+                                      void *ws, size_t ws_bytes, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE((dim == 2 || dim == 3) && nf >= 0 && ndup, "ms_delaunay_duplicates: bad arguments");
+    MS_REQUIRE(ws_bytes >= ms_delaunay_duplicates_workspace_bytes(nf), "ms_delaunay_duplicates: workspace too small");
+    *ndup = 0;
+    if (nf == 0) return 0;
+    MS_REQUIRE(corner_verts && pfaces && poffs && tfaces && dup_ids && dup_verts, "ms_delaunay_duplicates: bad arguments");
+    const int64_t nc = 3 * nf, tsz = dup_table_size(nc);
+    MS_REQUIRE(tsz < ((int64_t)1 << 31), "ms_delaunay_duplicates: too many crossing faces");
+    MsArena A(ws, ws_bytes);
+    unsigned long long *keys = A.take<unsigned long long>(tsz), *firstpos = A.take<unsigned long long>(tsz);
+    int32_t *slot_of = A.take<int32_t>(nc + 1), *flag = A.take<int32_t>(nc + 1), *rank = A.take<int32_t>(nc + 1);
+    void *scan_ws = A.take<char>(ms_scan_ws_bytes(nc));
+    MS_CUDA(cudaMemsetAsync(keys, 0xff, (size_t)tsz * 8, s));
+    MS_CUDA(cudaMemsetAsync(firstpos, 0xff, (size_t)tsz * 8, s));
+    MS_K("dup_insert", s); k_dup_insert<<<ms_blocks(nc, 256), 256, 0, s>>>(pfaces, poffs, nc, keys, firstpos, (uint32_t)(tsz - 1), slot_of);
+    MS_K("dup_flag", s); k_dup_flag<<<ms_blocks(nc, 256), 256, 0, s>>>(nc, slot_of, firstpos, flag);
+    if (ms_exclusive_scan_i32(flag, rank, nc, scan_ws, s)) return 2;
+    MS_K("dup_emit", s); k_dup_emit<<<ms_blocks(nc, 256), 256, 0, s>>>(corner_verts, dim, nv, pfaces, poffs, nc, slot_of, firstpos, rank, box_wx, box_wy,
+                                                                     tfaces, dup_ids, dup_verts);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    int32_t h = 0;
+    MS_CUDA(cudaMemcpyAsync(&h, rank + nc, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    MS_CUDA(cudaStreamSynchronize(s));
+    *ndup = h;
+    return 0;
+}

@@ -97,3 +97,37 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
                                    C.byref(nfull), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_split')
     F0 = int(nfull.value)
     return (_lib.d2h(full[:F0]).view(np.uint32), _lib.d2h(pfaces[:F - F0]).astype(np.int64), _lib.d2h(poffs[:F - F0]))
+
+
+def trim_partial_device(verts, pf, po, bbox0, bbox1, device='cuda:0'):
+    """Device twin of `synth.trim_partial` (TriMesh.cpp:513-560 for the faces that cross the box): duplicated vertices
+    numbered in first-appearance order by ms_delaunay_duplicates.  pf (Fp,3) vertex ids, po (Fp,3,2) offsets (host);
+    returns the same dict (periodic_faces, trimmed_faces, duplicated_vidxs, duplicated_verts)."""
+    _lib.require_cuda()
+    L = _lib.lib()
+    dev = torch.device(device)
+    verts = np.asarray(verts, np.float32)
+    V, dim = verts.shape
+    pf = np.ascontiguousarray(pf, np.int32).reshape(-1, 3)
+    po = np.ascontiguousarray(po, np.int8).reshape(-1, 3, 2)
+    nf = pf.shape[0]
+    out = dict(periodic_faces=pf.astype(np.uint32))
+    if nf == 0:
+        out.update(trimmed_faces=np.zeros((0, 3), np.uint32), duplicated_vidxs=np.zeros(0, np.uint32), duplicated_verts=np.zeros((0, dim), np.float32))
+        return out
+    boxw = (np.asarray(bbox1, np.float32)[:dim] - np.asarray(bbox0, np.float32)[:dim]).astype(np.float32)
+    cv = _lib.h2d(np.ascontiguousarray(verts[pf.reshape(-1)]), dev)
+    pfd, pod = _lib.h2d(pf, dev), _lib.h2d(po, dev)
+    tf = torch.empty((nf, 3), dtype=torch.int32, device=dev)
+    dids = torch.empty(3 * nf, dtype=torch.int32, device=dev)
+    dverts = torch.empty((3 * nf, dim), dtype=torch.float32, device=dev)
+    ws = _lib.workspace(L.ms_delaunay_duplicates_workspace_bytes(nf), dev)
+    nd = C.c_int64(0)
+    with torch.cuda.device(dev):
+        _lib.check(L.ms_delaunay_duplicates(cv.data_ptr(), V, dim, pfd.data_ptr(), pod.data_ptr(), nf, float(boxw[0]), float(boxw[1]),
+                                            tf.data_ptr(), dids.data_ptr(), dverts.data_ptr(), C.byref(nd), ws.data_ptr(), ws.numel(),
+                                            _lib.stream_ptr(dev)), 'ms_delaunay_duplicates')
+    n = int(nd.value)
+    out.update(trimmed_faces=_lib.d2h(tf).view(np.uint32), duplicated_vidxs=_lib.d2h(dids[:n]).view(np.uint32),
+               duplicated_verts=_lib.d2h(dverts[:n]))
+    return out

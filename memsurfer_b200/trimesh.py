@@ -130,7 +130,12 @@ class TriMesh(object):
         b0, b1 = self.bbox[0, :self.vertices.shape[1]], self.bbox[1, :self.vertices.shape[1]]
         if len(self._delaunay) == 3:                  # device producer: already split into inside / crossing faces
             faces, pf, po = self._delaunay
-            t = synth.trim_partial(self.vertices, pf, po, b0, b1)
+            if torch.cuda.is_available():      # duplicated-vertex numbering of the crossing faces on the device
+                from .delaunay import trim_partial_device
+                with torch.cuda.stream(self._stream or torch.cuda.current_stream(self.device)):
+                    t = trim_partial_device(self.vertices, pf, po, b0, b1, self.device)
+            else:
+                t = synth.trim_partial(self.vertices, pf, po, b0, b1)
             t['faces'] = faces
         else:
             dfaces, doffs = self._delaunay

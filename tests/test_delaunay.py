@@ -145,3 +145,19 @@ def test_periodic_delaunay_too_few_points_raises():
     m.set_bbox(b0, b1)
     with pytest.raises(IncompleteCells):
         m.compute_delaunay()
+
+
+@pytest.mark.gpu
+def test_duplicated_vertices_on_the_device_equal_the_reference_numbering():
+    """ms_delaunay_duplicates against synth.trim_partial (itself pinned bit for bit against the compiled reference's
+    trim_periodicDelaunay, tests/test_producer_layout.py): same first-appearance numbering, same float32 coordinates."""
+    from memsurfer_b200 import synth
+    from memsurfer_b200.delaunay import trim_partial_device
+    for pts, bbox in ((synth.make_leaflet(10000, seed=5)[0::2]), (synth.make_leaflet_rect(90, 36, seed=6)[0::2])):
+        df, do = synth.periodic_delaunay(pts[:, :2], bbox[0], bbox[1])
+        full = (do == 0).all(axis=(1, 2))
+        for verts, b0, b1 in ((pts, pts.min(0), pts.max(0)), (np.ascontiguousarray(pts[:, :2]), bbox[0, :2], bbox[1, :2])):
+            want = synth.trim_partial(verts, df[~full], do[~full], b0, b1)
+            got = trim_partial_device(verts, df[~full], do[~full], b0, b1)
+            for k in ("periodic_faces", "trimmed_faces", "duplicated_vidxs", "duplicated_verts"):
+                assert got[k].dtype == want[k].dtype and np.array_equal(got[k], want[k]), k

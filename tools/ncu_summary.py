@@ -27,14 +27,14 @@ def main(path):
             if w in hdr:
                 print(f"  {w:75s} {r[hdr.index(w)]:>18s} {units[hdr.index(w)]}")
         st = []
-        for i, h in enumerate(hdr):
-            if "warp_issue_stalled" in h and h.endswith("_per_warp_active.pct"):
+        for i, h in enumerate(hdr):      # warps stalled per issued instruction, by reason
+            if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio"):
                 try:
-                    st.append((float(r[i]), h.replace("smsp__warp_issue_stalled_", "").replace("_per_warp_active.pct", "")))
+                    st.append((float(r[i]), h.replace("smsp__average_warps_issue_stalled_", "").replace("_per_issue_active.ratio", "")))
                 except ValueError:
                     pass
         st.sort(reverse=True)
-        print("  stalls (% of warp-active):", ", ".join(f"{n} {v:.1f}" for v, n in st[:6]))
+        print("  stalled warps per issued instruction:", ", ".join(f"{n} {v:.2f}" for v, n in st[:7]))
 
 
 if __name__ == "__main__":

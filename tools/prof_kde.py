@@ -35,7 +35,7 @@ for rep in range(2):
         fr.run_density("c40", 2, 40.0, True, None, 8.0)
         fr.run_density("c10", 2, 10.0, True, fr.label_ids[1], 8.0)
     if a.mode == "labels":
-        fr.run_densities([40.0, 10.0], cutoff_sigmas=8.0)
+        fr.run_densities([10.0, 20.0, 30.0, 40.0], cutoff_sigmas=7.5)      # the bench.py call
     if a.mode in ("mesh", "all"):
         fr.run_properties()
     if a.mode in ("normals", "all"):
