@@ -522,7 +522,8 @@ def main():
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     pairs_allpairs_equiv = sum(fr.pairs_per_run(SIGMAS) for fr in frames)
-    pairs_step = sum(fr.evaluated_pairs(SIGMAS, cutoff_sigmas=args.kde_cutoff) for fr in frames)
+    both = [fr.evaluated_pairs(SIGMAS, cutoff_sigmas=args.kde_cutoff, split=True) for fr in frames]
+    pairs_step, pairs_fp64_step = sum(b[0] for b in both), sum(b[1] for b in both)
     kname = max(("kde_groups", "kde_pairs"), key=lambda k: prof.get(k, {"ms": 0.0})["ms"])
     kp = prof.get(kname, {"launches": 0, "ms": 0.0})
     roof = None
@@ -531,13 +532,23 @@ def main():
         # k_kde_pairs periodic 7 DADD + 4 DFMA + 2 DSETP + 1 DMUL = 14; k_kde_groups 5 DADD + 4 DFMA + 1 DMUL = 10
         instr = FP64_INSTR_PER_PAIR[kname]
         pairs_per_launch = pairs_step * psteps / kp["launches"]
+        fp64_pairs_per_launch = pairs_fp64_step * psteps / kp["launches"]
         avg_ms = kp["ms"] / kp["launches"]
         pps = pairs_per_launch / (avg_ms * 1e-3)
+        # evaluated pairs/s against the fp64 peak.  A pair counts as the 10 fp64-pipe instructions the
+        # fp64 path spends on it, whichever path evaluated it: `frac` is throughput in fp64-equivalent work,
+        # `fp64_pipe_frac` is what really went through the fp64 pipe.
         ach = pps * instr * 2.0 / 1e12
+        ach64 = fp64_pairs_per_launch / (avg_ms * 1e-3) * instr * 2.0 / 1e12
         roof = {"kernel": "k_" + kname, "bound": "fp64_fma", "achieved": ach, "peak": best, "unit": "TFLOP/s",
                 "frac": ach / best if best > 0 else None, "traffic": traffic.get(kname),
-                "definition": "evaluated pairs/s x fp64-pipe instructions per pair x 2 (every DADD/DMUL/DSETP/DFMA holds one "
-                              "FMA slot of the fp64 pipe) / DFMA-probe peak",
+                "definition": "evaluated pairs/s x 10 fp64-pipe instructions per pair x 2 (every DADD/DMUL/DSETP/DFMA holds one "
+                              "FMA slot of the fp64 pipe) / DFMA-probe peak.  Sources at least 4.5 sigma from a group's box are "
+                              "summed in fp32 (MUFU.EX2, error <= 2e-10 of a density) in the same launch: they count as evaluated "
+                              "pairs in `achieved` (fp64-equivalent work), and `fp64_pipe_frac` counts only the pairs that went "
+                              "through the fp64 pipe",
+                "fp64_pipe_achieved": ach64, "fp64_pipe_frac": ach64 / best if best > 0 else None,
+                "fp64_pairs_per_launch": fp64_pairs_per_launch, "fp32_far_field_pairs_per_launch": pairs_per_launch - fp64_pairs_per_launch,
                 "peak_source": "ms_dfma_probe in this process (no fp64 figure in MEASURED_PEAKS.json)",
                 "fp64_instr_per_pair": instr, "pairs_per_launch": pairs_per_launch, "avg_launch_ms": avg_ms,
                 "launches": kp["launches"], "evaluated_pairs_per_s": pps,

@@ -181,15 +181,17 @@ size_t ms_kde_labels_multi_workspace_bytes(int64_t nv, int nlabels);
 int ms_kde_labels_multi(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
                         int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
                         double *raw, void *ws, size_t ws_bytes, void *stream);
-/* Diagnostic twin: pairs[i] (host doubles) = pairs the launch of sigma i evaluates.  Syncs the stream. */
+/* Diagnostic twin: pairs (host, 2 * nsigma doubles): pairs[i] = pairs the launch of sigma i evaluates, pairs[nsigma + i] =
+ * those of them summed in fp64 (the rest, beyond 5 sigma, is summed in fp32).  Syncs the stream. */
 int ms_kde_labels_multi_pairs(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
                               int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
                               double *pairs, void *ws, size_t ws_bytes, void *stream);
 
 /* Diagnostic (roofline accounting): the number of pairs ms_kde (labels == NULL) or ms_kde_labels
  * evaluates for the same arguments -- nv*n_sources for the all-pairs kernel, the sum over cells of
- * targets x window sources for the cell list.  *pairs is a host double; ws sized by the matching
- * *_workspace_bytes.  Syncs the stream.                                                          */
+ * targets x window sources for the cell list.  pairs = TWO host doubles: all evaluated pairs, and those of them summed
+ * in fp64 (the cell-list kernel sums pairs beyond 5 sigma in fp32); ws sized by the matching *_workspace_bytes.
+ * Syncs the stream.                                                          */
 int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids,
                            const int32_t *labels, int nlabels,
                            int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,

@@ -19,9 +19,9 @@
 //
 // Arithmetic: fp64 on float32 inputs, compiled without FMA contraction.  Whether a bisector cuts off a cell vertex is
 // the in-circle predicate of four points; when the fp64 value of that test is within 1e-10 of zero (relative to its
-// terms) it is re-evaluated in double-double arithmetic on the exact coordinate differences (~104 bits: exact for
-// float32 inputs whose differences carry <= 26 bits, which includes every lattice) and an exact ZERO -- four or more
-// cocircular points -- is decided by the symbolic perturbation CGAL's Delaunay_triangulation_2 uses
+// terms) it is re-evaluated in double-double arithmetic on the exact coordinate differences, the four points taken in
+// one canonical (lexicographic) order so that every cell computes bit-identical values for a shared quadruple, and a
+// ZERO (|det| <= 2^-96 of its terms) -- four or more cocircular points -- is decided by the symbolic perturbation CGAL's Delaunay_triangulation_2 uses
 // (side_of_oriented_circle with `perturb`: points ordered lexicographically, the largest one is pushed off the
 // circle first [recalled, CGAL 4.13; CGAL itself is not in the tree]).  The answer is a function of the four points
 // only, so the four cells that share a degenerate Voronoi vertex agree and the stars always glue to a triangulation.
@@ -47,7 +47,11 @@ __device__ __forceinline__ int dl_orient(double ax, double ay, double bx, double
     const double ux = bx - ax, uy = by - ay, vx = cx - ax, vy = cy - ay;     // exact (float32-valued inputs)
     return dd_sign(dd_add(dd_two_prod(ux, vy), dd_neg(dd_two_prod(uy, vx))));
 }
-// sign of the in-circle determinant: > 0 iff d lies inside the circle through a, b, c (counter-clockwise)
+// sign of the in-circle determinant: > 0 iff d lies inside the circle through a, b, c (counter-clockwise).
+// The three products carry up to ~108 bits for 26-bit differences, two more than a double-double holds, so a value
+// within 2^-96 of the terms' magnitude is reported as ZERO (the caller then perturbs symbolically): a true non-zero
+// value that small is as good as cocircular, and the caller evaluates every quadruple in ONE canonical order, so
+// whatever is decided here is decided identically in all four cells that share the quadruple.
 __device__ __forceinline__ int dl_incircle(double ax, double ay, double bx, double by, double cx, double cy, double dx, double dy) {
     const double x0 = ax - dx, y0 = ay - dy, x1 = bx - dx, y1 = by - dy, x2 = cx - dx, y2 = cy - dy;   // exact
     const dd l0 = dd_add(dd_two_prod(x0, x0), dd_two_prod(y0, y0));
@@ -56,47 +60,75 @@ __device__ __forceinline__ int dl_incircle(double ax, double ay, double bx, doub
     const dd m0 = dd_add(dd_two_prod(x1, y2), dd_neg(dd_two_prod(y1, x2)));
     const dd m1 = dd_add(dd_two_prod(x2, y0), dd_neg(dd_two_prod(y2, x0)));
     const dd m2 = dd_add(dd_two_prod(x0, y1), dd_neg(dd_two_prod(y0, x1)));
-    return dd_sign(dd_add(dd_add(dd_mul(l0, m0), dd_mul(l1, m1)), dd_mul(l2, m2)));
+    const dd t0 = dd_mul(l0, m0), t1 = dd_mul(l1, m1), t2 = dd_mul(l2, m2);
+    const dd det = dd_add(dd_add(t0, t1), t2);
+    const double mag = fabs(t0.hi) + fabs(t1.hi) + fabs(t2.hi);
+    if (fabs(det.hi) <= 1.2621774483536189e-29 * mag) return 0;                    // 2^-96
+    return dd_sign(det);
+}
+// The point set: n original points followed by their periodic images.  An image is stored as the float32 sum
+// point + k * width, i.e. ROUNDED -- two cells that see the same four points through different images would then
+// evaluate the predicates on slightly different quadruples and could disagree on a nearly cocircular one (a lattice
+// whose spacing is not a power of two).  Every coordinate is therefore rebuilt as source + k * width in fp64, which
+// is exact for float32 operands: all the images of a configuration are exact translates of each other.
+struct DlPts { const float *pts; const int32_t *gsrc; int64_t n; double wx, wy; };
+__device__ __forceinline__ void dl_xy(const DlPts &P, int64_t i, double &x, double &y) {
+    x = (double)P.pts[3*i]; y = (double)P.pts[3*i + 1];
+    if (i >= P.n) {
+        const int64_t o = P.gsrc[i];
+        const double ox = (double)P.pts[3*o], oy = (double)P.pts[3*o + 1];
+        x = ox + rint((x - ox) / P.wx) * P.wx; y = oy + rint((y - oy) / P.wy) * P.wy;
+    }
 }
 // lexicographic (x, y, index) order of two points
-__device__ __forceinline__ bool dl_lex_less(const float *__restrict__ pts, int64_t i, int64_t j) {
-    const float xi = pts[3*i], xj = pts[3*j];
-    if (xi != xj) return xi < xj;
-    const float yi = pts[3*i + 1], yj = pts[3*j + 1];
-    if (yi != yj) return yi < yj;
-    return i < j;
+__device__ __forceinline__ bool dl_lex_less(const double (&X)[4], const double (&Y)[4], const int64_t (&id)[4], int i, int j) {
+    if (X[i] != X[j]) return X[i] < X[j];
+    if (Y[i] != Y[j]) return Y[i] < Y[j];
+    return id[i] < id[j];
 }
 // is q inside the circle through (p0, p1, p2), counter-clockwise and not collinear -- ties decided by perturbation
-__device__ __forceinline__ bool dl_inside_sos(const float *__restrict__ pts, int64_t p0, int64_t p1, int64_t p2, int64_t q) {
-    const double x0 = pts[3*p0], y0 = pts[3*p0+1], x1 = pts[3*p1], y1 = pts[3*p1+1], x2 = pts[3*p2], y2 = pts[3*p2+1], xq = pts[3*q], yq = pts[3*q+1];
-    const int s = dl_incircle(x0, y0, x1, y1, x2, y2, xq, yq);
-    if (s != 0) return s > 0;
-    // cocircular: walk the four points from the lexicographically largest down (CGAL: 2 iterations are enough)
-    int64_t o[4] = { p0, p1, p2, q };
+__device__ __forceinline__ bool dl_inside_sos(const DlPts &P, int64_t p0, int64_t p1, int64_t p2, int64_t q) {
+    const int64_t id[4] = { p0, p1, p2, q };
+    double X[4], Y[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) dl_xy(P, id[i], X[i], Y[i]);
+    // canonical order of the quadruple: lexicographic in the exact coordinates (the same in every image of it)
+    int o[4] = { 0, 1, 2, 3 };
+    int parity = 1;
 #pragma unroll
     for (int a = 0; a < 3; a++)
 #pragma unroll
-        for (int b = 0; b < 3 - a; b++) if (dl_lex_less(pts, o[b + 1], o[b])) { const int64_t t = o[b]; o[b] = o[b + 1]; o[b + 1] = t; }
+        for (int b = 0; b < 3 - a; b++)
+            if (dl_lex_less(X, Y, id, o[b + 1], o[b])) { const int t = o[b]; o[b] = o[b + 1]; o[b + 1] = t; parity = -parity; }
+    // the lifted 4 x 4 determinant is antisymmetric in its four points
+    const int s = parity * dl_incircle(X[o[0]], Y[o[0]], X[o[1]], Y[o[1]], X[o[2]], Y[o[2]], X[o[3]], Y[o[3]]);
+    if (s != 0) return s > 0;
+    // cocircular: walk the four points from the lexicographically largest down (CGAL: 2 iterations are enough)
     for (int i = 3; i > 0; i--) {
-        const int64_t w = o[i];
-        if (w == q) return false;                                   // ON_NEGATIVE_SIDE: outside
+        const int w = o[i];
+        if (w == 3) return false;                                   // ON_NEGATIVE_SIDE: outside
         int r = 0;
-        if (w == p2) r = dl_orient(x0, y0, x1, y1, xq, yq);
-        else if (w == p1) r = dl_orient(x0, y0, xq, yq, x2, y2);
-        else r = dl_orient(xq, yq, x1, y1, x2, y2);
+        if (w == 2) r = dl_orient(X[0], Y[0], X[1], Y[1], X[3], Y[3]);
+        else if (w == 1) r = dl_orient(X[0], Y[0], X[3], Y[3], X[2], Y[2]);
+        else r = dl_orient(X[3], Y[3], X[1], Y[1], X[2], Y[2]);
         if (r != 0) return r > 0;
     }
     return false;
 }
 
 #define DL_MAXV 24          // cell vertices kept per thread (a Voronoi cell has ~6)
+// security radius: a point farther than twice the cell's radius cannot cut the cell.  The margin keeps the points ON
+// that circle (bisector through the farthest cell vertex: the diagonal neighbour of a lattice point) in the list even
+// when rounding puts them just beyond it -- the symbolic perturbation may still count them as cutters, and the cell
+// across the diagonal will have asked the same question.  (|s| <= 1e-10 in dl_clip corresponds to 2e-10 here.)
+#define DL_SECURE (4.0 * (1.0 + 1e-8))
 
 struct DlCell { double x[DL_MAXV], y[DL_MAXV]; int g[DL_MAXV]; int n; };
 
 // clip the convex cell (counter-clockwise) with the half-plane {v : v.d <= |d|^2/2}; the new edge gets generator q.
 // Cell vertex i is the circumcentre of (p, g[i-1], g[i]) (counter-clockwise): it is cut off iff q lies inside that
 // circle.  The fp64 value decides unless it is within 1e-10 (relative) of zero; then the robust predicate does.
-__device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q, const float *__restrict__ pts, int64_t p) {
+__device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q, const DlPts &P, int64_t p) {
     const double h = 0.5 * (dx * dx + dy * dy);
     double s[DL_MAXV];
     unsigned outm = 0u;
@@ -106,7 +138,7 @@ __device__ __forceinline__ bool dl_clip(DlCell &c, double dx, double dy, int q, 
         bool out = s[i] > 0.0;
         const int ga = c.g[i == 0 ? c.n - 1 : i - 1], gb = c.g[i];
         if (ga >= 0 && gb >= 0 && ga != gb && fabs(s[i]) <= 1e-10 * (fabs(tx) + fabs(ty) + h))
-            out = dl_inside_sos(pts, p, ga, gb, q);
+            out = dl_inside_sos(P, p, ga, gb, q);
         outm |= (unsigned)out << i;
     }
     if (!outm) return true;
@@ -152,15 +184,16 @@ __device__ __forceinline__ void dl_square(DlCell &c, double R) {
     c.x[0] = -R; c.y[0] = -R; c.x[1] = R; c.y[1] = -R; c.x[2] = R; c.y[2] = R; c.x[3] = -R; c.y[3] = R;
     c.g[0] = c.g[1] = c.g[2] = c.g[3] = -1;
 }
-__device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int32_t *__restrict__ nbr, int k1, int64_t p, int64_t m,
+__device__ __forceinline__ int dl_cell(const DlPts &P, const int32_t *__restrict__ nbr, int k1, int64_t p, int64_t m,
                                        double reach2, DlCell &c) {
-    const double px = (double)pts[3*p], py = (double)pts[3*p + 1];
+    const double px = (double)P.pts[3*p], py = (double)P.pts[3*p + 1];       // p < n: an original point
     const int32_t *row = nbr + p * k1;
     // fast path: start from a square that contains every bisector of the list (half side = distance to the last neighbour)
     double far2 = 0.0;
     {
         const int32_t q = row[k1 - 1];
-        const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
+        double qx, qy; dl_xy(P, q, qx, qy);
+        const double dx = qx - px, dy = qy - py;
         far2 = dx * dx + dy * dy;
     }
     dl_square(c, sqrt(far2));
@@ -169,9 +202,10 @@ __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int3
     for (int j = 0; j < k1; j++) {
         const int32_t q = row[j];
         if ((int64_t)q == p) continue;
-        const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
-        if (dx * dx + dy * dy > 4.0 * r2) { complete = true; break; }
-        if (!dl_clip(c, dx, dy, q, pts, p)) return 0;
+        double qx, qy; dl_xy(P, q, qx, qy);
+        const double dx = qx - px, dy = qy - py;
+        if (dx * dx + dy * dy > DL_SECURE * r2) { complete = true; break; }
+        if (!dl_clip(c, dx, dy, q, P, p)) return 0;
         r2 = dl_radius2(c);
     }
     bool open = false;
@@ -186,21 +220,23 @@ __device__ __forceinline__ int dl_cell(const float *__restrict__ pts, const int3
         for (int j = 0; j < k1; j++) {
             const int32_t q = row[j];
             if ((int64_t)q == p) continue;
-            const double dx = (double)pts[3*(int64_t)q] - px, dy = (double)pts[3*(int64_t)q + 1] - py;
-            if (!dl_clip(c, dx, dy, q, pts, p)) return 0;
+            double qx, qy; dl_xy(P, q, qx, qy);
+            const double dx = qx - px, dy = qy - py;
+            if (!dl_clip(c, dx, dy, q, P, p)) return 0;
         }
         r2 = dl_radius2(c);
         for (int64_t q = 0; q < m; q++) {
             if (q == p) continue;
-            const double dx = (double)pts[3*q] - px, dy = (double)pts[3*q + 1] - py;
+            double qx, qy; dl_xy(P, q, qx, qy);
+            const double dx = qx - px, dy = qy - py;
             const double d2 = dx * dx + dy * dy;
-            if (d2 > 4.0 * r2 || d2 < far2) continue;             // cannot cut / closer than the list's last entry: already used
+            if (d2 > DL_SECURE * r2 || d2 < far2) continue;             // cannot cut / closer than the list's last entry: already used
             if (d2 == far2) {                                      // the last entry itself (or a tie with it): clip a point only once
                 bool used = false;
                 for (int j = 0; j < k1; j++) used |= (int64_t)row[j] == q;
                 if (used) continue;
             }
-            if (!dl_clip(c, dx, dy, (int)q, pts, p)) return 0;
+            if (!dl_clip(c, dx, dy, (int)q, P, p)) return 0;
             r2 = dl_radius2(c);
         }
     }
@@ -218,7 +254,8 @@ __global__ void __launch_bounds__(128) k_delaunay_star(const float *__restrict__
                                                        int32_t *__restrict__ dfaces, int8_t *__restrict__ doffs) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     DlCell c;
-    const int nv = p < n ? dl_cell(pts, nbr, k1, p, m, reach2, c) : 0;
+    DlPts P; P.pts = pts; P.gsrc = gsrc; P.n = n; P.wx = wx; P.wy = wy;
+    const int nv = p < n ? dl_cell(P, nbr, k1, p, m, reach2, c) : 0;
     if (!FILL) {
         // corners of all stars: 6n on a torus (Euler); less when a cocircular quadruple was left without a diagonal
         const int tot = __reduce_add_sync(0xffffffffu, nv);
@@ -278,7 +315,8 @@ extern "C" int ms_delaunay_periodic(const float *points_all, int64_t m, int64_t 
     MS_CUDA(cudaStreamSynchronize(s));
     *nfaces = h[0]; *n_incomplete = h[1];
     if (h[1] == 0 && (int64_t)h[2] != 6 * n) {      // degenerate input (exactly cocircular points): not a triangulation
-        *n_incomplete = -1;
+        const int64_t off = (int64_t)h[2] - 6 * n;      // star corners missing (< 0) or in excess
+        *n_incomplete = -(off < 0 ? -off : off);
         return 0;
     }
     if (h[1] != 0 || dfaces == NULL) return 0;

@@ -305,41 +305,57 @@ __global__ void __launch_bounds__(256) k_kde_cell_gather(const typename SrcT<DIM
 #define GR_THREADS (GR_NW * 32)
 #define GR_CAP 128               // sources per stage (per warp)
 #ifndef GR_TGT
-#define GR_TGT 32                // targets per group (64 = two per lane: 10 % more window pairs, 3 % slower)
+#define GR_TGT 64                // targets per group, GR_TGT/32 per lane.  Same box, ms/step of the launch series: 32: 9.40, 64: 8.12,
+                                 // 96: 8.73, 128: 9.37 -- more targets share the per-batch work (planning, copies, the near/far
+                                 // split) but widen the window (+11 % pairs at 64, +19 % at 96)
 #endif
 #define GR_TAB_BYTES (KDE_TAB * 16 * 8)
 
+#define KDE_MAXGAP 47
+#ifndef KDE_FAR_SIGMAS
+#define KDE_FAR_SIGMAS 4.5
+#endif
+#define KDE_FAR_SHARE 1e-4      // largest fp32 part of a sum, relative to its fp64 part, that is accepted (else: fp64 redo)
 struct KdeTiling {
     KdeGrid gs;               // fine source grid
     int B, nty, mf, wmax;     // fine rows per strip, strips, window reach in fine rows, widest group (columns)
     double rc2, cxs, cys;     // scaled cut-off radius^2 and fine cell pitch
+    double ri2;               // scaled radius^2 beyond which a pair is summed in fp32 (0: no far field)
+    float hx[KDE_MAXGAP + 1]; // half width of the window at `gap` full rows from the strip, rounded UP (< 0: the row is outside)
     double gscale;            // factor on the stored group x extents (1 unless the binning is shared between sigmas)
     double oscale;            // factor on every sum before it is added to the output (the kernel's sfactor, or 1)
 };
 struct KdeGroup { int t0, t1, strip, ca, cb, pad0, pad1, pad2; double xlo, xhi; };   // targets [t0,t1), fine columns [ca,cb], x extent
 
-// piece q of the window of the box [xlo,xhi] x strip TY: row q>>1 (bottom-up), part q&1
-// (1 = the part of the row that wrapped around the period).  code = 3*(sx+1)+(sy+1): the image shift
+// The window of the box [xlo,xhi] x strip TY is cut, row by row, into contiguous ranges of the sorted source array:
+// piece q = nparts*row + part, part 1 = what wrapped around the period.  code = 3*(sx+1)+(sy+1): the image shift
 // (sx*wx, sy*wy) to add to the targets.
-__device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, double xlo, double xhi, int q, const int32_t *__restrict__ sstart,
-                                                int &off, int &cnt, int &code) {
+__device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, double xlo, double xhi, int nparts, int q,
+                                                const int32_t *__restrict__ sstart, int &off, int &cnt, int &code) {
     off = 0; cnt = 0; code = 4;
     const KdeGrid &g = T.gs;
     const int rows = T.B + 2 * T.mf;
-    const int ri = q >> 1, part = q & 1;
+    // nparts = 2 only for groups whose window crosses the period in x (kde_window_parts): twice the pieces, half of them empty
+    const int part = nparts == 2 ? q & 1 : 0, ri = nparts == 2 ? q >> 1 : q;
     if (ri >= rows) return;
     const int gap = ri < T.mf ? T.mf - 1 - ri : (ri >= T.mf + T.B ? ri - T.mf - T.B : 0);   // full fine rows between row and strip
-    const double gy = (double)gap * T.cys;
-    const double h2 = T.rc2 - gy * gy;
-    if (h2 <= 0.0) return;
-    const double hx = sqrt(h2);
+    double hx;
+    if (gap <= KDE_MAXGAP) hx = (double)T.hx[gap];
+    else { const double gy = (double)gap * T.cys, h2 = T.rc2 - gy * gy; hx = h2 > 0.0 ? sqrt(h2) : -1.0; }
+    if (hx < 0.0) return;
     int row = TY * T.B - T.mf + ri, sy = 0;
     if (row < 0) { if (!g.periodic) return; row += g.ncy; sy = 1; }
     else if (row >= g.ncy) { if (!g.periodic) return; row -= g.ncy; sy = -1; }
-    int xa = (int)floor((xlo - hx - g.b0x) * g.inv_cx), xb = (int)floor((xhi + hx - g.b0x) * g.inv_cx), sx = 0;
+    int xa = (int)floor((xlo - hx - g.b0x) * g.inv_cx), xb = (int)floor((xhi + hx - g.b0x) * g.inv_cx), sx = 0;    // unwrapped columns
     if (!g.periodic) {
         if (part) return;
         xa = max(xa, 0); xb = min(xb, g.ncx - 1);
+    } else if (xb < 0) {
+        if (part) return;
+        xa += g.ncx; xb += g.ncx; sx = 1;
+    } else if (xa >= g.ncx) {
+        if (part) return;
+        xa -= g.ncx; xb -= g.ncx; sx = -1;
     } else if (xa < 0) {
         if (part == 0) { xa += g.ncx; xb = g.ncx - 1; sx = 1; } else { xa = 0; }
     } else if (xb >= g.ncx) {
@@ -349,6 +365,13 @@ __device__ __forceinline__ void kde_group_piece(const KdeTiling &T, int TY, doub
     off = __ldg(sstart + row * g.ncx + xa);
     cnt = __ldg(sstart + row * g.ncx + xb + 1) - off;
     code = 3 * (sx + 1) + (sy + 1);
+}
+// does the window of the box [xlo, xhi] reach across the period in x (then every range may come in two parts)?
+__device__ __forceinline__ int kde_window_parts(const KdeTiling &T, double xlo, double xhi) {
+    if (!T.gs.periodic) return 1;
+    const double hx = (double)T.hx[0];
+    const int xa = (int)floor((xlo - hx - T.gs.b0x) * T.gs.inv_cx), xb = (int)floor((xhi + hx - T.gs.b0x) * T.gs.inv_cx);
+    return (xa < 0 || xb >= T.gs.ncx) ? 2 : 1;
 }
 
 // 2^-(r/256) = sc * p with the lane-private table copy (tbase = shared address of the table + 8*(lane&15)).
@@ -418,7 +441,7 @@ __global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restric
 
 // ---- per-warp batch planner: the warp caches 32 consecutive pieces (lane = piece) and hands out runs of
 // them that fit one stage and share one image shift; a piece larger than a stage is sliced
-struct KdePlanState { int pbase, pos, intra, c_off, c_cnt, c_code; };
+struct KdePlanState { int pbase, pos, intra, c_off, c_cnt, c_code, nparts; };
 struct KdeBatch { int total, code, take_off, take_cnt, dst; };
 
 __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling &T, int TY, double xlo, double xhi, int q_hi,
@@ -427,7 +450,7 @@ __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling 
         if (st.pos >= 32) {
             st.pbase += 32; st.pos = 0; st.intra = 0;
             if (st.pbase >= q_hi) return false;
-            kde_group_piece(T, TY, xlo, xhi, st.pbase + lane, sstart, st.c_off, st.c_cnt, st.c_code);
+            kde_group_piece(T, TY, xlo, xhi, st.nparts, st.pbase + lane, sstart, st.c_off, st.c_cnt, st.c_code);
             if (st.pbase + lane >= q_hi) st.c_cnt = 0;
         }
         const int eff = lane < st.pos ? 0 : (lane == st.pos ? st.c_cnt - st.intra : st.c_cnt);
@@ -438,18 +461,25 @@ __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling 
         int pre = eff;                                   // inclusive prefix sum of the remaining piece sizes
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += v; }
-        const unsigned bad = __ballot_sync(0xffffffffu, eff > 0 && (st.c_code != code || pre > GR_CAP));
-        const int nfit = bad ? __ffs(bad) - 1 : 32;
-        b.code = code; b.take_cnt = 0; b.dst = pre - eff;
+        // the batch: the pieces of one image shift, in order, until the stage is full -- the piece that crosses the end
+        // of the stage is cut there and resumed in the next batch, so every batch but the last of a shift is full
+        const unsigned other = __ballot_sync(0xffffffffu, eff > 0 && st.c_code != code);
+        const int nsame = other ? __ffs(other) - 1 : 32;
+        const unsigned over = __ballot_sync(0xffffffffu, lane < nsame && eff > 0 && pre > GR_CAP);
+        b.code = code; b.dst = pre - eff;
         b.take_off = st.c_off + (lane == st.pos ? st.intra : 0);
-        if (nfit <= first) {                             // the first non-empty piece alone overflows a stage: take a slice
-            if (lane == first) b.take_cnt = GR_CAP;
-            b.total = GR_CAP;
-            if (first == st.pos) st.intra += GR_CAP; else { st.pos = first; st.intra = GR_CAP; }
+        if (over == 0u) {
+            b.take_cnt = lane < nsame ? eff : 0;
+            b.total = __shfl_sync(0xffffffffu, pre, nsame - 1);
+            st.pos = nsame; st.intra = 0;
         } else {
-            if (lane < nfit) b.take_cnt = eff;
-            b.total = __shfl_sync(0xffffffffu, pre, nfit - 1);
-            st.pos = nfit; st.intra = 0;
+            const int cut = __ffs(over) - 1;
+            const int part = GR_CAP - (pre - eff);       // what of the cut piece still fits (>= 0 on lane `cut`)
+            b.take_cnt = lane < cut ? eff : (lane == cut ? part : 0);
+            b.total = GR_CAP;
+            const int part_c = __shfl_sync(0xffffffffu, part, cut);
+            st.intra = (cut == st.pos ? st.intra : 0) + part_c;
+            st.pos = cut;
         }
         return true;
     }
@@ -468,6 +498,78 @@ __device__ __forceinline__ void kde_issue_batch(const KdeBatch &b, S *stage, con
         if (lane == 0) bulk_g2s(stage + dst, src + off, (uint32_t)cnt * (uint32_t)sizeof(S), bar);
     }
     __syncwarp();
+}
+
+// ---- far field in fp32.  A source that is at least r_in = 4.5 sigma away from every point of the group's box gives
+// terms below exp(-10.1) = 4e-5 of a near one, and all such terms together carry ~1e-4 of a sum: fp32 is enough for
+// them -- IF the coordinates are small.  Per staged batch the warp therefore (lane-parallel, four sources per lane)
+// measures every source against the box and rewrites the stage in place: the near sources compacted at its head as
+// they are, the far ones behind them as float coordinates relative to the centre of the group and scaled by
+// 1/sqrt(512) (one fp64 subtraction per SOURCE, not per pair: relative error of a term ~6e-6, of the sum ~2e-11).
+// The pair loops then run over the two lists: 10 DFMA-class + 7 other instructions per near pair, FADD/FFMA +
+// MUFU.EX2 = 8 issue slots per far pair.  Returns the number of near sources.
+template <int DIM> struct FarT;
+template <> struct FarT<2> { typedef float2 type; };
+template <> struct FarT<3> { typedef float4 type; };
+template <int DIM>
+__device__ __forceinline__ int kde_split_batch(typename SrcT<DIM>::type *Bs, int cnt, float hwx, float hwy, float ri2f,
+                                               double cx, double cy, float FS, int lane) {
+    typedef typename SrcT<DIM>::type S;
+    typedef typename FarT<DIM>::type F;
+    constexpr int K = GR_CAP / 32;
+    S v[K];
+    float fx[K], fy[K];
+    unsigned mn[K], mf[K];
+    int nnear = 0;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const bool valid = lane + 32 * k < cnt;
+        bool isfar = false;
+        if (valid) {
+            v[k] = Bs[lane + 32 * k];
+            fx[k] = (float)(v[k].x - cx); fy[k] = (float)(v[k].y - cy);
+            const float ax = fmaxf(fabsf(fx[k]) - hwx, 0.f), ay = fmaxf(fabsf(fy[k]) - hwy, 0.f);
+            isfar = fmaf(ay, ay, ax * ax) >= ri2f;
+        }
+        mn[k] = __ballot_sync(0xffffffffu, valid && !isfar);
+        mf[k] = __ballot_sync(0xffffffffu, valid && isfar);
+        nnear += __popc(mn[k]);
+    }
+    __syncwarp();                                  // every load above is done before the first store below
+    F *Fs = (F*)(Bs + nnear);
+    const unsigned lt = (1u << lane) - 1u;
+    int nb = 0, fb = 0;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        if ((mn[k] >> lane) & 1u) Bs[nb + __popc(mn[k] & lt)] = v[k];
+        else if ((mf[k] >> lane) & 1u) {
+            F f;
+            f.x = fx[k] * FS; f.y = fy[k] * FS;
+            if (DIM == 3) { ((float*)&f)[2] = (float)((const double*)&v[k])[2] * FS; ((float*)&f)[3] = 0.f; }
+            Fs[fb + __popc(mf[k] & lt)] = f;
+        }
+        nb += __popc(mn[k]); fb += __popc(mf[k]);
+    }
+    __syncwarp();
+    return nnear;
+}
+template <int DIM, int R>
+__device__ __forceinline__ void kde_far_sum(const typename FarT<DIM>::type *Fs, int cnt, const float (&ftx)[R], const float (&fty)[R],
+                                            const float (&ftz)[R], float (&facc)[R]) {
+    typedef typename FarT<DIM>::type F;
+#pragma unroll 8
+    for (int i = 0; i < cnt; i++) {
+        const F sp = Fs[i];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const float dx = sp.x - ftx[r], dy = sp.y - fty[r];
+            float r2 = fmaf(dy, dy, dx * dx);
+            if (DIM == 3) { const float dz = ((const float*)&sp)[2] - ftz[r]; r2 = fmaf(dz, dz, r2); }
+            float e;
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-r2));
+            facc[r] += e;
+        }
+    }
 }
 
 template <int DIM, bool CLAMP>
@@ -494,8 +596,12 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
     const uint32_t tabl = smem_u32(tab) + 8u * (uint32_t)(lane & 15);
     const int ncell = T.gs.ncx * T.gs.ncy;
     const int nrows = T.B + 2 * T.mf;
-    const int q_mid = 2 * (nrows / 2), q_end = 2 * nrows;
-    const int nitems = __ldg(gtotal) * nlabels * 2;
+    const int r_mid = nrows / 2;                 // an item takes the rows [0, r_mid) or [r_mid, nrows) of its window
+#ifndef GR_HALVES
+#define GR_HALVES 2
+#endif
+    const int nitems = __ldg(gtotal) * nlabels * GR_HALVES;
+    const bool far = T.ri2 > 0.0;
     uint32_t phase = 0u;                       // bit s = parity to wait for on stage s
 
     for (;;) {
@@ -503,12 +609,12 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
         if (lane == 0) item = (int)atomicAdd(counter, 1u);
         item = __shfl_sync(0xffffffffu, item, 0);
         if (item >= nitems) break;
-        const int half = item & 1, lab = (item >> 1) % nlabels, g = (item >> 1) / nlabels;
+        const int half = item % GR_HALVES, lab = (item / GR_HALVES) % nlabels, g = (item / GR_HALVES) / nlabels;
         const int4 gi = __ldg((const int4*)(groups + g));            // t0, t1, strip, ca
         const int g_cb = __ldg(&groups[g].cb);
         const double g_xlo = __ldg(&groups[g].xlo) * T.gscale, g_xhi = __ldg(&groups[g].xhi) * T.gscale;
         const int32_t *__restrict__ sstart = sstart_all + (size_t)lab * ncell;
-        const int q_lo = half ? q_mid : 0, q_hi = half ? q_end : q_mid;
+        const int r_lo = half ? r_mid : 0, r_hi = (half || GR_HALVES == 1) ? nrows : r_mid;
         for (int pa = gi.w; pa <= g_cb; pa += T.wmax) {               // one pass unless the group is wider than the period allows
             const int pb = min(g_cb, pa + T.wmax - 1);
             int a0 = gi.x, a1 = gi.y;
@@ -519,60 +625,91 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
                 xlo = T.gs.b0x + (double)pa * T.cxs; xhi = T.gs.b0x + (double)(pb + 1) * T.cxs;
             }
             if (a0 >= a1) continue;
-            double tx[2], ty[2], tz[2], acc[2];
+            // GR_R targets per lane
+            constexpr int GR_R = GR_TGT / 32;
+            double tx[GR_R], ty[GR_R], tz[GR_R], acc[GR_R];
+            // far field: coordinates relative to the centre of the group, scaled by 1/sqrt(512) so that the fp32 term is
+            // ex2(-(dx^2 + dy^2)); the centre moves with the periodic image of a batch, the targets do not
+            const double gcx = 0.5 * (xlo + xhi), gcy = T.gs.b0y + ((double)gi.z + 0.5) * (double)T.B * T.cys;
+            const float FS = 0.044194173824159216f;                  // 1 / sqrt(512)
+            float ftx[GR_R], fty[GR_R], ftz[GR_R], facc[GR_R];
 #pragma unroll
-            for (int r = 0; r < 2; r++) {
-                const int j = a0 + lane + r * 32;
+            for (int r = 0; r < GR_R; r++) {
+                const int j = a0 + lane + 32 * r;
                 S q; q.x = 0.0; q.y = 0.0; if (DIM == 3) { ((double*)&q)[2] = 0.0; }
                 if (j < a1) q = tgt[j];
-                tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0; acc[r] = 0.0;
+                tx[r] = q.x; ty[r] = q.y; tz[r] = DIM == 3 ? ((double*)&q)[2] : 0.0;
+                acc[r] = 0.0; facc[r] = 0.f;
+                ftx[r] = (float)(tx[r] - gcx) * FS; fty[r] = (float)(ty[r] - gcy) * FS; ftz[r] = (float)tz[r] * FS;
             }
-            const bool two = a0 + 32 < a1;
-            KdePlanState st; st.pbase = q_lo - 32; st.pos = 32; st.intra = 0; st.c_off = st.c_cnt = 0; st.c_code = 4;
+            // the distance of a source to the box is taken in fp32 from the centre-relative coordinates: the margin covers
+            // the rounding, a source within it simply stays in the fp64 list
+            const float hwx = (float)(0.5 * (xhi - xlo)), hwy = (float)(0.5 * (double)T.B * T.cys), ri2f = (float)T.ri2 * 1.0001f;
+            const int nparts = kde_window_parts(T, xlo, xhi);
+            // The fp32 part of a sum is trusted only while it is a small part: if it exceeds KDE_FAR_SHARE of the fp64
+            // part on any target (a target with few or no near sources: sparse ids, the rim of a cluster), the whole
+            // item is summed again in fp64.  Bound on the result: KDE_FAR_SHARE x the fp32 sum's error (~5e-6) < 1e-9.
+            bool use_far = far;
+          again:
+            KdePlanState st; st.pbase = nparts * r_lo - 32; st.pos = 32; st.intra = 0; st.c_off = st.c_cnt = 0; st.c_code = 4;
+            st.nparts = nparts;
+            const int q_hi = nparts * r_hi;
             KdeBatch cur, nxt;
             int s = 0;
             bool have = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, cur);
-            if (have) {
-                kde_issue_batch<S>(cur, buf, src, &bar[0], lane);
-            }
+            if (have) kde_issue_batch<S>(cur, buf, src, &bar[0], lane);
             while (have) {
                 const bool more = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, nxt);
-                if (more) {                    // stage s^1 was drained by this warp in the previous round
-                    kde_issue_batch<S>(nxt, buf + (s ^ 1) * GR_CAP, src, &bar[s ^ 1], lane);
-                }
+                if (more) kde_issue_batch<S>(nxt, buf + (s ^ 1) * GR_CAP, src, &bar[s ^ 1], lane);    // stage s^1 was drained in the previous round
                 mbar_wait(&bar[s], (phase >> s) & 1u); phase ^= 1u << s;
                 __syncwarp();                  // the lanes leave the try_wait loop one by one: reconverge before the pair loop
-                const double shx = (double)(cur.code / 3 - 1) * T.gs.wx, shy = (double)(cur.code % 3 - 1) * T.gs.wy;
-                const S *__restrict__ Bs = buf + s * GR_CAP;
-                if (two) {
-                    const double sx[2] = { tx[0] + shx, tx[1] + shx }, sy[2] = { ty[0] + shy, ty[1] + shy };
-                    kde_accumulate_t<DIM, CLAMP, 2>(Bs, cur.total, tabl, sx, sy, tz, acc);
-                } else {
-                    const double sx[1] = { tx[0] + shx }, sy[1] = { ty[0] + shy }, tz1[1] = { tz[0] };
-                    double a1v[1] = { acc[0] };
-                    kde_accumulate_t<DIM, CLAMP, 1>(Bs, cur.total, tabl, sx, sy, tz1, a1v);
-                    acc[0] = a1v[0];
+                const int cdx = (cur.code * 11) >> 5, cdy = cur.code - 3 * cdx;           // code / 3, code % 3 for code < 9
+                const double shx = cdx == 1 ? 0.0 : (cdx ? T.gs.wx : -T.gs.wx), shy = cdy == 1 ? 0.0 : (cdy ? T.gs.wy : -T.gs.wy);
+                S *Bs = buf + s * GR_CAP;
+                int nnear = cur.total;
+                if (use_far) nnear = kde_split_batch<DIM>(Bs, cur.total, hwx, hwy, ri2f, gcx + shx, gcy + shy, FS, lane);
+                {
+                    double sx[GR_R], sy[GR_R];
+#pragma unroll
+                    for (int r = 0; r < GR_R; r++) { sx[r] = tx[r] + shx; sy[r] = ty[r] + shy; }
+                    kde_accumulate_t<DIM, CLAMP, GR_R>(Bs, nnear, tabl, sx, sy, tz, acc);
                 }
-                __syncwarp();
+                if (use_far) {
+                    kde_far_sum<DIM, GR_R>((const typename FarT<DIM>::type*)(Bs + nnear), cur.total - nnear, ftx, fty, ftz, facc);
+                    __syncwarp();
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the next bulk copy into this stage follows generic stores
+                } else __syncwarp();
                 s ^= 1; have = more; cur = nxt;
             }
-            double *__restrict__ out = out_all + (size_t)lab * out_stride;
+            if (use_far) {
+                bool redo = false;
 #pragma unroll
-            for (int r = 0; r < 2; r++) {
-                const int j = a0 + lane + r * 32;
-                if (j < a1) atomicAdd(out + __ldg(tperm + j), acc[r] * T.oscale);
+                for (int r = 0; r < GR_R; r++) redo |= a0 + lane + 32 * r < a1 && (double)facc[r] > KDE_FAR_SHARE * acc[r];
+                if (__any_sync(0xffffffffu, redo)) {
+#pragma unroll
+                    for (int r = 0; r < GR_R; r++) { acc[r] = 0.0; facc[r] = 0.f; }
+                    use_far = false;
+                    goto again;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < GR_R; r++) {
+                const int j = a0 + lane + 32 * r;
+                if (j < a1) atomicAdd(out_all + (size_t)lab * out_stride + __ldg(tperm + j), (acc[r] + (double)facc[r]) * T.oscale);
             }
         }
     }
 }
 
-// pairs the group kernel evaluates: sum over groups of (#targets) x (#sources of every label in the window)
+// pairs the group kernel evaluates: sum over groups of (#targets) x (#sources of every label in the window);
+// total[0] = all pairs, total[1] = the near-field (fp64) ones
 __global__ void __launch_bounds__(128) k_kde_groups_count(const KdeGroup *__restrict__ groups, const int32_t *__restrict__ gtotal,
                                                           const int32_t *__restrict__ tstart, const int32_t *__restrict__ sstart_all,
+                                                          const double *__restrict__ src, int sstride,
                                                           int nlabels, KdeTiling T, unsigned long long *total) {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ncell = T.gs.ncx * T.gs.ncy, npieces = 2 * (T.B + 2 * T.mf);
-    unsigned long long mine = 0ull;
+    const int ncell = T.gs.ncx * T.gs.ncy, nrows = T.B + 2 * T.mf;
+    unsigned long long mine = 0ull, near_ = 0ull;
     if (g < gtotal[0]) {
         const KdeGroup G = groups[g];
         for (int pa = G.ca; pa <= G.cb; pa += T.wmax) {
@@ -584,18 +721,29 @@ __global__ void __launch_bounds__(128) k_kde_groups_count(const KdeGroup *__rest
                 xlo = T.gs.b0x + (double)pa * T.cxs; xhi = T.gs.b0x + (double)(pb + 1) * T.cxs;
             }
             if (a0 >= a1) continue;
-            unsigned long long nsrc = 0ull;
-            for (int l = 0; l < nlabels; l++)
-                for (int q = 0; q < npieces; q++) {
-                    int off, cnt, code;
-                    kde_group_piece(T, G.strip, xlo, xhi, q, sstart_all + (size_t)l * ncell, off, cnt, code);
+            unsigned long long nsrc = 0ull, nnear = 0ull;
+            const double ylo = T.gs.b0y + (double)G.strip * (double)T.B * T.cys, yhi = ylo + (double)T.B * T.cys;
+            for (int l = 0; l < nlabels; l++) {
+                int off, cnt, code;
+                for (int q = 0; q < 2 * nrows; q++) {
+                    kde_group_piece(T, G.strip, xlo, xhi, 2, q, sstart_all + (size_t)l * ncell, off, cnt, code);
                     nsrc += (unsigned long long)cnt;
+                    if (T.ri2 > 0.0) {               // the same test as kde_split_batch
+                        const double shx = (double)(code / 3 - 1) * T.gs.wx, shy = (double)(code % 3 - 1) * T.gs.wy;
+                        for (int i = off; i < off + cnt; i++) {
+                            const double x = src[(size_t)i * sstride] * T.gscale, y = src[(size_t)i * sstride + 1] * T.gscale;   // staged at the reference sigma's scale
+                            const double dx = fmax(fmax(xlo + shx - x, x - xhi - shx), 0.0), dy = fmax(fmax(ylo + shy - y, y - yhi - shy), 0.0);
+                            nnear += fma(dy, dy, dx * dx) >= T.ri2 ? 0ull : 1ull;
+                        }
+                    } else nnear += (unsigned long long)cnt;
                 }
+            }
             mine += nsrc * (unsigned long long)(a1 - a0);
+            near_ += nnear * (unsigned long long)(a1 - a0);
         }
     }
-    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(total, mine);
+    for (int o = 16; o > 0; o >>= 1) { mine += __shfl_xor_sync(0xffffffffu, mine, o); near_ += __shfl_xor_sync(0xffffffffu, near_, o); }
+    if ((threadIdx.x & 31) == 0 && mine) { atomicAdd(total, mine); atomicAdd(total + 1, near_); }
 }
 
 // ------------------------------------------------------------------ normalisation (TriMesh_kde.cpp:504-524)
@@ -746,6 +894,24 @@ static int kde_bin(const void *pts_, int64_t n, const KdeGrid &g, const int32_t 
     return 0;
 }
 
+// Sources at least KDE_FAR_SIGMAS sigma away from the box of a group are summed in fp32 (kde_split_batch / kde_far_sum):
+// at 4.5 sigma they carry exp(-4.5^2 / 2) = 4e-5 of a sum and an fp32 term on group-local coordinates is good to ~6e-6
+// (random) / 2.4e-7 (ex2.approx, possibly biased), i.e. <= 2e-10 of the result against the 1e-9 bar; measured against
+// the fp64 oracle on the bench frame: 1.8e-11 (5.0 sigma: 5.8e-12 = the fp64 path's own deviation, 6 % slower).
+// Only when the cut-off leaves a rim of at least one sigma beyond it.
+// half widths per gap (rounded up to float: the window may only grow), once on the host instead of a sqrt per piece
+static void kde_fill_half_widths(KdeTiling &T) {
+    for (int gap = 0; gap <= KDE_MAXGAP; gap++) {
+        const double gy = (double)gap * T.cys, h2 = T.rc2 - gy * gy;
+        T.hx[gap] = h2 > 0.0 ? nextafterf((float)sqrt(h2), INFINITY) : -1.f;
+    }
+}
+static double kde_far_radius2(double cutoff_sigmas, double sigma_scaled) {
+    if (cutoff_sigmas < KDE_FAR_SIGMAS + 1.0) return 0.0;
+    const double r = KDE_FAR_SIGMAS * sigma_scaled;
+    return r * r;
+}
+
 struct KdeCtx {
     KdePlan p; bool cells, tiles; KdeGrid g; KdeTiling tl; int type, periodic, nsplit, nlabels; bool clamp;
     double wx, wy; float sfactor;
@@ -829,6 +995,8 @@ static int kde_front(const float *verts, int64_t nv, const int32_t *ids, int64_t
             KdeGrid gs = g;
             gs.ncx = (int)ncxd; gs.ncy = T.nty * B;
             T.B = B; T.cxs = wx / gs.ncx; T.cys = tsy / B; T.rc2 = rcut * rcut; T.gscale = 1.0; T.oscale = 1.0;
+            T.ri2 = kde_far_radius2(cutoff_sigmas, sg * scale);
+            kde_fill_half_widths(T);
             T.mf = (int)ceil(rcut / T.cys);
             const int mxmax = (int)ceil(rcut / T.cxs);
             gs.b0x = (double)box6[0] * scale; gs.b0y = (double)box6[1] * scale;
@@ -1041,6 +1209,8 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
             T.cxs = T.gs.wx / T.gs.ncx; T.cys = T.gs.wy / T.gs.ncy;
             T.gs.inv_cx = 1.0 / T.cxs; T.gs.inv_cy = 1.0 / T.cys;
             T.rc2 = rcut * rcut;
+            T.ri2 = kde_far_radius2(cutoff_sigmas, sg * scales[i]);
+            kde_fill_half_widths(T);
             T.mf = (int)ceil(rcut / T.cys);
             const int mxmax = (int)ceil(rcut / T.cxs);
             T.wmax = periodic ? T.gs.ncx - 2 * mxmax - 1 : (1 << 30);
@@ -1055,9 +1225,11 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
     } else shared = false;
     if (!shared) {
         for (int i = 0; i < nsigma; i++) {
-            const int rc = pairs ? ms_kde_evaluated_pairs(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, pairs + i, ws, ws_bytes, stream)
+            double two[2] = { 0.0, 0.0 };
+            const int rc = pairs ? ms_kde_evaluated_pairs(verts, nv, NULL, 0, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, two, ws, ws_bytes, stream)
                                  : ms_kde_labels(verts, nv, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, raw + (size_t)i * per, ws, ws_bytes, stream);
             if (rc) return rc;
+            if (pairs) { pairs[i] = two[0]; pairs[nsigma + i] = two[1]; }
         }
         return 0;
     }
@@ -1067,14 +1239,14 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
     if (pairs) {             // diagnostic: the pairs every sigma's launch evaluates on this shared binning
         for (int i = 0; i < nsigma; i++) {
             c.tl = Ts[i]; c.tl.gscale = scales[i] / c.scale;
-            MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
-            MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
+            MS_CUDA(cudaMemsetAsync(c.counter, 0, 2 * sizeof(unsigned long long), s));
+            MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, (const double*)c.ssorted, c.type == 2 ? 2 : 4, c.nlabels, c.tl, c.counter);
             MS_K(NULL, s);
             MS_LAUNCH_CHECK();
-            unsigned long long h = 0ull;
-            MS_CUDA(cudaMemcpyAsync(&h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
+            unsigned long long h[2] = { 0ull, 0ull };
+            MS_CUDA(cudaMemcpyAsync(h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
             MS_CUDA(cudaStreamSynchronize(s));
-            pairs[i] = (double)h;
+            pairs[i] = (double)h[0]; pairs[nsigma + i] = (double)h[1];
         }
         return 0;
     }
@@ -1223,15 +1395,15 @@ extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int3
     KdeCtx c;
     int rc = kde_front(verts, nv, ids, nids, labels, nlabels, type, periodic, box6, sigma, cutoff_sigmas, ws, ws_bytes, s, c);
     if (rc) return rc;
-    if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); *pairs = (double)nv * (double)c.p.ns; return 0; }
-    MS_CUDA(cudaMemsetAsync(c.counter, 0, sizeof(unsigned long long), s));
+    if (!c.cells) { MS_CUDA(cudaStreamSynchronize(s)); pairs[0] = pairs[1] = (double)nv * (double)c.p.ns; return 0; }
+    MS_CUDA(cudaMemsetAsync(c.counter, 0, 2 * sizeof(unsigned long long), s));
     if (kde_build_groups(c, s)) return 2;
-    MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, c.nlabels, c.tl, c.counter);
+    MS_K("kde_cells_count", s); k_kde_groups_count<<<ms_blocks(c.max_groups, 128), 128, 0, s>>>(c.groups, c.gstart + c.tl.nty, c.tstart, c.sst, (const double*)c.ssorted, c.type == 2 ? 2 : 4, c.nlabels, c.tl, c.counter);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
-    unsigned long long h = 0ull;
-    MS_CUDA(cudaMemcpyAsync(&h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
+    unsigned long long h[2] = { 0ull, 0ull };
+    MS_CUDA(cudaMemcpyAsync(h, c.counter, sizeof(h), cudaMemcpyDeviceToHost, s));
     MS_CUDA(cudaStreamSynchronize(s));
-    *pairs = (double)h;
+    pairs[0] = (double)h[0]; pairs[1] = (double)h[1];
     return 0;
 }

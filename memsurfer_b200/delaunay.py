@@ -81,7 +81,7 @@ def periodic_delaunay_device(xy, box0, box1, device='cuda:0', knbrs=23, blayer=0
                                       dfaces.data_ptr(), doffs.data_ptr(), fcap,
                                       C.byref(nf), C.byref(bad), ws.data_ptr(), ws.numel(), st), 'ms_delaunay_periodic')
     if bad.value < 0:
-        raise IncompleteCells('the Voronoi cells do not add up to a triangulation of the torus')
+        raise IncompleteCells(f'the Voronoi cells do not add up to a triangulation of the torus ({-bad.value} star corners off 6 V)')
     if bad.value > 0:
         raise IncompleteCells(f'{bad.value} Voronoi cells cannot be closed inside the ghost layer '
                               f'({blayer} box widths): too few points for this box', retry=blayer < 0.4)

@@ -205,23 +205,24 @@ class LeafletFrame(object):
             return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
         return None
 
-    def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0, fused=True):
-        """Pairs the KDE kernels actually evaluate in run_densities (diagnostic; synchronises)."""
+    def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0, fused=True, split=False):
+        """Pairs the KDE kernels actually evaluate in run_densities (diagnostic; synchronises).  split=True: (all pairs,
+        pairs summed in fp64) -- the cut-off kernel sums the pairs beyond 5 sigma in fp32."""
         import ctypes as C
         L = _lib.lib()
-        total = 0.0
-        out = C.c_double(0)
+        total = near = 0.0
+        out = (C.c_double * 2)()
         fused = fused and self.label_index is not None and self.label_values.shape[0] <= 64
         if fused and len(sigmas) > 1:          # the sigmas share one binning (ms_kde_labels_multi)
             sg = (C.c_float * len(sigmas))(*[float(x) for x in sigmas])
-            per = (C.c_double * len(sigmas))()
+            per = (C.c_double * (2 * len(sigmas)))()
             for t in types:
                 _lib.check(L.ms_kde_labels_multi_pairs(self.kverts.data_ptr(), self.nv, self.label_index.data_ptr(),
                                                        int(self.label_values.shape[0]), int(t), int(self.periodic), self._box(cutoff_sigmas),
                                                        sg, len(sigmas), float(cutoff_sigmas), per, self.kde_ws.data_ptr(),
                                                        self.kde_ws.numel(), _lib.stream_ptr(self.device)), 'ms_kde_labels_multi_pairs')
-                total += sum(per)
-            return total
+                total += sum(per[:len(sigmas)]); near += sum(per[len(sigmas):])
+            return (total, near) if split else total
         for t in types:
             for s in sigmas:
                 if fused:
@@ -231,11 +232,11 @@ class LeafletFrame(object):
                 for ids, nids, lab, nl in sets:
                     _lib.check(L.ms_kde_evaluated_pairs(self.kverts.data_ptr(), self.nv, _lib.ptr(ids) if nids else None, nids,
                                                         _lib.ptr(lab), nl, int(t), int(self.periodic), self._box(cutoff_sigmas),
-                                                        float(s), float(cutoff_sigmas), C.byref(out), self.kde_ws.data_ptr(),
+                                                        float(s), float(cutoff_sigmas), out, self.kde_ws.data_ptr(),
                                                         self.kde_ws.numel(), _lib.stream_ptr(self.device)),
                                'ms_kde_evaluated_pairs')
-                    total += out.value
-        return total
+                    total += out[0]; near += out[1]
+        return (total, near) if split else total
 
     def pairs_per_run(self, sigmas, types=(2,)):
         """All-pairs-equivalent KDE pair count of run_densities."""
