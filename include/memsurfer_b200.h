@@ -161,6 +161,17 @@ int ms_kde_select(const double *raw, int64_t nv, int nlabels, const uint8_t *sel
                   int get_counts, double *density_f64, float *density_f32,
                   void *ws, size_t ws_bytes, void *stream);
 
+/* ms_kde_select without a workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, kernels and results as ms_kde_select; the scratch is a
+ * static device array inside the library, held by every GPU that loads it until exit (8 MiB + 32 KiB), so
+ * nv <= MS_KDE_SELECT_STATIC_MAX_NV -- larger sizes are rejected (status 1, ms_last_error says so).  All calls on a
+ * device share that array: calls that overlap on the GPU (two streams, two threads) race; calls on one stream, or
+ * otherwise ordered, do not.  Nothing has to be cleared between calls.  The device of `stream` must be current.  */
+#define MS_KDE_SELECT_STATIC_MAX_NV 1048576
+int ms_kde_select_static(const double *raw, int64_t nv, int nlabels, const uint8_t *select, double n_selected,
+                         int get_counts, double *density_f64, float *density_f32, void *stream);
+
 /* Any number of fields of one call in two launches (instead of ms_kde_select's two per field).  raw = nrows rows of nv
  * raw sums (e.g. the (nsigma, nlabels, nv) block of ms_kde_labels_multi: nrows = nsigma * nlabels).
  * ms_kde_label_totals: partials (ms_kde_label_totals_bytes(nrows) bytes) = fixed-order partial sums of every row.

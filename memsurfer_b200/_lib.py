@@ -52,6 +52,7 @@ _SIGNATURES = {
     "ms_kde_fields": (C.c_int, [_vp, _vp, _i64, _i32, _i32, C.POINTER(_i32), C.POINTER(C.c_uint64), C.POINTER(_f64), _i32, _vp, _vp, _vp]),
     "ms_kde_select_workspace_bytes": (_sz, [_i64]),
     "ms_kde_select": (C.c_int, [_vp, _i64, _i32, C.c_char_p, _f64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "ms_kde_select_static": (C.c_int, [_vp, _i64, _i32, C.c_char_p, _f64, _i32, _vp, _vp, _vp]),
     "ms_kde_evaluated_pairs": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i32, _i32, _i32, C.POINTER(_f32), _f32, _f64, C.POINTER(_f64), _vp, _sz, _vp]),
     "ms_overlap_workspace_bytes": (_sz, [_i64]),
     "ms_overlapping_pairs": (C.c_int, [_vp, _i64, _f64, _vp, _i64, C.POINTER(_i64), C.POINTER(_f64), _vp, _sz, _vp]),

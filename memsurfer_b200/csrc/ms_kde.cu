@@ -24,6 +24,7 @@
 //   * source points are staged into shared memory by the TMA engine (cp.async.bulk + mbarrier,
 //     double buffered); one broadcast LDS.128 per source feeds the lanes' DFMA chains.
 #include "ms_common.cuh"
+#include <mutex>
 #include <math.h>
 #include <stdlib.h>
 
@@ -1301,6 +1302,50 @@ extern "C" int ms_kde_select(const double *raw, int64_t nv, int nlabels, const u
     for (int l = 0; l < nlabels; l++) if (select[l]) mask |= 1ull << l;
     MsArena A(ws, ws_bytes);
     double *dens = A.take<double>(nv), *bsum = A.take<double>(nv / RED_T + 2);
+    const int nb = ms_blocks(nv, RED_T);
+    MS_K("kde_select", s); k_kde_select<<<nb, RED_T, 0, s>>>(raw, nv, nlabels, mask, 1.0 / (double)nv, dens, bsum);
+    MS_K("kde_emit", s); k_kde_emit<<<nb, RED_T, 0, s>>>(dens, nv, get_counts ? bsum : NULL, nb, n_selected, density_f64, density_f32);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ ms_kde_select without a workspace
+// No counterpart in the reference: added for callers that cannot allocate
+// (CUDA graph capture, tight serving loops).  Same two kernels as ms_kde_select; their scratch (nv densities +
+// one partial sum per block of RED_T) lives in a file-scope device array, which every GPU that loads the library
+// holds until exit (MS_KDE_SELECT_STATIC_MAX_NV vertices: 8 MiB + 32 KiB).  Nothing in it has to start at zero --
+// both kernels overwrite what they read -- but all calls on a device share it: calls that overlap on the GPU race.
+static __device__ __align__(256) double g_kde_select_scratch[MS_KDE_SELECT_STATIC_MAX_NV + MS_KDE_SELECT_STATIC_MAX_NV / RED_T + 2];
+#define KDE_STATIC_MAX_DEVICES 64
+static double *g_kde_select_scratch_ptr[KDE_STATIC_MAX_DEVICES];      // device address of the array, per device
+static std::mutex g_kde_select_scratch_lock;
+
+extern "C" int ms_kde_select_static(const double *raw, int64_t nv, int nlabels, const uint8_t *select, double n_selected, int get_counts,
+                                    double *density_f64, float *density_f32, void *stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    MS_REQUIRE(raw && select && nv > 0 && nlabels >= 1 && nlabels <= KDE_MAX_LABELS, "ms_kde_select_static: bad arguments");
+    MS_REQUIRE(nv <= (int64_t)MS_KDE_SELECT_STATIC_MAX_NV,
+               "ms_kde_select_static: %lld vertices exceed the static scratch (MS_KDE_SELECT_STATIC_MAX_NV = %lld); use ms_kde_select with a workspace",
+               (long long)nv, (long long)MS_KDE_SELECT_STATIC_MAX_NV);
+    int dev = -1;
+    MS_CUDA(cudaGetDevice(&dev));
+    MS_REQUIRE(dev >= 0 && dev < KDE_STATIC_MAX_DEVICES, "ms_kde_select_static: device %d out of range", dev);
+    double *scratch = NULL;
+    {
+        // in host code the array's NAME is a host-side stand-in, not a device address: ask the runtime once per device
+        std::lock_guard<std::mutex> hold(g_kde_select_scratch_lock);
+        if (!g_kde_select_scratch_ptr[dev]) {
+            double *ptr = NULL;
+            MS_CUDA(cudaGetSymbolAddress((void**)&ptr, g_kde_select_scratch));
+            MS_REQUIRE(ptr != NULL, "ms_kde_select_static: no device address for the scratch array");
+            g_kde_select_scratch_ptr[dev] = ptr;
+        }
+        scratch = g_kde_select_scratch_ptr[dev];
+    }
+    unsigned long long mask = 0ull;
+    for (int l = 0; l < nlabels; l++) if (select[l]) mask |= 1ull << l;
+    double *dens = scratch, *bsum = scratch + MS_KDE_SELECT_STATIC_MAX_NV;
     const int nb = ms_blocks(nv, RED_T);
     MS_K("kde_select", s); k_kde_select<<<nb, RED_T, 0, s>>>(raw, nv, nlabels, mask, 1.0 / (double)nv, dens, bsum);
     MS_K("kde_emit", s); k_kde_emit<<<nb, RED_T, 0, s>>>(dens, nv, get_counts ? bsum : NULL, nb, n_selected, density_f64, density_f32);
