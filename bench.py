@@ -569,7 +569,7 @@ def main():
                   "note": "algorithmic bytes per SURVEY 8(d); the passes are bound by the fp64 pipe (sqrt/div/atan2, "
                           "~1 250 fp64 instructions per face) and L2 gathers, not by HBM (DESIGN.md 4.2)"}
 
-    def hbm_record(names, units, bytes_per_unit, what, extra=None):
+    def hbm_record(names, units, bytes_per_unit, what, extra=None, traffic_key=None):
         ms_ = sum(prof.get(k, {"ms": 0.0})["ms"] for k in names)
         n_ = max([prof.get(k, {"launches": 0})["launches"] for k in names] + [0])
         if not n_:
@@ -578,7 +578,7 @@ def main():
         avg = ms_ / calls
         ach = units * bytes_per_unit / (avg * 1e-3) / 1e9
         r = {"kernel": " + ".join("k_" + k for k in names if k in prof), "bound": "hbm", "achieved": ach, "peak": hbm_peak,
-             "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": hbm_src, "bytes_per_unit": bytes_per_unit,
+             "unit": "GB/s", "frac": ach / hbm_peak, "traffic": traffic.get(traffic_key) if traffic_key else None, "peak_source": hbm_src, "bytes_per_unit": bytes_per_unit,
              "units_per_call": units, "avg_ms_per_call": avg, "calls": calls, "share_of_step": ms_ / ptotal_ms, "what": what}
         r.update(extra or {})
         return r
@@ -591,11 +591,13 @@ def main():
                           {"achieved_at_36_bytes_per_point": m_pts * KNN_BYTES_PER_POINT[0] / (knn_ms / max(1, len(frames) * psteps) * 1e-3) / 1e9 if knn_ms else None,
                            "candidate_distances_per_s": sum(p["cands"] for p in pinfo) * psteps / (prof.get("knn", {"ms": 0.0})["ms"] * 1e-3) if prof.get("knn") else None,
                            "candidates_per_query": float(np.mean([p["cands"] / p["m"] for p in pinfo])),
-                           "note": "latency / L2-bound in practice (SURVEY 8(d)): report both GB/s and candidate distances/s"})
+                           "note": "latency / L2-bound in practice (SURVEY 8(d)): report both GB/s and candidate distances/s; traffic = k_knn_thread alone"},
+                          traffic_key="knn_thread")
     roof_or = hbm_record(("orient",), m_pts, ORIENT_BYTES_PER_POINT(19),
                          "MST orientation: ONE cooperative kernel per leaflet (Boruvka rounds decided on the device)",
                          {"boruvka_rounds": [p["rounds"] for p in pinfo],
-                          "graph_edges_per_s": None if not prof.get("orient") else 9.7 * m_pts * len(frames) * psteps / (prof["orient"]["ms"] * 1e-3)})
+                          "graph_edges_per_s": None if not prof.get("orient") else 9.7 * m_pts * len(frames) * psteps / (prof["orient"]["ms"] * 1e-3)},
+                         traffic_key="orient")
 
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
