@@ -198,8 +198,19 @@ def staged(a, dtype):
 
 
 def h2d(arr, device):
-    """Asynchronous host->device copy on the current stream (true DMA when arr is page-locked)."""
-    return torch.from_numpy(arr).to(device, non_blocking=True)
+    """Asynchronous host->device copy (true DMA when arr is page-locked).  The copy runs on the upload stream that
+    belongs to the current stream and the current stream waits for it: the bytes start moving at once, under
+    whatever kernels the current stream still has queued, instead of behind them."""
+    device = torch.device(device)
+    cur = torch.cuda.current_stream(device)
+    us = side_stream(device, "up")
+    with torch.cuda.stream(us):
+        t = torch.from_numpy(arr).to(device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(us)
+    cur.wait_event(ev)
+    t.record_stream(cur)
+    return t
 
 
 def d2h(t):
@@ -242,13 +253,22 @@ def home_stream(fn):
 
 
 
-def copy_stream(device):
-    """Side stream for result downloads (one per device): copies overlap the kernels of the main stream."""
-    key = torch.device(device).index or 0
+def side_stream(device, kind):
+    """Side stream of the CURRENT stream for uploads ("up") or result downloads ("down"): one per (device, work
+    stream, kind), so that the copies of one leaflet never queue behind the other leaflet's -- a download that waits
+    for leaflet B's last kernel must not hold back leaflet A's finished results."""
+    device = torch.device(device)
+    cur = torch.cuda.current_stream(device)
+    key = (device.index or 0, int(cur.cuda_stream), kind)
     st = _copy_streams.get(key)
     if st is None:
         st = _copy_streams[key] = torch.cuda.Stream(device=device)
     return st
+
+
+def copy_stream(device):
+    """Side stream for result downloads: copies overlap the kernels of the work stream."""
+    return side_stream(device, "down")
 
 
 class Pending(object):

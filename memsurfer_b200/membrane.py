@@ -431,18 +431,25 @@ class Membrane(object):
         self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas, lazy=True))
 
     @_lib.home_stream
-    def _prefetch_densities(self, types, sigmas):
+    def _prefetch_densities(self, types, sigmas, after=None):
+        """Queue the pair sums of all sigmas; returns an event that marks their end (None if nothing was queued)."""
         if self.labels is None or self.memb_smooth is None or len(sigmas) < 2:
-            return
+            return None
         values, inverse = self._label_table()
         if values.shape[0] > self.MAX_FUSED_LABELS:
-            return
+            return None
         mesh = self._adopt(self.memb_smooth)
         if mesh._label_index is None:
             mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
+        queued = False
         for t in types:
             if t in (2, 3):
-                mesh.density_labels_prefetch(t, sigmas, self.KDE_CUTOFF_SIGMAS)
+                queued |= bool(mesh.density_labels_prefetch(t, sigmas, self.KDE_CUTOFF_SIGMAS, after=after))
+        if not queued:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(mesh.device))
+        return ev
 
     @staticmethod
     def compute_thickness(a, b, mtype='smooth'):
@@ -490,8 +497,16 @@ class Membrane(object):
     @staticmethod
     def compute_densities(membranes, types, sigmas, get_nlipdis, l):
         labels = [] if l == 'all' else [l]
-        for m in membranes:            # label-fused path: all sigmas of a type on one binning of the vertices
-            m._prefetch_densities(types, sigmas)
+        # label-fused path: all sigmas of a type on one binning of the vertices.  The membranes of a call run on their
+        # own streams; their pair sums are chained (each waits for the previous one's) so that the leaflets FINISH one
+        # after the other: the result downloads of the first then run under the kernels of the second instead of all
+        # downloads piling up behind the last kernel of the frame (the persistent pair kernels fill the GPU either way).
+        done = {}                      # per device
+        for m in membranes:
+            dkey = str(getattr(m, 'device', None))
+            ev = m._prefetch_densities(types, sigmas, after=done.get(dkey))
+            if ev is not None:
+                done[dkey] = ev
         for t in types:
             names = ['density_type{0}_{1}_k{2:.1f}'.format(t, l, s) for s in sigmas]
             for m in membranes:

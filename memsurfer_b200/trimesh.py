@@ -648,9 +648,10 @@ class TriMesh(object):
         return raw[0]
 
     @_lib.home_stream
-    def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0):
+    def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0, after=None):
         """Raw per-label sums of SEVERAL sigmas in one ms_kde_labels_multi call (the vertices are binned once);
-        fills the cache density_labels_device reads.  No-op for sigmas that are already cached."""
+        fills the cache density_labels_device reads.  No-op (returns False) for sigmas that are already cached.
+        `after`: a CUDA event the launches wait for."""
         _lib.require_cuda()
         L = _lib.lib()
         dev = self.device
@@ -658,7 +659,9 @@ class TriMesh(object):
         cache = d.setdefault('kde_raw', {})
         todo = [float(s) for s in sigmas if (int(type), float(s), float(cutoff_sigmas)) not in cache]
         if len(todo) < 2 or self._label_index is None:
-            return
+            return False
+        if after is not None:                 # see Membrane.compute_densities: one leaflet's pair sums after the other's
+            torch.cuda.current_stream(dev).wait_event(after)
         kverts = self._kde_verts_device()
         nv = kverts.shape[0]
         if 'labels' not in d:
@@ -671,6 +674,7 @@ class TriMesh(object):
                                          float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
                                          _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
         self._kde_raw_store([(int(type), s_, float(cutoff_sigmas)) for s_ in todo], raw)
+        return True
 
     @_lib.home_stream
     def density_select_device(self, raw, select, get_nlipids):
