@@ -594,7 +594,7 @@ def main():
                            "note": "latency / L2-bound in practice (SURVEY 8(d)): report both GB/s and candidate distances/s; traffic = k_knn_thread alone"},
                           traffic_key="knn_thread")
     roof_or = hbm_record(("orient",), m_pts, ORIENT_BYTES_PER_POINT(19),
-                         "MST orientation: ONE cooperative kernel per leaflet (Boruvka rounds decided on the device)",
+                         "MST orientation: ONE cooperative kernel per leaflet on HALF the SMs (Boruvka rounds decided on the device); the two leaflets of a frame run side by side on their streams, so avg_ms_per_call is also the wall time per FRAME (DESIGN.md 4.3)",
                          {"boruvka_rounds": [p["rounds"] for p in pinfo],
                           "graph_edges_per_s": None if not prof.get("orient") else 9.7 * m_pts * len(frames) * psteps / (prof["orient"]["ms"] * 1e-3)},
                          traffic_key="orient")
@@ -740,6 +740,7 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
                 for st_ in streams:
                     main.wait_stream(st_)
             rec = torch.stack(recs)
+            e_mid.record()                                  # this rank's frames are queued up to here; then the exchange
             return gather_summaries(rec) if world > 1 else rec
 
         for fr in sets[0]:
@@ -747,16 +748,21 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
         barrier()
         L = _lib.lib()
         L.ms_launch_count(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0, e1, e_mid = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        t_host = time.perf_counter()
         e0.record(); run_all(); e1.record()
+        t_host = (time.perf_counter() - t_host) * 1e3       # host time to QUEUE the rank's frames (launch-bound if ~ ms_total)
         torch.cuda.synchronize()
         launches = int(L.ms_launch_count(1))
         per_rank = gather_floats(e0.elapsed_time(e1))
+        per_rank_frames = gather_floats(e0.elapsed_time(e_mid))
+        per_rank_host = gather_floats(t_host)
         ms = max(per_rank)
         return {"config": f"configs[3]: {args.trajectory_frames} frames x 100k lipids (2 x {Vt} points), 8 types, sigmas {SIGMAS}, "
                           f"frame f -> rank f mod {world}; {ndistinct} distinct frames resident per rank, cycled",
                 "frames": args.trajectory_frames, "frames_per_s": args.trajectory_frames / (ms * 1e-3), "scaling": "strong",
                 "ms_total": ms, "ms_per_frame_per_rank": ms / max(1, len(mine)), "per_rank_ms": per_rank,
+                "per_rank_frames_ms": per_rank_frames, "per_rank_host_queue_ms": per_rank_host,
                 "launches_per_frame": launches / max(1, len(mine)), "collective": "one all_gather of the summary records at the end"}
     except Exception as e:
         return {"error": repr(e)}
