@@ -298,6 +298,12 @@ def d2h_async(t):
     return Pending(host, ev)
 
 
+def d2h_async_rows(t):
+    """One download for a whole (rows, n) block; returns a Pending per row (views of the one page-locked block)."""
+    p = d2h_async(t)
+    return [Pending(p.host[k], p.event) for k in range(t.shape[0])]
+
+
 class LazyResults(collections.abc.MutableMapping):
     """Mapping of numpy results whose values may still be downloading: `park(name, tensor)` starts the
     device->host copy and returns at once; ANY read access (`d[name]`, get, values, items, pop, iteration by

@@ -723,8 +723,9 @@ class TriMesh(object):
             o32 = torch.empty((nf, nv), dtype=torch.float32, device=dev)
             _lib.check(L.ms_kde_fields(raw.data_ptr(), tot.data_ptr(), nv, self._nlabels, nf, row0, masks, nsels,
                                        int(bool(get_nlipids)), o64.data_ptr(), o32.data_ptr(), _lib.stream_ptr(dev)), 'ms_kde_fields')
+            rows = _lib.d2h_async_rows(o32)             # one download for the block, a view per field
             for k, (_, n_) in enumerate(items):
-                self._fields.park(n_, o32[k])
+                self._fields.adopt(n_, rows[k])
                 self.attributes_f64.park(n_, o64[k])
         return [self._fields.raw(n_) for n_ in names]
 

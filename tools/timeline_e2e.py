@@ -40,3 +40,4 @@ print(f"{'total':26s} {tot:7.2f} ms")
 pr = cProfile.Profile()
 pr.enable(); step([]); pr.disable()
 pstats.Stats(pr).sort_stats("tottime").print_stats(22)
+pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
