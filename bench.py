@@ -445,7 +445,7 @@ def main():
     # ---- end to end through the drop-in API, from page-locked host arrays
     e2e, per_rank_e2e = None, None
     if not args.no_e2e:
-        bytes_io = {"h2d": 0, "d2h": 0}
+        bytes_io = {"h2d": 0, "d2h": 0, "queue_ms": []}
 
         def step_e2e():
             # one frame in the order of the reference's own driver (examples/ex_3lipid.py:165-175): build BOTH
@@ -454,6 +454,7 @@ def main():
             # lipid type; finally EVERY result is read back as numpy (downloads inside the timing)
             h2d = d2h = 0
             ms = []
+            t_host = time.perf_counter()
             for lf in leaflets:
                 m = Membrane(lf["points"], labels=lf["labels"], periodic=True, bbox=lf["bbox"], device=device)
                 m.compute_pnormals(18, wait=False)              # queued, like Membrane.compute() does
@@ -467,6 +468,7 @@ def main():
                 h2d += 4 * lf["labels"].shape[0]                # the per-vertex label index
             for l in ['all'] + list(range(len(FRACTIONS))):
                 Membrane.compute_densities(ms, [2], SIGMAS, True, l)
+            bytes_io["queue_ms"].append((time.perf_counter() - t_host) * 1e3)  # host time to queue the frame (no waiting in it)
             recs = []
             for m in ms:
                 mesh = m.memb_smooth
@@ -481,8 +483,10 @@ def main():
         e2e_ms, _, _, per_rank_e2e = timed(step_e2e, 2, esteps)
         e2e_ms /= esteps
         per_rank_e2e = [x / esteps for x in per_rank_e2e]
+        per_rank_queue = gather_floats(float(np.median(bytes_io["queue_ms"][-esteps:])))
         e2e = {"value": world * 1e3 / e2e_ms, "unit": "frames/s", "ms_per_step": e2e_ms,
                "h2d_bytes_per_step": bytes_io["h2d"], "d2h_bytes_per_step": bytes_io["d2h"],
+               "host_queue_ms_per_rank": per_rank_queue,
                "api": "memsurfer_b200.Membrane / TriMesh (page-locked host numpy in, numpy out)"}
 
     # ---- side measurements (every rank takes part in the trajectory; the rest is rank 0 only)

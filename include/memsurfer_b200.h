@@ -198,6 +198,20 @@ int ms_kde_labels_multi_pairs(const float *verts, int64_t nv, const int32_t *lab
                               int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
                               double *pairs, void *ws, size_t ws_bytes, void *stream);
 
+/* ms_kde_labels_multi that also emits, sigma by sigma, the normalised fields of `nsets` label sets (masks[f]: bit l =
+ * label l; n_selected[f] source vertices; HOST arrays) -- what Membrane.compute_densities (membrane.py:289-297) asks
+ * for in its loop over 'all' and every lipid type, normalised like TriMesh::kde (TriMesh_kde.cpp:504-524).  The fields
+ * of a sigma are written right after that sigma's pair sums: out_f32 / out_f64 (nsigma, nsets, nv), out_f64 may be
+ * NULL; partials = ms_kde_label_totals_bytes(nsigma * nlabels) bytes.  If host_f32 (page-locked, same shape) is
+ * given, every sigma's block is also copied there on `copy_stream` (a stream other than `stream`), ordered after its
+ * fields kernel: the downloads run under the next sigma's pair kernel.  The caller synchronises with copy_stream.   */
+int ms_kde_labels_multi_fields(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                               int type, int periodic, const float *box6, const float *sigmas, int nsigma,
+                               double cutoff_sigmas, double *raw, int nsets, const uint64_t *masks,
+                               const double *n_selected, int get_counts, double *partials, double *out_f64,
+                               float *out_f32, float *host_f32, void *copy_stream,
+                               void *ws, size_t ws_bytes, void *stream);
+
 /* Diagnostic (roofline accounting): the number of pairs ms_kde (labels == NULL) or ms_kde_labels
  * evaluates for the same arguments -- nv*n_sources for the all-pairs kernel, the sum over cells of
  * targets x window sources for the cell list.  pairs = TWO host doubles: all evaluated pairs, and those of them summed

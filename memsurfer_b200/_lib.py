@@ -47,6 +47,8 @@ _SIGNATURES = {
     "ms_kde_labels_multi_workspace_bytes": (_sz, [_i64, _i32]),
     "ms_kde_labels_multi": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i32, C.POINTER(_f32), C.POINTER(_f32), _i32, _f64, _vp, _vp, _sz, _vp]),
     "ms_kde_labels_multi_pairs": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i32, C.POINTER(_f32), C.POINTER(_f32), _i32, _f64, C.POINTER(_f64), _vp, _sz, _vp]),
+    "ms_kde_labels_multi_fields": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i32, C.POINTER(_f32), C.POINTER(_f32), _i32, _f64, _vp,
+                                             _i32, C.POINTER(C.c_uint64), C.POINTER(_f64), _i32, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ms_kde_label_totals_bytes": (_sz, [_i64]),
     "ms_kde_label_totals": (C.c_int, [_vp, _i64, _i64, _vp, _vp]),
     "ms_kde_fields": (C.c_int, [_vp, _vp, _i64, _i32, _i32, C.POINTER(_i32), C.POINTER(C.c_uint64), C.POINTER(_f64), _i32, _vp, _vp, _vp]),

@@ -1182,9 +1182,18 @@ extern "C" size_t ms_kde_labels_multi_workspace_bytes(int64_t nv, int nlabels) {
 extern "C" int ms_kde_evaluated_pairs(const float *verts, int64_t nv, const int32_t *ids, int64_t nids, const int32_t *labels, int nlabels,
                                       int type, int periodic, const float *box6, float sigma, double cutoff_sigmas,
                                       double *pairs, void *ws, size_t ws_bytes, void *stream);
+// Optional tail of every sigma inside the multi call: the normalised fields of `nsets` label sets are written (and, if
+// asked for, sent to page-locked host memory on a copy stream) as soon as that sigma's pair sums are queued -- the
+// downloads of one sigma then run under the pair kernel of the next instead of after the last one.
+struct KdeEmit {
+    int nsets; const uint64_t *masks; const double *nsel; int get_counts;
+    double *partials, *o64; float *o32, *host32; cudaStream_t copy;
+};
+static int kde_emit_sigma(const KdeEmit &E, const double *raw_i, int i, int64_t nv, int nlabels, cudaStream_t s);
+
 static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
                                  int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
-                                 double *raw, double *pairs, void *ws, size_t ws_bytes, void *stream) {
+                                 double *raw, double *pairs, void *ws, size_t ws_bytes, void *stream, const KdeEmit *emit = NULL) {
     cudaStream_t s = (cudaStream_t)stream;
     MS_REQUIRE(labels != NULL && (raw != NULL || pairs != NULL) && sigmas != NULL && nsigma >= 1, "ms_kde_labels_multi: labels, sigmas and an output are required");
     const size_t per = (size_t)nlabels * (size_t)nv;
@@ -1231,6 +1240,7 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
                                  : ms_kde_labels(verts, nv, labels, nlabels, type, periodic, box6, sigmas[i], cutoff_sigmas, raw + (size_t)i * per, ws, ws_bytes, stream);
             if (rc) return rc;
             if (pairs) { pairs[i] = two[0]; pairs[nsigma + i] = two[1]; }
+            else if (emit && kde_emit_sigma(*emit, raw + (size_t)i * per, i, nv, nlabels, s)) return 1;
         }
         return 0;
     }
@@ -1273,6 +1283,7 @@ static int kde_labels_multi_impl(const float *verts, int64_t nv, const int32_t *
         c.tl.oscale = (double)sfac[i];                // the groups kernel applies the kernel's sfactor itself
         const int rc = kde_launch_cells(c, nv, out, s, false);
         if (rc) return rc;
+        if (emit && kde_emit_sigma(*emit, out, i, nv, nlabels, s)) return 1;
     }
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
@@ -1402,6 +1413,44 @@ __global__ void __launch_bounds__(RED_T) k_kde_fields(const double *__restrict__
         if (o64) o64[(size_t)f * nv + j] = d;
         if (o32) o32[(size_t)f * nv + j] = (float)d;
     }
+}
+
+static int kde_emit_sigma(const KdeEmit &E, const double *raw_i, int i, int64_t nv, int nlabels, cudaStream_t s) {
+    double *part = E.partials + (size_t)i * nlabels * KDE_TOT_BLOCKS;
+    MS_K("kde_label_totals", s); k_kde_label_totals<<<dim3(KDE_TOT_BLOCKS, (unsigned)nlabels), RED_T, 0, s>>>(raw_i, nv, part);
+    KdeFieldSet F;
+    for (int f = 0; f < E.nsets; f++) { F.row0[f] = 0; F.mask[f] = E.masks[f]; F.nsel[f] = E.nsel[f]; }
+    const size_t off = (size_t)i * E.nsets * (size_t)nv;
+    MS_K("kde_fields", s);
+    k_kde_fields<<<dim3((unsigned)ms_blocks(nv, RED_T * FIELD_PER_T), (unsigned)E.nsets), RED_T, 0, s>>>(
+        raw_i, part, nv, nlabels, F, E.get_counts, E.o64 ? E.o64 + off : NULL, E.o32 ? E.o32 + off : NULL);
+    MS_K(NULL, s);
+    MS_LAUNCH_CHECK();
+    if (E.host32) {               // download on the copy stream, ordered after the fields kernel by an event
+        cudaEvent_t ev;
+        MS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        MS_CUDA(cudaEventRecord(ev, s));
+        MS_CUDA(cudaStreamWaitEvent(E.copy, ev, 0));
+        MS_CUDA(cudaMemcpyAsync(E.host32 + off, E.o32 + off, sizeof(float) * (size_t)E.nsets * (size_t)nv, cudaMemcpyDeviceToHost, E.copy));
+        MS_CUDA(cudaEventDestroy(ev));
+    }
+    return 0;
+}
+
+extern "C" int ms_kde_labels_multi_fields(const float *verts, int64_t nv, const int32_t *labels, int nlabels,
+                                          int type, int periodic, const float *box6, const float *sigmas, int nsigma, double cutoff_sigmas,
+                                          double *raw, int nsets, const uint64_t *masks, const double *n_selected, int get_counts,
+                                          double *partials, double *out_f64, float *out_f32, float *host_f32, void *copy_stream,
+                                          void *ws, size_t ws_bytes, void *stream) {
+    MS_REQUIRE(raw && masks && n_selected && partials && out_f32, "ms_kde_labels_multi_fields: raw, masks, n_selected, partials and out_f32 are required");
+    MS_REQUIRE(nsets >= 1 && nsets <= KDE_MAX_FIELDS && nlabels >= 1 && nlabels <= KDE_MAX_LABELS, "ms_kde_labels_multi_fields: 1 <= nsets <= %d", KDE_MAX_FIELDS);
+    for (int f = 0; f < nsets; f++)
+        MS_REQUIRE(masks[f] != 0ull && n_selected[f] > 0.0, "ms_kde_labels_multi_fields: set %d selects no source label", f);
+    MS_REQUIRE(host_f32 == NULL || (copy_stream != NULL && copy_stream != stream), "ms_kde_labels_multi_fields: downloads need a copy stream of their own");
+    KdeEmit E;
+    E.nsets = nsets; E.masks = masks; E.nsel = n_selected; E.get_counts = get_counts; E.partials = partials;
+    E.o64 = out_f64; E.o32 = out_f32; E.host32 = host_f32; E.copy = (cudaStream_t)copy_stream;
+    return kde_labels_multi_impl(verts, nv, labels, nlabels, type, periodic, box6, sigmas, nsigma, cutoff_sigmas, raw, NULL, ws, ws_bytes, stream, &E);
 }
 
 extern "C" size_t ms_kde_label_totals_bytes(int64_t nrows) { return (size_t)(nrows < 1 ? 1 : nrows) * KDE_TOT_BLOCKS * sizeof(double); }

@@ -430,8 +430,15 @@ class Membrane(object):
         lidxs = np.where(np.isin(self.labels, labels))[0]
         self.attributes.adopt(name, mesh.compute_density(type, sigma, name, get_nlipdis, lidxs, cutoff_sigmas, lazy=True))
 
+    # compute_densities is called once per label ('all', then every lipid type: examples/ex_3lipid.py:165-175).  The first
+    # call computes the pair sums of every label anyway; with this switch it also writes -- sigma by sigma, while the
+    # next sigma is being summed -- the fields of 'all' and of every single label and starts their downloads, so that
+    # the later calls find their results on the way to the host instead of queueing them behind the last kernel.
+    # Costs (1 + #labels) * #sigmas * 4 V bytes of device->host traffic whether or not the fields are asked for.
+    EMIT_LABEL_FIELDS = True
+
     @_lib.home_stream
-    def _prefetch_densities(self, types, sigmas, after=None):
+    def _prefetch_densities(self, types, sigmas, after=None, get_nlipdis=None):
         """Queue the pair sums of all sigmas; returns an event that marks their end (None if nothing was queued)."""
         if self.labels is None or self.memb_smooth is None or len(sigmas) < 2:
             return None
@@ -444,7 +451,14 @@ class Membrane(object):
         queued = False
         for t in types:
             if t in (2, 3):
-                queued |= bool(mesh.density_labels_prefetch(t, sigmas, self.KDE_CUTOFF_SIGMAS, after=after))
+                emit = None
+                if self.EMIT_LABEL_FIELDS and get_nlipdis is not None:
+                    nl = values.shape[0]
+                    sets = [list(range(nl))] + ([[k] for k in range(nl)] if nl > 1 else [])
+                    tags = ['all'] + ([values[k] for k in range(nl)] if nl > 1 else [])
+                    emit = (sets, bool(get_nlipdis),
+                            lambda s_, k, t=t, tags=tags: 'density_type{0}_{1}_k{2:.1f}'.format(t, tags[k], s_))
+                queued |= bool(mesh.density_labels_prefetch(t, sigmas, self.KDE_CUTOFF_SIGMAS, after=after, emit=emit))
         if not queued:
             return None
         ev = torch.cuda.Event()
@@ -504,7 +518,7 @@ class Membrane(object):
         done = {}                      # per device
         for m in membranes:
             dkey = str(getattr(m, 'device', None))
-            ev = m._prefetch_densities(types, sigmas, after=done.get(dkey))
+            ev = m._prefetch_densities(types, sigmas, after=done.get(dkey), get_nlipdis=get_nlipdis)
             if ev is not None:
                 done[dkey] = ev
         for t in types:

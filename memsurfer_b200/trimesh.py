@@ -82,6 +82,7 @@ class TriMesh(object):
         self.attributes = _lib.LazyResults()     # numpy on access; downloads may still be in flight
         self.attributes_f64 = LazyF64()   # fp64 twins, fetched from the device on first access
         self._fields = _lib.LazyResults() # KDE fields cached by name (TriMesh_kde.cpp:455-460)
+        self._emitted = {}                # name -> (get_nlipids, label selection) of fields written ahead of their request
         self._label_index = None         # optional per-vertex integer labels (label-fused KDE)
         self._nlabels = 0
         self._dev = {}                   # device-resident buffers
@@ -593,6 +594,7 @@ class TriMesh(object):
             total -= h['raw'].numel() * 8
             for k in [k for k, (hh, _) in cache.items() if hh is h]:
                 del cache[k]
+        return holder
 
     def _kde_totals(self, holder):
         """(nsigma * nlabels, 256) partial sums of every row of the block (one launch, cached with the block)."""
@@ -648,10 +650,14 @@ class TriMesh(object):
         return raw[0]
 
     @_lib.home_stream
-    def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0, after=None):
+    def density_labels_prefetch(self, type, sigmas, cutoff_sigmas=0.0, after=None, emit=None):
         """Raw per-label sums of SEVERAL sigmas in one ms_kde_labels_multi call (the vertices are binned once);
         fills the cache density_labels_device reads.  No-op (returns False) for sigmas that are already cached.
-        `after`: a CUDA event the launches wait for."""
+        `after`: a CUDA event the launches wait for.
+        `emit` = (sets, get_nlipids, namer): also write, sigma by sigma, the normalised fields of the label sets
+        `sets` (lists of label indices) under the names namer(sigma, k) and start their downloads inside the call
+        (ms_kde_labels_multi_fields): a field that is asked for later by that name, with the same selection and the
+        same get_nlipids, is already on its way to the host; any other request recomputes it."""
         _lib.require_cuda()
         L = _lib.lib()
         dev = self.device
@@ -669,11 +675,42 @@ class TriMesh(object):
         raw = torch.empty((len(todo), self._nlabels, nv), dtype=torch.float64, device=dev)
         ws = self._workspace('kde_ws', L.ms_kde_labels_multi_workspace_bytes(nv, self._nlabels))
         sg = (_lib.C.c_float * len(todo))(*todo)
-        _lib.check(L.ms_kde_labels_multi(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
-                                         int(bool(self.periodic)), self._kde_box(cutoff_sigmas), sg, len(todo),
-                                         float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
-                                         _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
-        self._kde_raw_store([(int(type), s_, float(cutoff_sigmas)) for s_ in todo], raw)
+        if emit is not None and len(emit[0]) * len(todo) <= 64:
+            sets, get_nlipids, namer = emit
+            C = _lib.C
+            ns, nsets = len(todo), len(sets)
+            masks, nsels = [], []
+            for sel_ in sets:
+                masks.append(int(sum(1 << int(l) for l in sel_)))
+                nsels.append(float(self._label_counts[np.asarray(sel_, dtype=np.int64)].sum()))
+            o32 = torch.empty((ns, nsets, nv), dtype=torch.float32, device=dev)
+            o64 = torch.empty((ns, nsets, nv), dtype=torch.float64, device=dev)
+            host = torch.empty((ns, nsets, nv), dtype=torch.float32, pin_memory=True)
+            tot = torch.empty(int(L.ms_kde_label_totals_bytes(ns * self._nlabels)) // 8, dtype=torch.float64, device=dev)
+            cs = _lib.copy_stream(dev)
+            _lib.check(L.ms_kde_labels_multi_fields(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
+                                                    int(bool(self.periodic)), self._kde_box(cutoff_sigmas), sg, ns, float(cutoff_sigmas),
+                                                    raw.data_ptr(), nsets, (C.c_uint64 * nsets)(*masks), (C.c_double * nsets)(*nsels),
+                                                    int(bool(get_nlipids)), tot.data_ptr(), o64.data_ptr(), o32.data_ptr(),
+                                                    host.data_ptr(), cs.cuda_stream, ws.data_ptr(), ws.numel(),
+                                                    _lib.stream_ptr(dev)), 'ms_kde_labels_multi_fields')
+            ev = torch.cuda.Event()
+            ev.record(cs)                       # after the last block's copy
+            o32.record_stream(cs)
+            for i, s_ in enumerate(todo):
+                for k, sel_ in enumerate(sets):
+                    n_ = namer(s_, k)
+                    self._fields.adopt(n_, _lib.Pending(host[i, k], ev))
+                    self.attributes_f64.park(n_, o64[i, k])
+                    self._emitted[n_] = (bool(get_nlipids), tuple(int(l) for l in sel_))
+            h = self._kde_raw_store([(int(type), s_, float(cutoff_sigmas)) for s_ in todo], raw)
+            h['totals'] = tot                   # the per-row partial sums of this block are already there
+        else:
+            _lib.check(L.ms_kde_labels_multi(kverts.data_ptr(), nv, d['labels'].data_ptr(), self._nlabels, int(type),
+                                             int(bool(self.periodic)), self._kde_box(cutoff_sigmas), sg, len(todo),
+                                             float(cutoff_sigmas), raw.data_ptr(), ws.data_ptr(), ws.numel(),
+                                             _lib.stream_ptr(dev)), 'ms_kde_labels_multi')
+            self._kde_raw_store([(int(type), s_, float(cutoff_sigmas)) for s_ in todo], raw)
         return True
 
     @_lib.home_stream
@@ -693,6 +730,15 @@ class TriMesh(object):
                                    _lib.stream_ptr(dev)), 'ms_kde_select')
         return o64, o32
 
+    def _drop_stale_emitted(self, name, get_nlipids, select):
+        """A field written ahead of its request (density_labels_prefetch(emit=...)) only stands for a request with the
+        same normalisation and the same label selection; anything else is computed afresh, like the reference would."""
+        e = self._emitted.get(name)
+        if e is not None and e != (bool(get_nlipids), tuple(int(l) for l in np.asarray(select).reshape(-1))):
+            self._emitted.pop(name, None)
+            if name in self._fields:
+                del self._fields[name]
+
     @_lib.home_stream
     def compute_density_labels_multi(self, type, sigmas, names, get_nlipids, select, cutoff_sigmas=0.0):
         """compute_density_labels for several sigmas of one label set at once: the fields that are not cached yet are
@@ -706,6 +752,8 @@ class TriMesh(object):
         sel[np.asarray(select, dtype=np.int64)] = True
         mask = int(sum(1 << int(l) for l in np.flatnonzero(sel)))
         nsel = float(self._label_counts[sel].sum())
+        for n_ in names:
+            self._drop_stale_emitted(n_, get_nlipids, select)
         todo = [(float(s_), n_) for s_, n_ in zip(sigmas, names) if n_ not in self._fields]
         by_block = {}
         for s_, n_ in todo:
@@ -739,6 +787,7 @@ class TriMesh(object):
             sel = np.zeros(self._nlabels, bool); sel[np.asarray(select, dtype=np.int64)] = True
             pidxs = np.empty([0]) if sel.all() else np.where(sel[np.maximum(self._label_index, 0)] & (self._label_index >= 0))[0]
             return self.compute_density(1, sigma, name, get_nlipids, pidxs, cutoff_sigmas, lazy=lazy)
+        self._drop_stale_emitted(name, get_nlipids, select)
         if name not in self._fields:
             raw = self.density_labels_device(type, sigma, cutoff_sigmas)
             o64, o32 = self.density_select_device(raw, select, get_nlipids)
