@@ -63,6 +63,7 @@ def parse_args():
                          "0 = all pairs, the reference's literal sum)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graphs", action="store_true", help="trajectory arm: queue every frame launch by launch instead of one CUDA graph per leaflet")
     ap.add_argument("--no-extras", action="store_true", help="skip the all-pairs, trajectory, type-3 and producer side measurements")
     ap.add_argument("--trajectory-frames", type=int, default=512, help="total frames of the configs[3] measurement (all ranks)")
     ap.add_argument("--no-pin", action="store_true", help="do not bind the rank to its own host cores")
@@ -724,6 +725,18 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
 
         streams = None if args.single_stream else [torch.cuda.Stream(device=device) for _ in range(2)]
 
+        graphs = not args.no_graphs and args.kde_cutoff > 0
+        if graphs:                     # one CUDA graph per resident leaflet: a frame is 2 launches instead of 92
+            for fs in sets:
+                for fr in fs:
+                    fr.capture(SIGMAS, 18, args.kde_cutoff)
+
+        def one(fr):
+            if graphs:
+                return fr.replay().clone()          # the graph writes its summary in place: keep a copy per frame
+            fr.run(SIGMAS, 18, args.kde_cutoff)
+            return fr.summary()
+
         def run_all():
             recs = []
             main = torch.cuda.current_stream(device)
@@ -733,12 +746,10 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
             for i in range(len(mine)):
                 for li, fr in enumerate(sets[i % ndistinct]):       # leaflet li of every frame on stream li
                     if streams is None:
-                        fr.run(SIGMAS, 18, args.kde_cutoff)
-                        recs.append(fr.summary())
+                        recs.append(one(fr))
                     else:
                         with torch.cuda.stream(streams[li]):
-                            fr.run(SIGMAS, 18, args.kde_cutoff)
-                            recs.append(fr.summary())
+                            recs.append(one(fr))
                             recs[-1].record_stream(main)
             if streams is not None:
                 for st_ in streams:
@@ -767,7 +778,10 @@ def measure_trajectory(args, rank, world, device, barrier, gather_floats):
                 "frames": args.trajectory_frames, "frames_per_s": args.trajectory_frames / (ms * 1e-3), "scaling": "strong",
                 "ms_total": ms, "ms_per_frame_per_rank": ms / max(1, len(mine)), "per_rank_ms": per_rank,
                 "per_rank_frames_ms": per_rank_frames, "per_rank_host_queue_ms": per_rank_host,
-                "launches_per_frame": launches / max(1, len(mine)), "collective": "one all_gather of the summary records at the end"}
+                "launches_per_frame": launches / max(1, len(mine)),
+                "cuda_graphs": None if not graphs else {"graphs_per_frame": 2, "kernels_per_graph": sets[0][0].graph_launches,
+                                                        "what": "LeafletFrame.capture(): one graph per leaflet, replayed per frame"},
+                "collective": "one all_gather of the summary records at the end"}
     except Exception as e:
         return {"error": repr(e)}
 

@@ -88,7 +88,8 @@ class LeafletFrame(object):
     # ------------------------------------------------------------------ the three stages
     def run_pnormals(self, knbrs=18, ndir_hint=+1):
         self.pnormals32, self.pnormals64, self.info = point_normals_device(
-            self.points, self.bbox, self.periodic, self.blayer, knbrs, ndir_hint)
+            self.points, self.bbox, self.periodic, self.blayer, knbrs, ndir_hint,
+            download_info=not torch.cuda.is_current_stream_capturing())
 
     def run_properties(self):
         L = _lib.lib()
@@ -192,6 +193,30 @@ class LeafletFrame(object):
         self.run_pnormals(knbrs)
         self.run_properties()
         self.run_densities(sigmas, cutoff_sigmas=cutoff_sigmas, fused=fused)
+
+    # ------------------------------------------------------------------ the frame as one CUDA graph
+    def capture(self, sigmas, knbrs=18, cutoff_sigmas=0.0):
+        """Record run() + summary() of this leaflet as ONE CUDA graph (the chain has no host round trip and every
+        buffer keeps its address) and return it; replay() then costs one launch instead of ~46.  Valid while the
+        shapes, the box and the sigmas stay what they were at capture time -- new coordinates of the same system
+        (an NVT trajectory) are copied into self.points / self.verts before a replay; a changed box means a new
+        capture.  The first call runs the frame once eagerly (workspaces, function attributes)."""
+        L = _lib.lib()
+        self.run(sigmas, knbrs, cutoff_sigmas)
+        self.summary()
+        torch.cuda.current_stream(self.device).synchronize()
+        g = torch.cuda.CUDAGraph()
+        L.ms_launch_count(1)
+        with torch.cuda.graph(g):
+            self.run(sigmas, knbrs, cutoff_sigmas)
+            rec = self.summary()
+        self.graph, self.graph_summary, self.graph_launches = g, rec, int(L.ms_launch_count(1))
+        return g
+
+    def replay(self):
+        """Launch the captured frame on the current stream; returns the (F,4) summary tensor (overwritten by the next replay)."""
+        self.graph.replay()
+        return self.graph_summary
 
     def _box(self, cutoff_sigmas):
         if self.periodic:

@@ -51,7 +51,18 @@ class PointNormalsInfo(dict):
         return dict.__repr__(self._resolve())
 
 
-def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1, keep=None):
+class _InfoOnDevice(object):
+    """Stand-in for a download in flight: the status block stays on the device until somebody looks at it (used while
+    a CUDA graph is being captured, where a copy on a side stream would leave the capture unjoined)."""
+
+    def __init__(self, info):
+        self.info = info
+
+    def result(self):
+        return self.info.cpu().numpy()
+
+
+def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1, keep=None, download_info=True):
     """Device pipeline of Membrane.compute_pnormals (membrane.py:124-157).
 
     points_dev: (n,3) float32 CUDA tensor.  Returns (pnormals f32 (n,3), pnormals f64 (n,3), info)
@@ -86,7 +97,7 @@ def point_normals_device(points_dev, bbox, periodic, blayer, knbrs, ndir_hint=+1
     o64 = torch.empty((n, 3), dtype=torch.float64, device=dev)
     _lib.check(L.ms_finish_pnormals(nrm.data_ptr(), n, int(ndir_hint), o32.data_ptr(), o64.data_ptr(),
                                     ws.data_ptr(), ws.numel(), st), 'ms_finish_pnormals')
-    pinfo = PointNormalsInfo(_lib.d2h_async(info))
+    pinfo = PointNormalsInfo(_lib.d2h_async(info) if download_info else _InfoOnDevice(info))
     if keep is not None:
         m = pinfo['m']
         keep.update(points_all=pts_all[:m], ghost_src=gsrc[:m], nbr=nbr[:m], normals_all=nrm[:m], normals_pca=keep['normals_pca'][:m])

@@ -148,3 +148,44 @@ def test_config4_large_deformed_membrane_sigma_sweep(oracle):
     mesh.compute_density_labels(3, 20.0, "t3", False, [0, 1, 2], cutoff_sigmas=8.0)
     raw3 = oracle.kde_raw_targets(pts, np.zeros(0, np.int32), tg, 3, 20.0, bb) / V
     ok, err = close(mesh.attributes_f64["t3"][tg], raw3); assert ok, err
+
+
+@pytest.mark.gpu
+def test_leaflet_frame_as_cuda_graph_equals_eager_run():
+    """LeafletFrame.capture()/replay(): the frame as one CUDA graph gives the same bits as the launch-by-launch run,
+    also after new coordinates were copied into the resident buffers (an NVT trajectory step)."""
+    import torch
+    from memsurfer_b200 import synth, TriMesh
+    from memsurfer_b200.frame import LeafletFrame
+    sig = [10.0, 20.0, 30.0]
+
+    def frame(seed):
+        pts, labels, bbox = synth.make_leaflet(6400, seed=seed, ntypes=3, fractions=[0.5, 0.3, 0.2])
+        mesh = TriMesh(pts, periodic=True)
+        mesh.set_bbox(bbox[0], bbox[1])
+        mesh.compute_delaunay()
+        return pts, labels, bbox, mesh
+
+    pts, labels, bbox, mesh = frame(3)
+    eager = LeafletFrame(pts, labels, bbox, mesh)
+    eager.run(sig, 18, 7.5)
+    want = eager.summary().cpu().numpy()
+    want_pn = eager.pnormals64.cpu().numpy()
+    g = LeafletFrame(pts, labels, bbox, mesh)
+    g.capture(sig, 18, 7.5)
+    assert g.graph_launches > 20
+    for _ in range(2):
+        got = g.replay().cpu().numpy()
+        assert np.array_equal(got, want)
+        assert np.array_equal(g.pnormals64.cpu().numpy(), want_pn)
+        assert g.info['n_unoriented'] == 0
+    # jiggle the coordinates inside the same box: same buffers, same graph
+    rng = np.random.default_rng(0)
+    pts2 = pts.copy()
+    pts2[:, 2] += rng.normal(0, 0.05, len(pts)).astype(np.float32)
+    eager2 = LeafletFrame(pts2, labels, bbox, mesh)
+    eager2.run(sig, 18, 7.5)
+    g.points.copy_(torch.from_numpy(pts2))
+    got2 = g.replay().cpu().numpy()
+    assert np.array_equal(g.pnormals64.cpu().numpy(), eager2.pnormals64.cpu().numpy())
+    assert np.array_equal(got2, eager2.summary().cpu().numpy())
