@@ -544,15 +544,50 @@ __device__ __forceinline__ int kde_split_batch(typename SrcT<DIM>::type *Bs, int
     for (int k = 0; k < K; k++) {
         if ((mn[k] >> lane) & 1u) Bs[nb + __popc(mn[k] & lt)] = v[k];
         else if ((mf[k] >> lane) & 1u) {
-            F f;
-            f.x = fx[k] * FS; f.y = fy[k] * FS;
-            if (DIM == 3) { ((float*)&f)[2] = (float)((const double*)&v[k])[2] * FS; ((float*)&f)[3] = 0.f; }
-            Fs[fb + __popc(mf[k] & lt)] = f;
+            const int j = fb + __popc(mf[k] & lt);
+            if (DIM == 2) {                        // two sources per 16 bytes: {x0, x1, y0, y1} for the packed FADD2/FFMA2 loop
+                float *q = (float*)Fs + 4 * (j >> 1) + (j & 1);
+                q[0] = fx[k] * FS; q[2] = fy[k] * FS;
+            } else {
+                F f;
+                f.x = fx[k] * FS; f.y = fy[k] * FS;
+                ((float*)&f)[2] = (float)((const double*)&v[k])[2] * FS; ((float*)&f)[3] = 0.f;
+                Fs[j] = f;
+            }
         }
         nb += __popc(mn[k]); fb += __popc(mf[k]);
     }
+    if (DIM == 2 && (fb & 1) && lane == 0) {       // odd count: the last pair is completed by a source at infinity (term 0)
+        float *q = (float*)Fs + 4 * (fb >> 1) + 1;
+        q[0] = 1e18f; q[2] = 0.f;
+    }
     __syncwarp();
     return nnear;
+}
+// 2-D far field, two sources per step on the packed fp32 pipe: FADD2 x2, FMUL2, FFMA2, 2 x MUFU.EX2, FADD2 per TWO pairs
+// (the scalar loop spends 8 issue slots per pair, of which the MUFU is one: the XU pipe sustains one per 8 cycles, so
+// the scalar loop keeps the issue port as busy as the XU -- this one leaves half of the port to the other warps)
+template <int R>
+__device__ __forceinline__ void kde_far_sum2(const float4 *Fp, int cnt, const float (&ftx)[R], const float (&fty)[R], float (&facc)[R]) {
+    float2 ntx[R], nty[R], a2[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) { ntx[r] = make_float2(-ftx[r], -ftx[r]); nty[r] = make_float2(-fty[r], -fty[r]); a2[r] = make_float2(0.f, 0.f); }
+    const int np = (cnt + 1) >> 1;
+#pragma unroll 4
+    for (int i = 0; i < np; i++) {
+        const float4 sp = Fp[i];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const float2 dx = __fadd2_rn(make_float2(sp.x, sp.y), ntx[r]), dy = __fadd2_rn(make_float2(sp.z, sp.w), nty[r]);
+            const float2 r2 = __ffma2_rn(dy, dy, __fmul2_rn(dx, dx));
+            float2 e;
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(-r2.x));
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(-r2.y));
+            a2[r] = __fadd2_rn(a2[r], e);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) facc[r] += a2[r].x + a2[r].y;
 }
 template <int DIM, int R>
 __device__ __forceinline__ void kde_far_sum(const typename FarT<DIM>::type *Fs, int cnt, const float (&ftx)[R], const float (&fty)[R],
@@ -676,7 +711,8 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
                     kde_accumulate_t<DIM, CLAMP, GR_R>(Bs, nnear, tabl, sx, sy, tz, acc);
                 }
                 if (use_far) {
-                    kde_far_sum<DIM, GR_R>((const typename FarT<DIM>::type*)(Bs + nnear), cur.total - nnear, ftx, fty, ftz, facc);
+                    if (DIM == 2) kde_far_sum2<GR_R>((const float4*)(Bs + nnear), cur.total - nnear, ftx, fty, facc);
+                    else kde_far_sum<DIM, GR_R>((const typename FarT<DIM>::type*)(Bs + nnear), cur.total - nnear, ftx, fty, ftz, facc);
                     __syncwarp();
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the next bulk copy into this stage follows generic stores
                 } else __syncwarp();
