@@ -294,17 +294,24 @@ __global__ void __launch_bounds__(256) k_kde_cell_gather(const typename SrcT<DIM
 // their order, i.e. bit-reproducible.  The 256-entry exp2 table is replicated 16x (entry e of copy k
 // at double index e*16+k, lane l reads copy l&15): every lane of a half-warp owns its bank pair, so
 // the table LDS.64 costs 2 wavefronts instead of ~6.5 (ncu on the first cell-list kernel: 4.1-way conflicts).
+// CTA shape: registers beat warps.  No pipe is saturated (fp64 ~40 %, XU ~20 %, issue ~70 %): the loop is bound by
+// dependent chains, so what counts is how many pairs a warp keeps in flight.  16 warps per SM with 128 registers each
+// and 16 sources x 2 targets unrolled beat 24 warps with 80 registers (same box, ms per frame of the 8 launches):
+//   12 x 2, unroll 8: 7.62 | 8 x 2, unroll 8: 6.88 | 8 x 2, unroll 16: 6.77 | 8 x 2, unroll 32: 6.99 | 16 x 1: 6.89
+//   6 x 2: 7.29 | 12 x 1: 7.27 | 7 x 2: 8.08 | 10 x 2: 7.83 | 20 x 1: 7.86 | stages of 96 / 160 / 192 sources: 6.82 / 6.87 / 7.56
 #ifndef GR_NW
-#define GR_NW 12                 // warps per CTA
+#define GR_NW 8                  // warps per CTA
 #endif
 #ifndef GR_MINB
 #define GR_MINB 2                // CTAs per SM
 #endif
 #ifndef GR_UNROLL
-#define GR_UNROLL 8
+#define GR_UNROLL 16
 #endif
 #define GR_THREADS (GR_NW * 32)
+#ifndef GR_CAP
 #define GR_CAP 128               // sources per stage (per warp)
+#endif
 #ifndef GR_TGT
 #define GR_TGT 64                // targets per group, GR_TGT/32 per lane.  Same box, ms/step of the launch series: 32: 9.40, 64: 8.12,
                                  // 96: 8.73, 128: 9.37 -- more targets share the per-batch work (planning, copies, the near/far
@@ -445,6 +452,7 @@ __global__ void __launch_bounds__(128) k_kde_group_fill(const int32_t *__restric
 struct KdePlanState { int pbase, pos, intra, c_off, c_cnt, c_code, nparts; };
 struct KdeBatch { int total, code, take_off, take_cnt, dst; };
 
+template <int CAP>
 __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling &T, int TY, double xlo, double xhi, int q_hi,
                                               const int32_t *__restrict__ sstart, int lane, KdeBatch &b) {
     for (;;) {
@@ -466,7 +474,7 @@ __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling 
         // of the stage is cut there and resumed in the next batch, so every batch but the last of a shift is full
         const unsigned other = __ballot_sync(0xffffffffu, eff > 0 && st.c_code != code);
         const int nsame = other ? __ffs(other) - 1 : 32;
-        const unsigned over = __ballot_sync(0xffffffffu, lane < nsame && eff > 0 && pre > GR_CAP);
+        const unsigned over = __ballot_sync(0xffffffffu, lane < nsame && eff > 0 && pre > CAP);
         b.code = code; b.dst = pre - eff;
         b.take_off = st.c_off + (lane == st.pos ? st.intra : 0);
         if (over == 0u) {
@@ -475,9 +483,9 @@ __device__ __forceinline__ bool kde_plan_next(KdePlanState &st, const KdeTiling 
             st.pos = nsame; st.intra = 0;
         } else {
             const int cut = __ffs(over) - 1;
-            const int part = GR_CAP - (pre - eff);       // what of the cut piece still fits (>= 0 on lane `cut`)
+            const int part = CAP - (pre - eff);       // what of the cut piece still fits (>= 0 on lane `cut`)
             b.take_cnt = lane < cut ? eff : (lane == cut ? part : 0);
-            b.total = GR_CAP;
+            b.total = CAP;
             const int part_c = __shfl_sync(0xffffffffu, part, cut);
             st.intra = (cut == st.pos ? st.intra : 0) + part_c;
             st.pos = cut;
@@ -509,6 +517,8 @@ __device__ __forceinline__ void kde_issue_batch(const KdeBatch &b, S *stage, con
 // 1/sqrt(512) (one fp64 subtraction per SOURCE, not per pair: relative error of a term ~6e-6, of the sum ~2e-11).
 // The pair loops then run over the two lists: 10 DFMA-class + 7 other instructions per near pair, FADD/FFMA +
 // MUFU.EX2 = 8 issue slots per far pair.  Returns the number of near sources.
+// sources per stage: a 3-D source is 32 bytes, so half as many keep the stage (and the CTAs per SM) what they are in 2-D
+template <int DIM> struct GrCap { static constexpr int value = DIM == 3 ? GR_CAP / 2 : GR_CAP; };
 template <int DIM> struct FarT;
 template <> struct FarT<2> { typedef float2 type; };
 template <> struct FarT<3> { typedef float4 type; };
@@ -517,7 +527,7 @@ __device__ __forceinline__ int kde_split_batch(typename SrcT<DIM>::type *Bs, int
                                                double cx, double cy, float FS, int lane) {
     typedef typename SrcT<DIM>::type S;
     typedef typename FarT<DIM>::type F;
-    constexpr int K = GR_CAP / 32;
+    constexpr int K = GrCap<DIM>::value / 32;
     S v[K];
     float fx[K], fy[K];
     unsigned mn[K], mf[K];
@@ -616,16 +626,17 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
                                                                    int nlabels, int64_t out_stride, KdeTiling T, unsigned *counter,
                                                                    double *__restrict__ out_all) {
     typedef typename SrcT<DIM>::type S;
+    constexpr int CAP = GrCap<DIM>::value;
     extern __shared__ __align__(128) unsigned char gr_smem[];
     double *tab = (double*)gr_smem;                                             // [KDE_TAB][16]
-    S *buf_all = (S*)(gr_smem + GR_TAB_BYTES);                                  // [GR_NW][2][GR_CAP]
-    uint64_t *bar_all = (uint64_t*)(gr_smem + GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S));   // [GR_NW][2]
+    S *buf_all = (S*)(gr_smem + GR_TAB_BYTES);                                  // [GR_NW][2][CAP]
+    uint64_t *bar_all = (uint64_t*)(gr_smem + GR_TAB_BYTES + (size_t)GR_NW * 2 * CAP * sizeof(S));   // [GR_NW][2]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < KDE_TAB * 16; i += GR_THREADS) {
         const double v = c_exp2_tab[i >> 4];
         tab[i] = CLAMP ? v : __hiloint2double(__double2hiint(v) + ((i >> 4) << (20 - KDE_TAB_LOG)), __double2loint(v));
     }
-    S *buf = buf_all + (size_t)warp * 2 * GR_CAP;
+    S *buf = buf_all + (size_t)warp * 2 * CAP;
     uint64_t *bar = bar_all + warp * 2;
     if (lane == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncthreads();
@@ -692,16 +703,16 @@ __global__ void __launch_bounds__(GR_THREADS, GR_MINB) k_kde_groups(const typena
             const int q_hi = nparts * r_hi;
             KdeBatch cur, nxt;
             int s = 0;
-            bool have = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, cur);
+            bool have = kde_plan_next<CAP>(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, cur);
             if (have) kde_issue_batch<S>(cur, buf, src, &bar[0], lane);
             while (have) {
-                const bool more = kde_plan_next(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, nxt);
-                if (more) kde_issue_batch<S>(nxt, buf + (s ^ 1) * GR_CAP, src, &bar[s ^ 1], lane);    // stage s^1 was drained in the previous round
+                const bool more = kde_plan_next<CAP>(st, T, gi.z, xlo, xhi, q_hi, sstart, lane, nxt);
+                if (more) kde_issue_batch<S>(nxt, buf + (s ^ 1) * CAP, src, &bar[s ^ 1], lane);    // stage s^1 was drained in the previous round
                 mbar_wait(&bar[s], (phase >> s) & 1u); phase ^= 1u << s;
                 __syncwarp();                  // the lanes leave the try_wait loop one by one: reconverge before the pair loop
                 const int cdx = (cur.code * 11) >> 5, cdy = cur.code - 3 * cdx;           // code / 3, code % 3 for code < 9
                 const double shx = cdx == 1 ? 0.0 : (cdx ? T.gs.wx : -T.gs.wx), shy = cdy == 1 ? 0.0 : (cdy ? T.gs.wy : -T.gs.wy);
-                S *Bs = buf + s * GR_CAP;
+                S *Bs = buf + s * CAP;
                 int nnear = cur.total;
                 if (use_far) nnear = kde_split_batch<DIM>(Bs, cur.total, hwx, hwy, ri2f, gcx + shx, gcy + shy, FS, lane);
                 {
@@ -1106,7 +1117,7 @@ static int kde_build_groups(const KdeCtx &c, cudaStream_t s) {
 template <int DIM, bool CLAMP>
 static int kde_run_groups(const KdeCtx &c, int64_t nv, double *out, cudaStream_t s, bool build = true) {
     typedef typename SrcT<DIM>::type S;
-    const size_t smem = GR_TAB_BYTES + (size_t)GR_NW * 2 * GR_CAP * sizeof(S) + (size_t)GR_NW * 2 * sizeof(uint64_t);
+    const size_t smem = GR_TAB_BYTES + (size_t)GR_NW * 2 * GrCap<DIM>::value * sizeof(S) + (size_t)GR_NW * 2 * sizeof(uint64_t);
     // set on every call (idempotent, a few microseconds): no per-process cache, any device, any thread.
     // Two 2-D CTAs (64 KB table + 48 KB of stages each) only fit with the whole 228 KB carved out as shared memory.
     MS_CUDA(cudaFuncSetAttribute(k_kde_groups<DIM, CLAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
