@@ -140,6 +140,35 @@ def orient_normals_device(points_dev, nbr_dev, normals_dev, phase_times=None):
     return int(info[_lib.INFO_UNORIENTED].item())
 
 
+_label_pool = None
+
+
+def _label_table_of(lab, pinned):
+    """(distinct values, per-point index into them, counts, the index as int32 [page-locked if `pinned`]) of a label
+    array.  Pure numpy that releases the GIL: Membrane.__init__ starts it on a worker thread, so that the ~2 ms it takes
+    for 500 000 points are spent while the point normals are being queued, not in front of the first KDE launch."""
+    if lab.dtype.kind in 'iu' and lab.size > 0 and lab.min() >= 0 and lab.max() < 65536:
+        # small non-negative integers: counting is much cheaper than the sort inside np.unique
+        counts = np.bincount(lab)
+        present = counts > 0
+        values = np.flatnonzero(present).astype(lab.dtype)
+        inverse = lab if present.all() else (np.cumsum(present) - 1)[lab]      # 0..L-1 all in use: the labels are their own index
+        counts = counts[present]
+    else:
+        values, inverse, counts = np.unique(lab, return_inverse=True, return_counts=True)
+    index32 = _lib.pinned_empty(inverse.shape, np.int32) if pinned else np.empty(inverse.shape, np.int32)
+    np.copyto(index32, inverse, casting='unsafe')
+    return values, inverse, counts, index32
+
+
+def _label_table_async(lab):
+    global _label_pool
+    if _label_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _label_pool = ThreadPoolExecutor(2, thread_name_prefix="ms_labels")
+    return _label_pool.submit(_label_table_of, lab, True)
+
+
 class Membrane(object):
     """Create and analyse membrane surfaces (GPU hot path, host surface producer)."""
 
@@ -191,9 +220,12 @@ class Membrane(object):
         self._pset_dev, self._pset_event, self._stream, self._overlap = None, None, None, None
         self._outside, self._points_at_upload = None, True      # self.points still equals what was uploaded
         self._pset_nbytes = self.points.nbytes
+        self._label_future = None
         if torch.cuda.is_available():
             self._stream = _lib.next_stream(self.device)
             self._upload_and_check(kwargs.get('check_overlaps', True))
+            if self.labels is not None:
+                self._label_future = _label_table_async(self.labels)
 
         self._pnormals = None            # float32 numpy once fetched
         self._pnormals_pending = None    # its download in flight (_lib.Pending)
@@ -390,22 +422,12 @@ class Membrane(object):
     MAX_FUSED_LABELS = 64
 
     def _label_table(self):
-        """Distinct label values and the per-point index into them (computed once)."""
+        """Distinct label values and the per-point index into them (computed once -- in the background since the
+        constructor when a GPU is present, see _label_table_of)."""
         if getattr(self, '_label_values', None) is None:
-            lab = self.labels
-            if lab.dtype.kind in 'iu' and lab.size > 0 and lab.min() >= 0 and lab.max() < 65536:
-                # small non-negative integers: counting is much cheaper than the sort inside np.unique
-                counts = np.bincount(lab)
-                present = counts > 0
-                self._label_values = np.flatnonzero(present).astype(lab.dtype)
-                if present.all():                  # 0..L-1 all in use: the labels are their own index
-                    self._label_inverse = lab
-                else:
-                    self._label_inverse = (np.cumsum(present) - 1)[lab]
-                self._label_counts = counts[present]
-            else:
-                self._label_values, self._label_inverse, self._label_counts = \
-                    np.unique(lab, return_inverse=True, return_counts=True)
+            fut, self._label_future = getattr(self, '_label_future', None), None
+            table = fut.result() if fut is not None else _label_table_of(self.labels, False)
+            self._label_values, self._label_inverse, self._label_counts, self._label_index32 = table
         return self._label_values, self._label_inverse
 
     @_lib.home_stream
@@ -427,7 +449,7 @@ class Membrane(object):
             fused = values.shape[0] <= self.MAX_FUSED_LABELS
         if fused:
             if mesh._label_index is None:
-                mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
+                mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts, index32=self._label_index32)
             select = np.arange(values.shape[0]) if len(labels) == 0 else np.where(np.isin(values, labels))[0]
             if select.shape[0] == 0:
                 # none of the requested labels occurs in this leaflet: the reference's np.where(np.in1d(...)) is
@@ -458,7 +480,7 @@ class Membrane(object):
             return None
         mesh = self._adopt(self.memb_smooth)
         if mesh._label_index is None:
-            mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts)
+            mesh.set_vertex_labels(inverse, values.shape[0], self._label_counts, index32=self._label_index32)
         queued = False
         for t in types:
             if t in (2, 3):
@@ -513,7 +535,7 @@ class Membrane(object):
             return False
         mesh = self._adopt(self.memb_smooth)
         if mesh._label_index is None:
-            mesh.set_vertex_labels(self._label_table()[1], self._label_values.shape[0], self._label_counts)
+            mesh.set_vertex_labels(self._label_table()[1], self._label_values.shape[0], self._label_counts, index32=self._label_index32)
         vals = mesh.compute_density_labels_multi(t, sigmas, names, get_nlipdis, select, self.KDE_CUTOFF_SIGMAS)
         for n_, v in zip(names, vals):
             self.attributes.adopt(n_, v)

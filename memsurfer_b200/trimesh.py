@@ -611,13 +611,17 @@ class TriMesh(object):
         """Drop the raw per-label pair sums kept for later compute_density_labels calls (device memory)."""
         self._dev.pop('kde_raw', None)
 
-    def set_vertex_labels(self, label_index, nlabels, counts=None):
+    def set_vertex_labels(self, label_index, nlabels, counts=None, index32=None):
         """Integer label in [0, nlabels) per vertex (negative: never a KDE source).  Enables the label-fused
-        KDE: one pass evaluates every vertex pair once and keeps the sums apart by the source's label."""
+        KDE: one pass evaluates every vertex pair once and keeps the sums apart by the source's label.
+        index32: the same index as a ready int32 array (page-locked if it is to be uploaded by DMA); used as it is."""
         label_index = np.asarray(label_index)
         if label_index.shape != (self.vertices.shape[0],):
             raise ValueError(f'{self.tag()} expects one label per vertex')
-        self._label_index = _lib.pinned_copy(label_index, np.int32)
+        if index32 is not None and index32.shape == label_index.shape and index32.dtype == np.int32:
+            self._label_index = index32
+        else:
+            self._label_index = _lib.pinned_copy(label_index, np.int32)
         self._nlabels = int(nlabels)
         self._label_counts = np.asarray(counts) if counts is not None else \
             np.bincount(label_index[label_index >= 0], minlength=self._nlabels)
