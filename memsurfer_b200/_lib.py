@@ -227,6 +227,35 @@ _copy_streams = {}
 _work_streams = {}
 
 
+class uploading(object):
+    """`with uploading(device) as keep:` -- host->device copies made inside run on the upload stream of the current
+    stream (they start at once, under whatever kernels the current stream has queued) and the current stream waits for
+    them at the end of the block.  Device tensors must be ALLOCATED inside the block too (so that the allocator never
+    hands out memory that a queued kernel of the current stream still uses) and passed to keep(t), which ties their
+    lifetime to the current stream."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+
+    def __enter__(self):
+        self.cur = torch.cuda.current_stream(self.device)
+        self.us = side_stream(self.device, "up")
+        self.ctx = torch.cuda.stream(self.us)
+        self.ctx.__enter__()
+        return self.keep
+
+    def keep(self, t):
+        t.record_stream(self.cur)
+        return t
+
+    def __exit__(self, *exc):
+        ev = torch.cuda.Event()
+        ev.record(self.us)
+        self.ctx.__exit__(*exc)
+        self.cur.wait_event(ev)
+        return False
+
+
 def next_stream(device, nstreams=2):
     """Round-robin over a small pool of work streams per device.  Every Membrane (and the meshes it drives) runs
     on one of them, so that the stream synchronisations of one leaflet (read-backs of counts, result downloads)

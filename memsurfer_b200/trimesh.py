@@ -247,17 +247,18 @@ class TriMesh(object):
             Vd = self._duplicated_verts.shape[0] if include_periodic else 0
             F0 = self.faces.shape[0]
             Ft = self._trimmed_faces.shape[0] if include_periodic else 0
-            dv = torch.empty((V + Vd, 3), dtype=torch.float32, device=self.device)
-            df = torch.empty((F0 + Ft, 3), dtype=torch.int32, device=self.device)
             host = [self.vertices, self.faces]
-            dv[:V].copy_(torch.from_numpy(self.vertices), non_blocking=True)
-            df[:F0].copy_(torch.from_numpy(self.faces.view(np.int32)), non_blocking=True)
-            if Vd:
-                dv[V:].copy_(torch.from_numpy(self._duplicated_verts), non_blocking=True)
-                host.append(self._duplicated_verts)
-            if Ft:
-                df[F0:].copy_(torch.from_numpy(self._trimmed_faces.view(np.int32)), non_blocking=True)
-                host.append(self._trimmed_faces)
+            with _lib.uploading(self.device) as keep:          # on the upload stream: under the kernels already queued
+                dv = keep(torch.empty((V + Vd, 3), dtype=torch.float32, device=self.device))
+                df = keep(torch.empty((F0 + Ft, 3), dtype=torch.int32, device=self.device))
+                dv[:V].copy_(torch.from_numpy(self.vertices), non_blocking=True)
+                df[:F0].copy_(torch.from_numpy(self.faces.view(np.int32)), non_blocking=True)
+                if Vd:
+                    dv[V:].copy_(torch.from_numpy(self._duplicated_verts), non_blocking=True)
+                    host.append(self._duplicated_verts)
+                if Ft:
+                    df[F0:].copy_(torch.from_numpy(self._trimmed_faces.view(np.int32)), non_blocking=True)
+                    host.append(self._trimmed_faces)
             d['verts'], d['faces'], d['_host'] = dv, df, tuple(host)
         d['nv'] = V
         return d

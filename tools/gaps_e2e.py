@@ -82,3 +82,11 @@ for i in range(len(merged) - 1):
     prev = max((e for e in gpu if e["cat"] == "kernel" and e["ts"] + e["dur"] <= a + 1e-3), key=lambda e: e["ts"] + e["dur"])
     print(f"  {b - a:6.0f} us at t = {a - t0:6.0f}: after {prev['name'][:28]:28s} before {nxt['name'][:28]:28s} copies: "
           + ", ".join(f"{e['name'][7:11]} {e['args'].get('bytes', 0) / 1e6:.1f}MB {e['dur']:.0f}us" for e in cps[:5]))
+agg = {}
+for e in gpu:
+    if e["cat"] == "kernel":
+        k = e["name"].split("(")[0][:40]
+        a = agg.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += e["dur"]
+print("kernel time by name (us):")
+for k, (n, d) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:16]:
+    print(f"  {k:42s} {n:4d} {d:9.0f}")
