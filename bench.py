@@ -635,6 +635,20 @@ def main():
             line["kde_type3"] = {"ms_per_leaflet": t3_ms / 3, "what": "16 type-3 fields of one leaflet (4 sigmas x (all + 3 types)), device-resident"}
         except Exception as e:
             line["kde_type3"] = {"error": repr(e)}
+        # the same 16 type-2 fields on a NON-periodic mesh of the same vertices (DistanceKernels.hpp:75-86: plain
+        # Euclidean distance, no images; the window is clipped at the data's extent)
+        try:
+            from memsurfer_b200.frame import LeafletFrame
+            lf0 = leaflets[0]
+            fmesh = TriMesh(lf0["points"], faces=np.asarray(lf0["tri"]["faces"]), periodic=False, device=device)
+            fnp = LeafletFrame(lf0["points"], lf0["labels"], lf0["bbox"], fmesh, device=device)
+            def tnp():
+                fnp.run_densities(SIGMAS, types=(2,), cutoff_sigmas=args.kde_cutoff)
+            np_ms = timed_local(tnp, 1, 3)
+            line["kde_nonperiodic"] = {"ms_per_leaflet": np_ms / 3, "what": "16 type-2 fields of one leaflet on a non-periodic mesh, device-resident"}
+            del fnp, fmesh
+        except Exception as e:
+            line["kde_nonperiodic"] = {"error": repr(e)}
         # the mesh producer is NOT part of a frame; reported beside it
         lf = leaflets[0]
         try:

@@ -225,9 +225,11 @@ class LeafletFrame(object):
                 b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
             return _lib.box6(b)
         if cutoff_sigmas > 0:
-            v = self.mesh.vertices
-            lo, hi = v.min(axis=0), v.max(axis=0)
-            return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
+            if getattr(self, '_extent', None) is None:           # once per frame object: two passes over the vertices
+                v = self.mesh.vertices
+                lo, hi = v.min(axis=0), v.max(axis=0)
+                self._extent = np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32)
+            return _lib.box6(self._extent)
         return None
 
     def evaluated_pairs(self, sigmas, types=(2,), cutoff_sigmas=0.0, fused=True, split=False):

@@ -491,9 +491,11 @@ class TriMesh(object):
                 b = np.array([b[0], b[1], 0, b[2], b[3], 0], np.float32)
             return _lib.box6(b)
         if cutoff_sigmas > 0:
-            # non-periodic cut-off: the cell list only needs the extent of the vertices
-            lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
-            return _lib.box6(np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32))
+            # non-periodic cut-off: the cell list only needs the extent of the vertices (two passes over them: kept)
+            if getattr(self, '_extent6', None) is None:
+                lo, hi = self.vertices.min(axis=0), self.vertices.max(axis=0)
+                self._extent6 = np.array([lo[0], lo[1], 0, hi[0], hi[1], 0], np.float32)
+            return _lib.box6(self._extent6)
         return None
 
     def _kde_verts_device(self):
