@@ -252,10 +252,11 @@ __device__ __forceinline__ void knn_scan_fast(const float4 *__restrict__ sorted,
 // ring-by-ring search around cell (cx,cy) until the K-th distance lies inside the explored square
 template <int K, bool FAST>
 __device__ __forceinline__ unsigned knn_search(const float4 *__restrict__ sorted, const Grid &g, const int32_t *__restrict__ start,
-                                           int cx, int cy, double qx, double qy, double qz, double (&bd)[K], int (&bi)[K], bool &tie) {
+                                           int cx, int cy, double qx, double qy, double qz, double (&bd)[K], int (&bi)[K], bool &tie,
+                                           int r0 = 0) {
     const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
     unsigned ncand = 0;
-    for (int r = 0; ; r++) {
+    for (int r = r0; ; r++) {
         for (int yy = cy - r; yy <= cy + r; yy++) {
             if (yy < 0 || yy >= g.ny) continue;
             const bool full_row = (yy == cy - r) || (yy == cy + r);
@@ -333,6 +334,183 @@ __global__ void __launch_bounds__(KNNT_T) k_knn_thread(const float4 *__restrict_
     }
 }
 
+// ---- the same search with the 3 x 3 block of cells pre-screened in float32 (r2).
+// In k_knn_thread the warp runs the K-slot exchange chain (~6 instructions per slot) whenever ANY of its lanes accepts
+// a candidate, i.e. for nearly every one of the ~63 candidates of the 3 x 3 block, although a lane only needs ~K of
+// them.  Here a thread first writes the float32 distances of the block's candidates to shared memory, finds from a
+// 32-bin histogram a threshold below which at least K of them lie (K + ~2 on average), and only those go through the
+// exact fp64 distance and the exchange chain -- every lane walking to ITS next candidate before the warp runs the
+// chain once for all of them: ~25 chain passes per warp instead of ~63.
+// Exactness: if x is one of the true K nearest then at most K - 1 candidates are closer than x; at least K candidates
+// have a float32 distance <= T, so one of them is not closer than x, and with a relative error eps (2.4e-7) of the
+// float32 distance d32(x) <= T (1 + eps)^2: the margin 1e-5 keeps every true neighbour.  The chain and its tie flags
+// are those of knn_scan_fast; a query whose block holds fewer than K or more than KNNS_CAP candidates, and the ring
+// expansion beyond the block, take the code of k_knn_thread.
+#define KNNS_CAP 96
+template <int K>
+__global__ void __launch_bounds__(KNNT_T) k_knn_select(const float4 *__restrict__ sorted, int64_t m_cap, const int64_t *__restrict__ info,
+                                                       const Grid *__restrict__ gp,
+                                                       const int32_t *__restrict__ start, int k1, int32_t *__restrict__ nbr,
+                                                       int64_t *__restrict__ info_out) {
+    extern __shared__ int32_t sm_nbr[];                   // first: float d32[KNNS_CAP][KNNT_T] + uint8 hist[32][KNNT_T]; then the output staging
+    float *smd = (float*)sm_nbr;
+    unsigned char *smh = (unsigned char*)(smd + KNNS_CAP * KNNT_T);
+    const int tid = threadIdx.x;
+    const int64_t m = ms_count(info, m_cap);
+    if ((int64_t)blockIdx.x * KNNT_T >= m) return;         // capacity-sized launch: blocks beyond the point count leave at once
+    const Grid g = *gp;
+    const int64_t q = (int64_t)blockIdx.x * KNNT_T + tid;
+    double bd[K]; int bi[K];
+#pragma unroll
+    for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
+    int qi = -1;
+    unsigned ncand = 0;
+    const bool live = q < m && g.ok;
+    float4 me = make_float4(0.f, 0.f, 0.f, 0.f);
+    int cx = 0, cy = 0, n = 0, pb0 = 0, pb1 = 0, pb2 = 0, l0 = 0, l1 = 0;
+    bool tie = false, screened = false;
+    float thr = -1.f;
+    int nsel = 0;
+    if (live) {
+        me = sorted[q];
+        qi = __float_as_int(me.w);
+        cell_of(g, me.x, me.y, cx, cy);
+        const int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.nx - 1);
+        int len[3] = { 0, 0, 0 }, pb[3] = { 0, 0, 0 };
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const int yy = cy - 1 + r;
+            if (yy < 0 || yy >= g.ny) continue;
+            pb[r] = __ldg(start + yy * g.nx + x0);
+            len[r] = __ldg(start + yy * g.nx + x1 + 1) - pb[r];
+        }
+        pb0 = pb[0]; pb1 = pb[1]; pb2 = pb[2]; l0 = len[0]; l1 = len[0] + len[1];
+        n = l1 + len[2];
+        screened = n >= K && n <= KNNS_CAP;
+        if (screened) {
+            float dmax = 0.f;
+            int i = 0;
+#pragma unroll
+            for (int r = 0; r < 3; r++)
+                for (int p = pb[r]; p < pb[r] + len[r]; p++, i++) {
+                    const float4 c = __ldg(sorted + p);
+                    const float dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
+                    const float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    smd[i * KNNT_T + tid] = d;
+                    dmax = fmaxf(dmax, d);
+                }
+            screened = dmax > 0.f && dmax < 1e30f;
+            if (screened) {
+#pragma unroll
+                for (int b = 0; b < 32; b++) smh[b * KNNT_T + tid] = 0;
+                const float scale = 32.f / dmax;
+                for (int j = 0; j < n; j++) {
+                    const int b = min(31, (int)(smd[j * KNNT_T + tid] * scale));
+                    smh[b * KNNT_T + tid]++;
+                }
+                int cum = 0, bstar = 31;
+#pragma unroll
+                for (int b = 0; b < 32; b++) {
+                    cum += smh[b * KNNT_T + tid];
+                    if (cum >= K && bstar == 31) bstar = b;
+                }
+                // every candidate of the bins 0..bstar: d * scale < bstar + 1 in float arithmetic, i.e. d below this edge
+                thr = bstar == 31 ? dmax * 1.00002f : ((float)(bstar + 1) / scale) * 1.00002f;
+                // the candidates below the threshold, compacted in place as indices (slot nsel <= j: its distance was read)
+                int *sel = (int*)smd;
+                for (int j = 0; j < n; j++)
+                    if (smd[j * KNNT_T + tid] <= thr) { sel[nsel * KNNT_T + tid] = j; nsel++; }
+            }
+        }
+    }
+    // ---- exact pass over the screened candidates, the warp in step
+    {
+        const double qx = me.x, qy = me.y, qz = me.z;
+        const int *sel = (const int*)smd;
+        const int nn = screened ? nsel : 0;
+        for (int it = 0; ; it++) {
+            const bool have = it < nn;
+            if (!__any_sync(0xffffffffu, have)) break;
+            if (have) {
+                const int i = sel[it * KNNT_T + tid];
+                const int p = i < l0 ? pb0 + i : (i < l1 ? pb1 + (i - l0) : pb2 + (i - l1));
+                const float4 c = __ldg(sorted + p);
+                const double dx = qx - (double)c.x, dy = qy - (double)c.y, dz = qz - (double)c.z;
+                double cd = dx * dx; cd += dy * dy; cd += dz * dz;
+                const int ci = __float_as_int(c.w);
+                if (!(cd < bd[K - 1])) tie |= (cd == bd[K - 1]);
+                else {
+                    if (K > 1) tie |= (bd[K - 1] == bd[K - 2]) && bd[K - 1] < DBL_MAX;
+                    double last_d = cd; int last_i = ci; bool prev = false;
+#pragma unroll
+                    for (int j = 0; j < K; j++) {
+                        const double cur_d = bd[j]; const int cur_i = bi[j];
+                        const bool lt = cd < cur_d;
+                        bd[j] = lt ? (prev ? last_d : cd) : cur_d;
+                        bi[j] = lt ? (prev ? last_i : ci) : cur_i;
+                        last_d = cur_d; last_i = cur_i; prev = lt;
+                    }
+                }
+            }
+        }
+        if (live) {
+            if (screened) {
+                ncand = (unsigned)n;
+                // is the K-th distance inside the explored 3 x 3 block?  (the test of knn_search after ring 1)
+                const double rx = (qx - (double)g.lox), ry = (qy - (double)g.loy);
+                const bool whole = cx - 1 <= 0 && cy - 1 <= 0 && cx + 1 >= g.nx - 1 && cy + 1 >= g.ny - 1;
+                const double b0 = cx - 1 > 0 ? rx - (double)(cx - 1) * g.h : DBL_MAX;
+                const double b1 = cx + 1 < g.nx - 1 ? (double)(cx + 2) * g.h - rx : DBL_MAX;
+                const double b2 = cy - 1 > 0 ? ry - (double)(cy - 1) * g.h : DBL_MAX;
+                const double b3 = cy + 1 < g.ny - 1 ? (double)(cy + 2) * g.h - ry : DBL_MAX;
+                const double bm = fmin(fmin(b0, b1), fmin(b2, b3));
+                const bool done = whole || (bm > 0.0 && bd[K - 1] < DBL_MAX && sqrt(bd[K - 1]) < bm * (1.0 - 1e-9));
+                if (!done) ncand += knn_search<K, true>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie, 2);
+            } else {
+                ncand = knn_search<K, true>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
+            }
+#pragma unroll
+            for (int j = 1; j < K; j++) tie |= (bd[j] == bd[j - 1]) && bd[j] < DBL_MAX;      // ties inside the kept list
+            if (tie) {             // rare: repeat with the exact (distance, index) order
+                if (info_out) atomicAdd((unsigned long long*)(info_out + MS_INFO_KNN_TIES), 1ull);
+#pragma unroll
+                for (int j = 0; j < K; j++) { bd[j] = DBL_MAX; bi[j] = 0x7fffffff; }
+                ncand += knn_search<K, false>(sorted, g, start, cx, cy, qx, qy, qz, bd, bi, tie);
+            }
+        }
+    }
+    if (info_out) {             // diagnostic: candidate distances evaluated (one atomic per warp)
+        unsigned long long c = ncand;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if ((tid & 31) == 0 && c) atomicAdd((unsigned long long*)(info_out + MS_INFO_KNN_CANDS), c);
+    }
+    if (q < m && !g.ok) qi = __float_as_int(sorted[q].w);      // non-finite input: the row is all -1
+    __syncthreads();                                            // the distances are dead: the block's rows take their place
+    int32_t *sm_q = sm_nbr + KNNT_T * k1;
+    sm_q[tid] = qi;
+#pragma unroll
+    for (int j = 0; j < K; j++) if (j < k1) sm_nbr[tid * k1 + j] = (bi[j] == 0x7fffffff) ? -1 : bi[j];
+    __syncthreads();
+    const float inv_k1 = 1.0f / (float)k1;
+    for (int e = tid; e < KNNT_T * k1; e += KNNT_T) {
+        int row = (int)(((float)e + 0.5f) * inv_k1);          // e / k1 for e < 4096 (exact: the quotient is far from an integer edge)
+        int col = e - row * k1;
+        if (col < 0) { row--; col += k1; } else if (col >= k1) { row++; col -= k1; }
+        const int id = sm_q[row];
+        if (id >= 0) nbr[(int64_t)id * k1 + col] = sm_nbr[e];
+    }
+}
+
+template <int K>
+static int knn_select_launch(const float4 *sorted, int64_t m_cap, const int64_t *info, const Grid *g, const int32_t *start, int k1, int32_t *nbr,
+                             int64_t *info_out, cudaStream_t s) {
+    const size_t smem = (size_t)KNNS_CAP * KNNT_T * sizeof(float) + 32 * KNNT_T;      // >= the KNNT_T * (k1 + 1) ints of the output staging
+    MS_CUDA(cudaFuncSetAttribute(k_knn_select<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_knn_select<K><<<ms_blocks(m_cap, KNNT_T), KNNT_T, smem, s>>>(sorted, m_cap, info, g, start, k1, nbr, info_out);
+    return 0;
+}
+
 template <int K>
 static void knn_thread_launch(const float4 *sorted, int64_t m_cap, const int64_t *info, const Grid *g, const int32_t *start, int k1, int32_t *nbr,
                               int64_t *info_out, cudaStream_t s) {
@@ -390,8 +568,13 @@ extern "C" int ms_knn(const float *points_all, int64_t m_cap, int64_t *info, int
     if (k1 <= 8) knn_thread_launch<8>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
     else if (k1 <= 12) knn_thread_launch<12>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
     else if (k1 <= 16) knn_thread_launch<16>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+#ifndef KNN_NO_SELECT
+    else if (k1 <= 19) { if (knn_select_launch<19>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s)) return 2; }
+    else if (k1 <= 24) { if (knn_select_launch<24>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s)) return 2; }
+#else
     else if (k1 <= 19) knn_thread_launch<19>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
     else if (k1 <= 24) knn_thread_launch<24>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
+#endif
     else knn_thread_launch<32>(cl.sorted, m_cap, info, cl.grid, cl.start, k1, nbr, info, s);
     MS_K(NULL, s);
     MS_LAUNCH_CHECK();
