@@ -21,7 +21,7 @@ launches)
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file "$OUT/launches.csv" \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-extras --single-stream > "$OUT/ncu_launches.log" 2>&1; echo "launches rc=$?" | tee -a "$OUT/rc.txt" ;;
 ncu)
-  for spec in "labels:k_kde_groups:4" "mesh:k_pad_verts|k_corner_terms|k_vertex_gather8:3" "normals:k_knn_thread|k_pca|k_orient:3"; do
+  for spec in "labels:k_kde_groups:4" "mesh:k_pad_verts|k_corner_terms|k_vertex_gather8:3" "normals:k_knn_select|k_knn_thread|k_pca|k_orient:3"; do
     mode=${spec%%:*}; rest=${spec#*:}; rx=${rest%%:*}; cnt=${rest##*:}
     timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$rx" -c "$cnt" -f -o "$OUT/ncu_$mode" \
         python tools/prof_kde.py --mode "$mode" > "$OUT/ncu_$mode.log" 2>&1; echo "ncu_$mode rc=$?" | tee -a "$OUT/rc.txt"
