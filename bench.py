@@ -63,6 +63,8 @@ def parse_args():
                          "0 = all pairs, the reference's literal sum)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--split-streams", action="store_true",
+                    help="experiment: the point-normal chain of a leaflet on a stream of its own, beside its mesh + KDE work")
     ap.add_argument("--no-graphs", action="store_true", help="trajectory arm: queue every frame launch by launch instead of one CUDA graph per leaflet")
     ap.add_argument("--no-extras", action="store_true", help="skip the all-pairs, trajectory, type-3 and producer side measurements")
     ap.add_argument("--trajectory-frames", type=int, default=512, help="total frames of the configs[3] measurement (all ranks)")
@@ -354,6 +356,7 @@ def main():
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
 
     side_streams = None if args.single_stream else [torch.cuda.Stream(device=device) for _ in frames]
+    normal_streams = [torch.cuda.Stream(device=device) for _ in frames] if args.split_streams else None
     use_streams = [True]
 
     def step_local(cutoff=None):
@@ -368,7 +371,15 @@ def main():
                 continue
             side_streams[i].wait_stream(main)
             with torch.cuda.stream(side_streams[i]):
-                fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
+                if normal_streams is not None:
+                    normal_streams[i].wait_stream(side_streams[i])
+                    with torch.cuda.stream(normal_streams[i]):
+                        fr.run_pnormals(18)
+                    fr.run_properties()
+                    fr.run_densities(SIGMAS, cutoff_sigmas=args.kde_cutoff if cutoff is None else cutoff)
+                    side_streams[i].wait_stream(normal_streams[i])
+                else:
+                    fr.run(SIGMAS, 18, args.kde_cutoff if cutoff is None else cutoff)
                 recs.append(fr.summary())
                 recs[-1].record_stream(main)
         if side_streams is not None and use_streams[0]:
