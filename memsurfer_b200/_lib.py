@@ -329,6 +329,16 @@ def d2h_async(t):
     return Pending(host, ev)
 
 
+_in_flight = []
+
+
+def keep_until(event, obj):
+    """Hold a reference to `obj` (page-locked memory a copy of the LIBRARY is writing to -- torch's pinned-memory cache
+    only knows about copies it issued itself) until `event` has completed; finished entries are dropped on every call."""
+    _in_flight[:] = [(e, o) for e, o in _in_flight if not e.query()]
+    _in_flight.append((event, obj))
+
+
 def d2h_async_rows(t):
     """One download for a whole (rows, n) block; returns a Pending per row (views of the one page-locked block)."""
     p = d2h_async(t)

@@ -704,6 +704,7 @@ class TriMesh(object):
             ev = torch.cuda.Event()
             ev.record(cs)                       # after the last block's copy
             o32.record_stream(cs)
+            _lib.keep_until(ev, host)           # the copies were issued by the library: keep the block out of torch's cache till then
             for i, s_ in enumerate(todo):
                 for k, sel_ in enumerate(sets):
                     n_ = namer(s_, k)
