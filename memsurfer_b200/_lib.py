@@ -332,10 +332,16 @@ def d2h_async(t):
 _in_flight = []
 
 
+def release_finished():
+    """Drop the references keep_until holds for copies that have completed (call before allocating page-locked memory,
+    so that the blocks of the previous frame are back in torch's cache by then)."""
+    _in_flight[:] = [(e, o) for e, o in _in_flight if not e.query()]
+
+
 def keep_until(event, obj):
     """Hold a reference to `obj` (page-locked memory a copy of the LIBRARY is writing to -- torch's pinned-memory cache
-    only knows about copies it issued itself) until `event` has completed; finished entries are dropped on every call."""
-    _in_flight[:] = [(e, o) for e, o in _in_flight if not e.query()]
+    only knows about copies it issued itself) until `event` has completed."""
+    release_finished()
     _in_flight.append((event, obj))
 
 

@@ -692,6 +692,7 @@ class TriMesh(object):
                 nsels.append(float(self._label_counts[np.asarray(sel_, dtype=np.int64)].sum()))
             o32 = torch.empty((ns, nsets, nv), dtype=torch.float32, device=dev)
             o64 = torch.empty((ns, nsets, nv), dtype=torch.float64, device=dev)
+            _lib.release_finished()
             host = torch.empty((ns, nsets, nv), dtype=torch.float32, pin_memory=True)
             tot = torch.empty(int(L.ms_kde_label_totals_bytes(ns * self._nlabels)) // 8, dtype=torch.float64, device=dev)
             cs = _lib.copy_stream(dev)
