@@ -131,6 +131,24 @@ def test_periodic_delaunay_lattice_and_clustered_sets():
 
 
 @pytest.mark.gpu
+def test_periodic_delaunay_lattice_with_a_spacing_that_is_no_power_of_two():
+    """The xy lattice of the reference's examples/data/noisy.off: 101 x 101 points 0.02 apart in the box [-1.01, 1.01]^2.
+    Neither the coordinates nor the period are dyadic, so the float32 ghost images are rounded copies and the same four
+    cocircular points look slightly different from every cell -- the predicates must still agree (exact image
+    coordinates, canonical order), else the stars do not glue (this input raised IncompleteCells before)."""
+    from memsurfer_b200.delaunay import periodic_delaunay_device
+    g = (np.arange(101, dtype=np.float64) * 0.02 - 1.0).astype(np.float32)
+    xy = np.ascontiguousarray(np.stack(np.meshgrid(g, g, indexing='ij'), axis=-1).reshape(-1, 2))
+    b0, b1 = np.array([-1.01, -1.01, 0], np.float32), np.array([1.01, 1.01, 0], np.float32)
+    gf, go = periodic_delaunay_device(xy, b0, b1)
+    _torus_checks(xy, gf, go, (b1[:2] - b0[:2]).astype(np.float64))
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(xy.shape[0])                          # the answer must not depend on the numbering being a raster
+    gf2, go2 = periodic_delaunay_device(np.ascontiguousarray(xy[perm]), b0, b1)
+    _torus_checks(np.ascontiguousarray(xy[perm]), gf2, go2, (b1[:2] - b0[:2]).astype(np.float64))
+
+
+@pytest.mark.gpu
 def test_periodic_delaunay_too_few_points_raises():
     """A box with far too few points for a periodic triangulation inside the ghost layer: reported, not papered over
     with a host triangulation."""
