@@ -129,7 +129,12 @@ __global__ void __launch_bounds__(256) k_pad_verts(const float *__restrict__ ver
 //    an end point that is an original vertex (every face on the edge is in that list); edges between two
 //    duplicated vertices feed dropped rows only.  The neighbour's unit normal and area are recomputed from its
 //    own three vertices (same operations as for g: the result does not depend on who computes it).
-__global__ void __launch_bounds__(128) k_corner_terms(const float4 *__restrict__ v4, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
+// 12 blocks of 128 threads per SM (40 registers, a few spilled words): the pass waits on dependent gathers, so resident
+// warps count for more than registers (0.339 -> 0.307 ms per frame; 16 blocks: the same)
+#ifndef CT_MINB
+#define CT_MINB 12
+#endif
+__global__ void __launch_bounds__(128, CT_MINB) k_corner_terms(const float4 *__restrict__ v4, const uint32_t *__restrict__ faces, int64_t nf, int64_t nv,
                                                       const int32_t *__restrict__ off, const int32_t *__restrict__ adj,
                                                       const uint8_t *__restrict__ keep, int want_mean,
                                                       double *__restrict__ al, double *__restrict__ He, uint8_t *__restrict__ hflag) {
@@ -197,7 +202,11 @@ __global__ void __launch_bounds__(128) k_corner_terms(const float4 *__restrict__
 #define VG_T 128
 #define VG_V 16           // vertices per block (x VG_Q quantities = VG_T summing threads)
 #define VG_Q 8            // doubles per entry: pn.x, pn.y, pn.z, corner area, triangle area, angle term, H term 0, H term 1
-__global__ void __launch_bounds__(VG_T) k_vertex_gather8(
+// 12 blocks per SM (40 registers): 0.43 -> 0.33 ms per frame; 14 blocks spill into the summing loop (0.41)
+#ifndef VG_MINB
+#define VG_MINB 12
+#endif
+__global__ void __launch_bounds__(VG_T, VG_MINB) k_vertex_gather8(
         const float4 *__restrict__ v4, const uint32_t *__restrict__ faces, int64_t nv,
         const int32_t *__restrict__ off, const int32_t *__restrict__ adj, const uint8_t *__restrict__ keep,
         const double *__restrict__ al, const double *__restrict__ He, const uint8_t *__restrict__ hflag,
