@@ -18,9 +18,11 @@
 //       k_kde_pairs   all V x n_ids pairs (the reference's sum).  Single-wrap minimum image as
 //                     min(|dx|, boxw-|dx|): the reference adds boxw to the smaller coordinate when
 //                     |dx| >= boxw/2, and (|dx|-boxw)^2 == min(|dx|, boxw-|dx|)^2;
-//       k_kde_groups  pairs inside the window box(32 targets) (+) disc(cutoff_sigmas*sigma) of a fine cell list
+//       k_kde_groups  pairs inside the window box(64 targets) (+) disc(cutoff_sigmas*sigma) of a fine cell list
 //                     (dropped relative tail mass <= exp(-cutoff_sigmas^2/2)); the periodic image shift is
-//                     applied once per staged batch, so there is no per-pair wrap arithmetic at all;
+//                     applied once per staged batch, so there is no per-pair wrap arithmetic at all; sources at
+//                     least 4.5 sigma away from the box are summed in float32 on the packed fp32 pipe + MUFU.EX2
+//                     (their share of a sum is < 1e-4: kde_split_batch / kde_far_sum2, with an fp64 redo guard);
 //   * source points are staged into shared memory by the TMA engine (cp.async.bulk + mbarrier,
 //     double buffered); one broadcast LDS.128 per source feeds the lanes' DFMA chains.
 #include "ms_common.cuh"
